@@ -1,0 +1,41 @@
+"""Shared helpers for replaying golden fixtures through a finder-like object."""
+import hashlib
+import os
+
+import numpy as np
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+STREAM_CASES = ["stream_wikipedia6k", "stream_unipartite5k", "stream_adv_k3", "stream_adv_k20", "stream_adv_replay",
+                "stream_ties", "stream_ties_k8", "stream_nofake", "stream_k1", "stream_k31"]
+
+
+def load(name):
+    return np.load(os.path.join(GOLDEN, name + ".npz"))
+
+
+def digest(arrs):
+    h = hashlib.sha256()
+    for a in arrs:
+        h.update(np.ascontiguousarray(a).tobytes())
+    return np.frombuffer(h.digest(), dtype=np.uint8).copy()
+
+
+def batches(g):
+    """Yield (b, nodes int32, ts f64, eidx int64) exactly as make_golden.py fed the reference."""
+    src, dst, neg, ts, eidx = g["src"], g["dst"], g["neg"], g["ts"], g["eidx"]
+    bs, E, no_fake = int(g["bs"]), len(g["src"]), bool(g["no_fake"])
+    for b in range((E + bs - 1) // bs):
+        lo, hi = b * bs, min(E, (b + 1) * bs)
+        parts = [src[lo:hi], dst[lo:hi]] + ([] if no_fake else [neg[lo:hi]])
+        yield b, np.concatenate(parts).astype(np.int32), np.concatenate([ts[lo:hi]] * len(parts)), eidx[lo:hi].astype(np.int64)
+
+
+def replay(finder, g):
+    """Run all batches; return per-batch digests and the kept full outputs of the last batches."""
+    no_fake = bool(g["no_fake"])
+    digs, outs = [], {}
+    for b, nodes, tt, ee in batches(g):
+        out = finder.streaming_topk_no_fake(nodes, tt, ee) if no_fake else finder.streaming_topk(nodes, tt, ee)
+        digs.append(digest([a for lst in out for a in lst]))
+        outs[b] = [np.stack(x) for x in out]
+    return np.stack(digs), outs
