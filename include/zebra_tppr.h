@@ -1,0 +1,113 @@
+/*
+ * zebra_tppr.h — C ABI of libzebra_tppr.so (sm_100a), the B200-native T-PPR hot path of Zebra.
+ *
+ * Each entry point is what a maintainer of the reference would bind (ctypes)
+ * in place of the numba jitclass methods named beside it.  Reference = LuckyLYM/Zebra,
+ * paths relative to the reference root.
+ *
+ * Conventions
+ *   - every function returns 0 on success, non-zero on error; zebra_last_error() gives the text.
+ *     No exceptions cross the ABI.
+ *   - plain pointers and sizes only.  "host" pointers are ordinary CPU memory, "dev" pointers are
+ *     CUDA device memory owned by the caller (e.g. torch tensors).  The library never frees
+ *     caller memory.
+ *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream); all device work of
+ *     a call is enqueued on it.  A handle is not re-entrant.
+ *   - node ids index rows of the tables: 0 <= id < num_nodes (the reference reserves id 0 as the
+ *     padding node, train.py:124-125).
+ */
+#ifndef ZEBRA_TPPR_H
+#define ZEBRA_TPPR_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct zebra_tppr zebra_tppr_t;
+
+/* ---- lifetime: replaces tppr_finder.__init__ (utils/util.py:393-400) ------------------------ */
+
+/* k <= 31 (one candidate pair per warp lane); n_tppr <= 8. */
+int zebra_tppr_create(zebra_tppr_t **out, int64_t num_nodes, int32_t k, int32_t n_tppr,
+                      const double *alpha_list, const double *beta_list, int32_t device);
+int zebra_tppr_destroy(zebra_tppr_t *h);
+
+/* Bytes of ONE instance's table (num_nodes fixed-size records) and of one record.  Record
+ * layout (little endian): { int32 eidx, int32 node }[k] | f64 ts[k] | f64 score[k] | f64 norm |
+ * int32 count | pad to a multiple of 128 B.  A zero-filled table is the empty state. */
+size_t zebra_tppr_table_bytes(const zebra_tppr_t *h);
+size_t zebra_tppr_record_bytes(const zebra_tppr_t *h);
+
+/* Point the handle at n_tppr caller-owned device tables (one per (alpha,beta) instance).
+ * reset_tppr / backup_tppr / restore_tppr / restore_val_tppr (utils/util.py:402-444) are done by
+ * the caller swapping or zero-filling tables and re-binding; the reference's aliasing semantics
+ * therefore live in host code, not here. */
+int zebra_tppr_bind_tables(zebra_tppr_t *h, void *const *dev_tables);
+
+/* Zero the dependency counters (device + host mirror).  Optional; call only when no work of
+ * this handle is in flight. */
+int zebra_tppr_reset_tickets(zebra_tppr_t *h, void *stream);
+
+/* ---- streaming top-k: replaces tppr_finder.streaming_topk / streaming_topk_no_fake /
+ *      single_streaming_topk / compute_val_tppr (utils/util.py:473-576, 581-679, 682-782,
+ *      787-873) -------------------------------------------------------------------------------
+ *
+ * One chronological span of n edges.  For every instance and every edge i, in order:
+ * (1) the CURRENT vectors of src, dst (and neg) are written to output rows i, i+n (, i+2n)
+ * exactly as extract_streaming_tppr does (utils/util.py:447-469), then (2) both endpoint vectors
+ * are updated from their OLD values (decay, merge, new key, top-k) and committed.
+ *
+ *   host_nodes     int32 [rows_per_edge*n]  = [src ; dst ; neg]      (rows_per_edge 3)
+ *                                           = [src ; dst]            (rows_per_edge 2 or 0)
+ *   host_ts        f64   [>= n]             only the first n are read (utils/util.py:499)
+ *   host_eidx      int64 [n]                must fit int32 (utils/util.py:450-451 narrows them)
+ *   rows_per_edge  3 = with negative rows, 2 = no fake, 0 = update only (no output rows)
+ *   inst           -1 = all instances, else only that instance is updated/extracted
+ *   dev_out        device buffer of zebra_tppr_out_bytes(h, n, rows_per_edge) bytes, or NULL to
+ *                  use an internal one.  Layout: for each instance j:
+ *                  int32 nodes[R*k] | int32 eidx[R*k] | f32 dt[R*k] | f32 w[R*k],  R = rows*n.
+ *                  Rows of instances excluded by `inst` are zero.
+ *   host_out       if non-NULL, the same bytes are copied back to it and the call returns after
+ *                  the copy completed (synchronous, like the reference).  If NULL the call only
+ *                  enqueues work on `stream`.
+ */
+size_t zebra_tppr_out_bytes(const zebra_tppr_t *h, int64_t n, int32_t rows_per_edge);
+int zebra_tppr_stream(zebra_tppr_t *h, const int32_t *host_nodes, const double *host_ts,
+                      const int64_t *host_eidx, int64_t n, int32_t rows_per_edge, int32_t inst,
+                      void *dev_out, void *host_out, void *stream);
+
+/* compute_val_tppr's inputs are int64 pandas columns (train.py:243); same semantics as
+ * zebra_tppr_stream(rows_per_edge = 0) over all instances, chunked and pipelined internally. */
+int zebra_tppr_update_only(zebra_tppr_t *h, const int64_t *host_src, const int64_t *host_dst,
+                           const double *host_ts, const int64_t *host_eidx, int64_t n_edges,
+                           void *stream);
+
+/* Debug / test access: copy the vectors of `n_ids` nodes of instance `inst` to host arrays
+ * (counts int32[n_ids], eidx int32[n_ids*k], node int32[n_ids*k], ts f64[n_ids*k],
+ * score f64[n_ids*k], norm f64[n_ids]).  Synchronous. */
+int zebra_tppr_read_state(zebra_tppr_t *h, int32_t inst, const int64_t *host_ids, int64_t n_ids,
+                          int32_t *counts, int32_t *eidx, int32_t *node, double *ts,
+                          double *score, double *norm, void *stream);
+
+/* Wait for the work enqueued on `stream` and report a device-side failure (dependency wait
+ * time-out) of any span since the previous check.  zebra_tppr_stream with host_out == NULL is
+ * asynchronous and does not check by itself. */
+int zebra_tppr_sync_check(zebra_tppr_t *h, void *stream);
+
+/* Counters of the last zebra_tppr_stream / update_only call: [0] work items, [1] prunes that took
+ * the exact tie path, [2] kernel launches so far on this handle, [3] spin time-outs (must be 0). */
+int zebra_tppr_counters(zebra_tppr_t *h, int64_t *out4);
+
+/* Device time of the last span kernel(s) in milliseconds (CUDA events on `stream`); -1 if none. */
+double zebra_tppr_last_kernel_ms(zebra_tppr_t *h);
+
+const char *zebra_last_error(void);
+const char *zebra_build_info(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ZEBRA_TPPR_H */

@@ -1,0 +1,49 @@
+"""ctypes binding of libzebra_tppr.so (include/zebra_tppr.h).  No CPU fallback: if the library is
+missing it is built; if it cannot be loaded, importing code gets the error."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+from . import build as _build
+
+_lib = None
+
+_VP, _I64, _I32, _D = C.c_void_p, C.c_int64, C.c_int32, C.c_double
+
+SIGNATURES = {
+    "zebra_tppr_create": (C.c_int, [C.POINTER(_VP), _I64, _I32, _I32, _VP, _VP, _I32]),
+    "zebra_tppr_destroy": (C.c_int, [_VP]),
+    "zebra_tppr_table_bytes": (C.c_size_t, [_VP]),
+    "zebra_tppr_record_bytes": (C.c_size_t, [_VP]),
+    "zebra_tppr_bind_tables": (C.c_int, [_VP, _VP]),
+    "zebra_tppr_reset_tickets": (C.c_int, [_VP, _VP]),
+    "zebra_tppr_out_bytes": (C.c_size_t, [_VP, _I64, _I32]),
+    "zebra_tppr_stream": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _I32, _I32, _VP, _VP, _VP]),
+    "zebra_tppr_update_only": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _I64, _VP]),
+    "zebra_tppr_read_state": (C.c_int, [_VP, _I32, _VP, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+    "zebra_tppr_sync_check": (C.c_int, [_VP, _VP]),
+    "zebra_tppr_counters": (C.c_int, [_VP, _VP]),
+    "zebra_tppr_last_kernel_ms": (_D, [_VP]),
+    "zebra_last_error": (C.c_char_p, []),
+    "zebra_build_info": (C.c_char_p, []),
+}
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        so = _build.SO
+        if not os.path.exists(so):
+            so = _build.build()
+        L = C.CDLL(so)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def check(rc: int):
+    if rc != 0:
+        raise RuntimeError("libzebra_tppr: " + lib().zebra_last_error().decode())

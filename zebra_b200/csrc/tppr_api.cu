@@ -1,0 +1,405 @@
+// tppr_api.cu — host side of libzebra_tppr.so: the C ABI declared in include/zebra_tppr.h.
+//
+// The host's only jobs are (a) turning a chronological span into per-access dependency
+// thresholds (one pass, two uint32 per node), (b) staging the span through pinned memory and
+// (c) launching the persistent span kernel.  All T-PPR arithmetic runs on the GPU; there is no
+// CPU fallback: without a CUDA device every entry point fails with an error.
+#include "tppr_device.cuh"
+#include "../../include/zebra_tppr.h"
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return 1;
+}
+
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t _e = (call);                                                                   \
+        if (_e != cudaSuccess) return fail("%s failed: %s (%s:%d)", #call, cudaGetErrorString(_e), __FILE__, __LINE__); \
+    } while (0)
+
+constexpr int64_t kChunk = 1 << 18;  // edges per launch of a long span
+
+struct Staging {
+    char *host = nullptr;   // pinned
+    char *dev = nullptr;
+    size_t cap = 0;         // edges
+    cudaEvent_t free_ev = nullptr;
+    bool pending = false;
+};
+
+}  // namespace
+
+struct zebra_tppr {
+    int64_t num_nodes = 0;
+    int32_t k = 0, n_tppr = 0, stride = 0, device = 0;
+    double alpha[zebra::kMaxInst], beta[zebra::kMaxInst];
+    char *tables[zebra::kMaxInst] = {};
+    uint32_t *done = nullptr;                 // [n_tppr][num_nodes]
+    std::vector<uint32_t> acc, lastw;         // host mirror: accesses issued / count at last write
+    uint32_t *ticket = nullptr;
+    uint32_t ticket_base = 0;
+    int32_t *status = nullptr;                // device [4]
+    int32_t *status_host = nullptr;           // pinned [4]
+    Staging stg[2];
+    int stg_next = 0;
+    char *out_dev = nullptr;
+    size_t out_cap = 0;
+    char *out_pinned = nullptr;
+    size_t out_pinned_cap = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timed = false;
+    int max_blocks = 0;
+    int64_t launches = 0, last_items = 0, last_ties = 0, timeouts = 0;
+};
+
+namespace {
+
+size_t record_bytes(int k) { return (static_cast<size_t>(24) * k + 16 + 127) / 128 * 128; }
+
+// bytes per edge in a staging slot: src,dst,neg,eidx,thr_s,thr_d,thr_n (4 B each) + ts (8 B)
+constexpr size_t kEdgeBytes = 7 * 4 + 8;
+
+int ensure_staging(zebra_tppr *h, Staging &s, size_t edges)
+{
+    if (s.cap >= edges) return 0;
+    if (s.pending) { CU(cudaEventSynchronize(s.free_ev)); s.pending = false; }
+    if (s.host) CU(cudaFreeHost(s.host));
+    if (s.dev) CU(cudaFree(s.dev));
+    size_t cap = std::max<size_t>(edges, 1024);
+    CU(cudaMallocHost(&s.host, cap * kEdgeBytes));
+    CU(cudaMalloc(&s.dev, cap * kEdgeBytes));
+    if (!s.free_ev) CU(cudaEventCreateWithFlags(&s.free_ev, cudaEventDisableTiming));
+    s.cap = cap;
+    return 0;
+}
+
+// Fills one staging slot for edges [lo, lo+m) of the span and advances the host mirrors.
+// Access thresholds: a writer waits for every earlier access of the node, a reader for the last
+// earlier writer.  A negative equal to src or dst is served from the writer's registers.
+template <typename NodeT>
+int prepare_chunk(zebra_tppr *h, Staging &s, const NodeT *src, const NodeT *dst, const NodeT *neg, const double *ts,
+                  const int64_t *eidx, int64_t m)
+{
+    const size_t cap = (static_cast<size_t>(m) + 7) & ~static_cast<size_t>(7);   // SoA stride of this launch
+    int32_t *o_src = reinterpret_cast<int32_t *>(s.host);
+    int32_t *o_dst = o_src + cap, *o_neg = o_dst + cap, *o_e = o_neg + cap;
+    uint32_t *t_s = reinterpret_cast<uint32_t *>(o_e + cap), *t_d = t_s + cap, *t_n = t_d + cap;
+    double *o_ts = reinterpret_cast<double *>(t_n + cap);
+    uint32_t *acc = h->acc.data(), *lastw = h->lastw.data();
+    const int64_t N = h->num_nodes;
+    for (int64_t i = 0; i < m; ++i) {   // validate before touching the mirrors
+        const int64_t a = src[i], b = dst[i], g = neg ? static_cast<int64_t>(neg[i]) : a;
+        const int64_t e = eidx[i];
+        if (a < 0 || a >= N || b < 0 || b >= N || g < 0 || g >= N)
+            return fail("node id out of range at edge %lld (num_nodes=%lld)", (long long)i, (long long)N);
+        if (e < 0 || e > 0x7fffffffLL) return fail("edge id %lld does not fit int32", (long long)e);
+    }
+    for (int64_t i = 0; i < m; ++i) {
+        const int64_t a = src[i], b = dst[i], g = neg ? static_cast<int64_t>(neg[i]) : a;
+        const int64_t e = eidx[i];
+        o_src[i] = static_cast<int32_t>(a); o_dst[i] = static_cast<int32_t>(b); o_neg[i] = static_cast<int32_t>(g);
+        o_e[i] = static_cast<int32_t>(e);
+        o_ts[i] = ts[i];
+        uint32_t thn = 0;
+        if (neg && g != a && g != b) { thn = lastw[g]; acc[g]++; }
+        t_n[i] = thn;
+        t_s[i] = acc[a]; lastw[a] = ++acc[a];
+        if (b != a) { t_d[i] = acc[b]; lastw[b] = ++acc[b]; }
+        else t_d[i] = 0;
+    }
+    return 0;
+}
+
+int launch_chunk(zebra_tppr *h, Staging &s, int64_t m, int64_t n_total, int64_t i_offset, int32_t rows_per_edge,
+                 int32_t inst_mask, char *out, cudaStream_t st)
+{
+    const size_t cap = (static_cast<size_t>(m) + 7) & ~static_cast<size_t>(7);
+    CU(cudaMemcpyAsync(s.dev, s.host, cap * kEdgeBytes, cudaMemcpyHostToDevice, st));
+    if (i_offset == 0) CU(cudaEventRecord(h->ev0, st));
+    zebra::SpanParams p;
+    memset(&p, 0, sizeof p);
+    p.n_chunk = m; p.n_total = n_total; p.i_offset = i_offset; p.rows_total = static_cast<int64_t>(rows_per_edge) * n_total;
+    p.k = h->k; p.n_tppr = h->n_tppr; p.rows_per_edge = rows_per_edge; p.inst_mask = inst_mask; p.stride = h->stride;
+    p.ticket_base = h->ticket_base;
+    p.src = reinterpret_cast<const int32_t *>(s.dev);
+    p.dst = p.src + cap; p.neg = p.dst + cap; p.eidx = p.neg + cap;
+    p.thr_s = reinterpret_cast<const uint32_t *>(p.eidx + cap); p.thr_d = p.thr_s + cap; p.thr_n = p.thr_d + cap;
+    p.ts = reinterpret_cast<const double *>(p.thr_n + cap);
+    for (int j = 0; j < h->n_tppr; ++j) {
+        p.tables[j] = h->tables[j];
+        p.done[j] = h->done + static_cast<size_t>(j) * h->num_nodes;
+        p.alpha[j] = h->alpha[j]; p.beta[j] = h->beta[j];
+    }
+    p.out = out; p.ticket = h->ticket; p.status = h->status;
+    const int64_t items = m * h->n_tppr;
+    int blocks = static_cast<int>(std::min<int64_t>((items + zebra::kWarpsPerBlock - 1) / zebra::kWarpsPerBlock, h->max_blocks));
+    if (blocks < 1) blocks = 1;
+    zebra::tppr_span_kernel<<<blocks, zebra::kWarpsPerBlock * 32, 0, st>>>(p);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(s.free_ev, st));
+    s.pending = true;
+    // every warp of the grid draws exactly one ticket past the end
+    h->ticket_base += static_cast<uint32_t>(items) + static_cast<uint32_t>(blocks) * zebra::kWarpsPerBlock;
+    h->launches++;
+    h->last_items += items;
+    return 0;
+}
+
+int check_status(zebra_tppr *h, cudaStream_t st)
+{
+    CU(cudaMemcpyAsync(h->status_host, h->status, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    h->last_ties = h->status_host[1];
+    if (h->status_host[0] != 0) {
+        h->timeouts++;
+        return fail("T-PPR span kernel: dependency wait timed out (status=%d)", h->status_host[0]);
+    }
+    return 0;
+}
+
+template <typename NodeT>
+int run_span(zebra_tppr *h, const NodeT *src, const NodeT *dst, const NodeT *neg, const double *ts, const int64_t *eidx,
+             int64_t n, int32_t rows_per_edge, int32_t inst_mask, char *out, cudaStream_t st)
+{
+    for (int j = 0; j < h->n_tppr; ++j)
+        if (!h->tables[j]) return fail("zebra_tppr_bind_tables has not been called");
+    CU(cudaSetDevice(h->device));
+    CU(cudaMemsetAsync(h->status + 1, 0, 3 * sizeof(int32_t), st));   // [0] (time-out) is sticky
+    h->last_items = 0;
+    for (int64_t lo = 0; lo < n; lo += kChunk) {
+        const int64_t m = std::min(kChunk, n - lo);
+        Staging &s = h->stg[h->stg_next];
+        h->stg_next ^= 1;
+        if (ensure_staging(h, s, static_cast<size_t>(m) + 8)) return 1;
+        if (s.pending) { CU(cudaEventSynchronize(s.free_ev)); s.pending = false; }
+        if (prepare_chunk(h, s, src + lo, dst + lo, neg ? neg + lo : nullptr, ts + lo, eidx + lo, m)) return 1;
+        if (launch_chunk(h, s, m, n, lo, rows_per_edge, inst_mask, out, st)) return 1;
+    }
+    CU(cudaEventRecord(h->ev1, st));
+    h->timed = true;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *zebra_last_error(void) { return g_err.c_str(); }
+
+const char *zebra_build_info(void) { return "libzebra_tppr sm_100a fp64 no-fma " __DATE__ " " __TIME__; }
+
+int zebra_tppr_create(zebra_tppr_t **out, int64_t num_nodes, int32_t k, int32_t n_tppr, const double *alpha_list,
+                      const double *beta_list, int32_t device)
+{
+    if (!out) return fail("null out pointer");
+    *out = nullptr;
+    if (num_nodes <= 0) return fail("num_nodes must be positive");
+    if (k < 1 || k > 31) return fail("k=%d unsupported: this build keeps one candidate pair per warp lane (1 <= k <= 31)", k);
+    if (n_tppr < 1 || n_tppr > zebra::kMaxInst) return fail("n_tppr=%d unsupported (1..%d)", n_tppr, zebra::kMaxInst);
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail("no CUDA device: libzebra_tppr has no CPU path (%s)", e == cudaSuccess ? "0 devices" : cudaGetErrorString(e));
+    if (device < 0 || device >= ndev) return fail("device %d out of range", device);
+    CU(cudaSetDevice(device));
+    zebra_tppr *h = new zebra_tppr();
+    h->num_nodes = num_nodes; h->k = k; h->n_tppr = n_tppr; h->device = device;
+    h->stride = static_cast<int32_t>(record_bytes(k));
+    for (int j = 0; j < n_tppr; ++j) { h->alpha[j] = alpha_list[j]; h->beta[j] = beta_list[j]; }
+    h->acc.assign(static_cast<size_t>(num_nodes), 0u);
+    h->lastw.assign(static_cast<size_t>(num_nodes), 0u);
+    CU(cudaMalloc(&h->done, sizeof(uint32_t) * num_nodes * n_tppr));
+    CU(cudaMemset(h->done, 0, sizeof(uint32_t) * num_nodes * n_tppr));
+    CU(cudaMalloc(&h->ticket, sizeof(uint32_t)));
+    CU(cudaMemset(h->ticket, 0, sizeof(uint32_t)));
+    CU(cudaMalloc(&h->status, 4 * sizeof(int32_t)));
+    CU(cudaMemset(h->status, 0, 4 * sizeof(int32_t)));
+    CU(cudaMallocHost(&h->status_host, 4 * sizeof(int32_t)));
+    CU(cudaEventCreate(&h->ev0));
+    CU(cudaEventCreate(&h->ev1));
+    int per_sm = 0, sms = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, zebra::tppr_span_kernel, zebra::kWarpsPerBlock * 32, 0));
+    CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    h->max_blocks = std::max(1, per_sm * sms);
+    *out = h;
+    return 0;
+}
+
+int zebra_tppr_destroy(zebra_tppr_t *h)
+{
+    if (!h) return 0;
+    cudaSetDevice(h->device);
+    cudaDeviceSynchronize();
+    for (auto &s : h->stg) {
+        if (s.host) cudaFreeHost(s.host);
+        if (s.dev) cudaFree(s.dev);
+        if (s.free_ev) cudaEventDestroy(s.free_ev);
+    }
+    if (h->done) cudaFree(h->done);
+    if (h->ticket) cudaFree(h->ticket);
+    if (h->status) cudaFree(h->status);
+    if (h->status_host) cudaFreeHost(h->status_host);
+    if (h->out_dev) cudaFree(h->out_dev);
+    if (h->out_pinned) cudaFreeHost(h->out_pinned);
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    delete h;
+    return 0;
+}
+
+size_t zebra_tppr_record_bytes(const zebra_tppr_t *h) { return h ? static_cast<size_t>(h->stride) : 0; }
+size_t zebra_tppr_table_bytes(const zebra_tppr_t *h) { return h ? static_cast<size_t>(h->stride) * h->num_nodes : 0; }
+
+int zebra_tppr_bind_tables(zebra_tppr_t *h, void *const *dev_tables)
+{
+    if (!h || !dev_tables) return fail("null argument");
+    for (int j = 0; j < h->n_tppr; ++j) {
+        if (!dev_tables[j]) return fail("table %d is null", j);
+        if (reinterpret_cast<uintptr_t>(dev_tables[j]) % 16) return fail("table %d is not 16-byte aligned", j);
+        h->tables[j] = static_cast<char *>(dev_tables[j]);
+    }
+    return 0;
+}
+
+int zebra_tppr_reset_tickets(zebra_tppr_t *h, void *stream)
+{
+    if (!h) return fail("null handle");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(st));
+    CU(cudaMemsetAsync(h->done, 0, sizeof(uint32_t) * h->num_nodes * h->n_tppr, st));
+    std::fill(h->acc.begin(), h->acc.end(), 0u);
+    std::fill(h->lastw.begin(), h->lastw.end(), 0u);
+    return 0;
+}
+
+size_t zebra_tppr_out_bytes(const zebra_tppr_t *h, int64_t n, int32_t rows_per_edge)
+{
+    if (!h) return 0;
+    return static_cast<size_t>(h->n_tppr) * 16 * static_cast<size_t>(rows_per_edge) * n * h->k;
+}
+
+int zebra_tppr_stream(zebra_tppr_t *h, const int32_t *host_nodes, const double *host_ts, const int64_t *host_eidx,
+                      int64_t n, int32_t rows_per_edge, int32_t inst, void *dev_out, void *host_out, void *stream)
+{
+    if (!h) return fail("null handle");
+    if (n < 0) return fail("negative edge count");
+    if (rows_per_edge != 0 && rows_per_edge != 2 && rows_per_edge != 3) return fail("rows_per_edge must be 0, 2 or 3");
+    if (inst < -1 || inst >= h->n_tppr) return fail("instance %d out of range", inst);
+    if (n == 0) return 0;
+    if (!host_nodes || !host_ts || !host_eidx) return fail("null input");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    CU(cudaSetDevice(h->device));
+    const size_t ob = zebra_tppr_out_bytes(h, n, rows_per_edge);
+    char *out = static_cast<char *>(dev_out);
+    if (rows_per_edge && !out) {
+        if (h->out_cap < ob) {
+            CU(cudaStreamSynchronize(st));
+            if (h->out_dev) CU(cudaFree(h->out_dev));
+            CU(cudaMalloc(&h->out_dev, ob));
+            h->out_cap = ob;
+        }
+        out = h->out_dev;
+    }
+    const int32_t mask = inst < 0 ? ((1 << h->n_tppr) - 1) : (1 << inst);
+    if (rows_per_edge && inst >= 0) CU(cudaMemsetAsync(out, 0, ob, st));
+    const int32_t *neg = rows_per_edge == 3 ? host_nodes + 2 * n : nullptr;
+    if (run_span<int32_t>(h, host_nodes, host_nodes + n, neg, host_ts, host_eidx, n, rows_per_edge, mask, out, st)) return 1;
+    if (host_out && rows_per_edge) {
+        CU(cudaMemcpyAsync(host_out, out, ob, cudaMemcpyDeviceToHost, st));
+        return check_status(h, st);
+    }
+    if (host_out || !rows_per_edge) return check_status(h, st);
+    return 0;
+}
+
+int zebra_tppr_update_only(zebra_tppr_t *h, const int64_t *host_src, const int64_t *host_dst, const double *host_ts,
+                           const int64_t *host_eidx, int64_t n_edges, void *stream)
+{
+    if (!h) return fail("null handle");
+    if (n_edges < 0) return fail("negative edge count");
+    if (n_edges == 0) return 0;
+    if (!host_src || !host_dst || !host_ts || !host_eidx) return fail("null input");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (run_span<int64_t>(h, host_src, host_dst, nullptr, host_ts, host_eidx, n_edges, 0, (1 << h->n_tppr) - 1, nullptr, st))
+        return 1;
+    return check_status(h, st);
+}
+
+int zebra_tppr_read_state(zebra_tppr_t *h, int32_t inst, const int64_t *host_ids, int64_t n_ids, int32_t *counts,
+                          int32_t *eidx, int32_t *node, double *ts, double *score, double *norm, void *stream)
+{
+    if (!h) return fail("null handle");
+    if (inst < 0 || inst >= h->n_tppr || !h->tables[inst]) return fail("bad instance");
+    if (n_ids <= 0) return 0;
+    for (int64_t a = 0; a < n_ids; ++a)
+        if (host_ids[a] < 0 || host_ids[a] >= h->num_nodes) return fail("node id out of range");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    CU(cudaSetDevice(h->device));
+    const int k = h->k;
+    const size_t nk = static_cast<size_t>(n_ids) * k;
+    const size_t bytes = n_ids * 8 + n_ids * 4 + nk * 4 * 2 + nk * 8 * 2 + n_ids * 8;
+    char *d = nullptr;
+    CU(cudaMalloc(&d, bytes));
+    int64_t *d_ids = reinterpret_cast<int64_t *>(d);
+    double *d_ts = reinterpret_cast<double *>(d_ids + n_ids), *d_sc = d_ts + nk, *d_norm = d_sc + nk;
+    int32_t *d_cnt = reinterpret_cast<int32_t *>(d_norm + n_ids), *d_e = d_cnt + n_ids, *d_n = d_e + nk;
+    cudaError_t e = cudaMemcpyAsync(d_ids, host_ids, n_ids * 8, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) {
+        zebra::tppr_read_state_kernel<<<static_cast<unsigned>(n_ids), 32, 0, st>>>(h->tables[inst], h->stride, k, d_ids, n_ids,
+                                                                                  d_cnt, d_e, d_n, d_ts, d_sc, d_norm);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(counts, d_cnt, n_ids * 4, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(eidx, d_e, nk * 4, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(node, d_n, nk * 4, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(ts, d_ts, nk * 8, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(score, d_sc, nk * 8, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(norm, d_norm, n_ids * 8, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    cudaFree(d);
+    if (e != cudaSuccess) return fail("read_state failed: %s", cudaGetErrorString(e));
+    return 0;
+}
+
+int zebra_tppr_sync_check(zebra_tppr_t *h, void *stream)
+{
+    if (!h) return fail("null handle");
+    return check_status(h, static_cast<cudaStream_t>(stream));
+}
+
+int zebra_tppr_counters(zebra_tppr_t *h, int64_t *out4)
+{
+    if (!h || !out4) return fail("null argument");
+    out4[0] = h->last_items; out4[1] = h->last_ties; out4[2] = h->launches; out4[3] = h->timeouts;
+    return 0;
+}
+
+double zebra_tppr_last_kernel_ms(zebra_tppr_t *h)
+{
+    if (!h || !h->timed) return -1.0;
+    if (cudaEventSynchronize(h->ev1) != cudaSuccess) return -1.0;
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, h->ev0, h->ev1) != cudaSuccess) return -1.0;
+    return ms;
+}
+
+}  // extern "C"

@@ -1,0 +1,186 @@
+"""Drop-in replacement for the reference's numba `tppr_finder` (LuckyLYM/Zebra utils/util.py:391-873).
+
+Same constructor, attributes, method names, argument meaning and return types; the per-node score
+dictionaries are device-resident fixed-capacity top-k tables and every update runs in the
+sm_100a span kernel behind the C ABI (include/zebra_tppr.h).  There is no CPU path: constructing
+a finder without a CUDA device raises.
+
+Snapshot semantics.  In the reference `backup_tppr`, `restore_val_tppr` and the cache written by
+`compute_val_tppr` are shallow numba typed-List copies, i.e. they ALIAS the live containers
+(utils/util.py:436-444, 872-873).  The default here reproduces exactly that by
+handing out references to the same device tables, because parity is judged against what the
+reference does.  `ZEBRA_TPPR_SNAPSHOT=strict` (or strict_snapshots=True) switches the three calls
+to real device-to-device clones, the semantics the reference's author presumably intended.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+import torch
+
+from ._lib import check, lib
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, torch.Tensor):
+        return C.c_void_p(a.data_ptr())
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class tppr_finder:  # noqa: N801  (name kept from the reference)
+    def __init__(self, num_nodes, k, n_tppr, alpha_list, beta_list, device=None, strict_snapshots=None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("zebra_b200.tppr_finder needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+        self.num_nodes = int(num_nodes)
+        self.k = int(k)
+        self.n_tppr = int(n_tppr)
+        self.alpha_list = [float(a) for a in alpha_list]
+        self.beta_list = [float(b) for b in beta_list]
+        if len(self.alpha_list) != self.n_tppr or len(self.beta_list) != self.n_tppr:
+            raise ValueError("alpha_list and beta_list must have n_tppr entries")
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        if strict_snapshots is None:
+            strict_snapshots = os.environ.get("ZEBRA_TPPR_SNAPSHOT", "").lower() == "strict"
+        self.strict_snapshots = bool(strict_snapshots)
+        self._L = lib()
+        h = C.c_void_p()
+        a = (C.c_double * self.n_tppr)(*self.alpha_list)
+        b = (C.c_double * self.n_tppr)(*self.beta_list)
+        check(self._L.zebra_tppr_create(C.byref(h), self.num_nodes, self.k, self.n_tppr, a, b, self.device.index or 0))
+        self._h = h
+        self._table_bytes = self._L.zebra_tppr_table_bytes(h)
+        self._record_bytes = self._L.zebra_tppr_record_bytes(h)
+        self._host_out = None
+        self._tables = None
+        self.reset_val_tppr()
+        self.reset_tppr()
+
+    # ---- state management (utils/util.py:402-444) ----
+    def _new_tables(self):
+        return [torch.zeros(self._table_bytes, dtype=torch.uint8, device=self.device) for _ in range(self.n_tppr)]
+
+    def _bind(self):
+        arr = (C.c_void_p * self.n_tppr)(*[t.data_ptr() for t in self._tables])
+        check(self._L.zebra_tppr_bind_tables(self._h, arr))
+
+    def _snapshot(self, tables):
+        return [t.clone() for t in tables] if self.strict_snapshots else list(tables)
+
+    def reset_tppr(self):
+        self._tables = self._new_tables()
+        self._bind()
+
+    def reset_val_tppr(self):
+        self._val_tables = self._new_tables()
+
+    def backup_tppr(self):
+        return self._snapshot(self._tables)
+
+    def restore_tppr(self, backup):
+        self._tables = list(backup)
+        self._bind()
+
+    def restore_val_tppr(self):
+        self._tables = self._snapshot(self._val_tables)
+        self._bind()
+
+    # ---- streaming (utils/util.py:473-576, 581-679, 682-782, 787-873) ----
+    def _stream_ptr(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _run(self, source_nodes, timestamps, edge_idxs, rows_per_edge, inst, to_host):
+        nodes = np.ascontiguousarray(source_nodes, dtype=np.int32)
+        ts = np.ascontiguousarray(timestamps, dtype=np.float64)
+        eidx = np.ascontiguousarray(edge_idxs, dtype=np.int64)
+        n = len(eidx)
+        rows = rows_per_edge * n
+        if len(nodes) != max(rows_per_edge, 2) * n or len(ts) < n:
+            raise ValueError("source_nodes/timestamps do not match edge_idxs")
+        nbytes = self._L.zebra_tppr_out_bytes(self._h, n, rows_per_edge)
+        dev_out = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=self.device)
+        host = None
+        if to_host and nbytes:
+            if self._host_out is None or self._host_out.numel() < nbytes:
+                self._host_out = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+            host = self._host_out
+        with torch.cuda.device(self.device):
+            check(self._L.zebra_tppr_stream(self._h, _ptr(nodes), _ptr(ts), _ptr(eidx), n, rows_per_edge, inst,
+                                            _ptr(dev_out) if nbytes else None, _ptr(host), self._stream_ptr()))
+        plane = rows * self.k
+        if to_host:
+            buf = host.numpy()[:nbytes] if nbytes else np.zeros(0, np.uint8)
+            outs = ([], [], [], [])
+            for j in range(self.n_tppr):
+                base = j * plane * 16
+                for q, dt in enumerate((np.int32, np.int32, np.float32, np.float32)):
+                    a = buf[base + q * plane * 4: base + (q + 1) * plane * 4].view(dt).reshape(rows, self.k).copy()
+                    outs[q].append(a)
+            return outs
+        outs = ([], [], [], [])
+        for j in range(self.n_tppr):
+            base = j * plane * 16
+            for q, dt in enumerate((torch.int32, torch.int32, torch.float32, torch.float32)):
+                outs[q].append(dev_out[base + q * plane * 4: base + (q + 1) * plane * 4].view(dt).view(rows, self.k))
+        return outs
+
+    def streaming_topk(self, source_nodes, timestamps, edge_idxs):
+        """[src;dst;neg] int32[3n], f64[3n], int64[n] -> 4 lists of n_tppr arrays [3n,k] (i32,i32,f32,f32)."""
+        return self._run(source_nodes, timestamps, edge_idxs, 3, -1, True)
+
+    def streaming_topk_no_fake(self, source_nodes, timestamps, edge_idxs):
+        return self._run(source_nodes, timestamps, edge_idxs, 2, -1, True)
+
+    def single_streaming_topk(self, source_nodes, timestamps, edge_idxs, tppr_id):
+        o = self._run(source_nodes, timestamps, edge_idxs, 3, int(tppr_id), True)
+        return tuple(x[int(tppr_id)] for x in o)
+
+    def streaming_topk_device(self, source_nodes, timestamps, edge_idxs, rows_per_edge=3):
+        """Level-1 fast path: same result as streaming_topk, left on the GPU as torch tensors
+        (asynchronous on the current stream; nothing is copied back)."""
+        return self._run(source_nodes, timestamps, edge_idxs, rows_per_edge, -1, False)
+
+    def compute_val_tppr(self, sources, targets, timestamps, edge_idxs):
+        src = np.ascontiguousarray(sources, dtype=np.int64)
+        dst = np.ascontiguousarray(targets, dtype=np.int64)
+        ts = np.ascontiguousarray(timestamps, dtype=np.float64)
+        eidx = np.ascontiguousarray(edge_idxs, dtype=np.int64)
+        with torch.cuda.device(self.device):
+            check(self._L.zebra_tppr_update_only(self._h, _ptr(src), _ptr(dst), _ptr(ts), _ptr(eidx), len(src),
+                                                 self._stream_ptr()))
+        self._val_tables = self._snapshot(self._tables)
+
+    # ---- introspection (tests) ----
+    def state(self, inst, nodes):
+        """Vectors of `nodes` in instance `inst`: list of (eidx, node, ts, score, norm) in slot order."""
+        ids = np.ascontiguousarray(nodes, dtype=np.int64)
+        m, k = len(ids), self.k
+        cnt = np.zeros(m, np.int32); e = np.zeros((m, k), np.int32); nd = np.zeros((m, k), np.int32)
+        t = np.zeros((m, k), np.float64); s = np.zeros((m, k), np.float64); nm = np.zeros(m, np.float64)
+        with torch.cuda.device(self.device):
+            check(self._L.zebra_tppr_read_state(self._h, int(inst), _ptr(ids), m, _ptr(cnt), _ptr(e), _ptr(nd), _ptr(t),
+                                                _ptr(s), _ptr(nm), self._stream_ptr()))
+        return [(e[a, :cnt[a]].astype(np.int64), nd[a, :cnt[a]].astype(np.int64), t[a, :cnt[a]], s[a, :cnt[a]], float(nm[a]))
+                for a in range(m)]
+
+    def sync_check(self):
+        check(self._L.zebra_tppr_sync_check(self._h, self._stream_ptr()))
+
+    def counters(self):
+        o = np.zeros(4, np.int64)
+        check(self._L.zebra_tppr_counters(self._h, _ptr(o)))
+        return {"items": int(o[0]), "tie_prunes": int(o[1]), "launches": int(o[2]), "timeouts": int(o[3])}
+
+    def last_kernel_ms(self):
+        return float(self._L.zebra_tppr_last_kernel_ms(self._h))
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                self._L.zebra_tppr_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
