@@ -1,0 +1,50 @@
+"""Quick timing probe (not the bench): per-batch streaming and bulk update-only throughput."""
+import sys, time, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np, torch
+from zebra_b200 import synth
+from zebra_b200.finder import tppr_finder
+
+def per_batch(name, n_edges, bs=200):
+    st = synth.make_stream(name, n_edges=n_edges)
+    neg = synth.make_negatives(st, bs)
+    f = tppr_finder(st.shape.table_nodes, 20, 2, [0.1, 0.1], [0.5, 0.95])
+    batches = []
+    for lo in range(0, n_edges, bs):
+        hi = min(lo + bs, n_edges)
+        batches.append((np.concatenate([st.src[lo:hi], st.dst[lo:hi], neg[lo:hi]]).astype(np.int32),
+                        np.concatenate([st.ts[lo:hi]] * 3), st.eidx[lo:hi]))
+    for mode in ("host", "device"):
+        f.reset_tppr()
+        for b in batches[:20]:
+            f.streaming_topk(*b)
+        f.reset_tppr()
+        torch.cuda.synchronize(); t = time.perf_counter(); kms = 0.0
+        for b in batches:
+            if mode == "host":
+                f.streaming_topk(*b); kms += f.last_kernel_ms()
+            else:
+                f.streaming_topk_device(*b)
+        f.sync_check()
+        dt = time.perf_counter() - t
+        print(f"{name} bs={bs} {mode}: {n_edges/dt/1e6:.3f} M edges/s  ({dt/len(batches)*1e6:.1f} us/batch, kernel {kms/len(batches)*1e3:.1f} us/batch) ties={f.counters()}", flush=True)
+
+def bulk(name, n_edges=None):
+    st = synth.make_stream(name, n_edges=n_edges)
+    E = st.n_edges
+    f = tppr_finder(st.shape.table_nodes, 20, 2, [0.1, 0.1], [0.5, 0.95])
+    src, dst = st.src.astype(np.int64), st.dst.astype(np.int64)
+    f.compute_val_tppr(src[:100000], dst[:100000], st.ts[:100000], st.eidx[:100000])
+    for _ in range(2):
+        f.reset_tppr()
+        torch.cuda.synchronize(); t = time.perf_counter()
+        f.compute_val_tppr(src, dst, st.ts, st.eidx)
+        dt = time.perf_counter() - t
+        print(f"{name} bulk update-only E={E}: {E/dt/1e6:.2f} M edges/s wall, kernel-span {f.last_kernel_ms():.1f} ms -> {E/f.last_kernel_ms()/1e3:.2f} M edges/s, GB/s alg={E*2*1976/f.last_kernel_ms()/1e6:.1f} {f.counters()}", flush=True)
+
+if __name__ == "__main__":
+    per_batch("wikipedia", 157474)
+    per_batch("reddit", 200000)
+    per_batch("wikitalk", 400000)
+    bulk("reddit")
+    bulk("wikitalk")
