@@ -1,0 +1,295 @@
+"""bench.py — T-PPR maintenance throughput on B200 (see DESIGN.md "Measurement").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Workload (config.workload): BASELINE.json configs[4], the stream the metric's target is quoted on —
+Wiki-Talk-shaped synthetic unipartite stream (1,140,149 nodes, 7,833,140 edges), streaming T-PPR
+with negatives, topk=20, two (alpha,beta) pairs, batches of 200 edges.  One step = reset the tables
+and stream the whole span once.
+
+  value   edges/s with the span resident in HBM (a "plan": edge records + dependency tickets uploaded
+          once), outputs written to HBM, timed with CUDA events on the launching stream.
+  e2e     edges/s through the reference-facing call tppr_finder.streaming_topk (numpy in, numpy out):
+          every batch is prepared on the host, copied host->device, computed, and its 4*n_tppr result
+          arrays copied device->host inside the timed region.
+  roofline / cpu_baseline: see DESIGN.md.  The CPU leg executes oracle/ (the C port of the reference's
+          single-threaded numba path) as a reported baseline only.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+K, BS = 20, 200
+ALPHAS, BETAS = [0.1, 0.1], [0.5, 0.95]
+WORKLOAD = "wikitalk"
+METRIC, UNIT = "tppr_streaming_edges_per_sec", "edges/s"
+
+
+def bytes_per_edge(k=K, n_tppr=len(ALPHAS)):
+    """Algorithmic bytes of one streamed edge: per instance read 3 vectors, write 2,
+    48k output bytes, 28-byte edge record.  V(k) = 24k + 8."""
+    return n_tppr * (5 * (24 * k + 8) + 48 * k + 28)
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def load_workload(n_edges=None, seed=None):
+    from zebra_b200 import synth
+    st = synth.make_stream(WORKLOAD, n_edges=n_edges, seed=seed)
+    neg = synth.make_negatives(st, BS)
+    return st, neg
+
+
+def cpu_port_throughput(st, neg, sample_edges, threads):
+    """The oracle (C port of the reference's numba path) on the first `sample_edges` edges of the
+    workload, bs=200 batches with negatives.  threads > 1 runs the independent (alpha,beta) instances
+    concurrently (ctypes releases the GIL); the reference itself is single-threaded."""
+    import oracle
+    n = min(sample_edges, st.n_edges)
+    N = st.shape.table_nodes
+    finders = ([oracle.OracleFinder(N, K, 1, [a], [b]) for a, b in zip(ALPHAS, BETAS)] if threads > 1
+               else [oracle.OracleFinder(N, K, len(ALPHAS), ALPHAS, BETAS)])
+    batches = []
+    for lo in range(0, n, BS):
+        hi = min(n, lo + BS)
+        batches.append((np.concatenate([st.src[lo:hi], st.dst[lo:hi], neg[lo:hi]]).astype(np.int32),
+                        np.concatenate([st.ts[lo:hi]] * 3), st.eidx[lo:hi]))
+
+    def work(f):
+        for b in batches:
+            f.streaming_topk(*b)
+
+    t = time.perf_counter()
+    if len(finders) == 1:
+        work(finders[0])
+    else:
+        ths = [threading.Thread(target=work, args=(f,)) for f in finders]
+        [x.start() for x in ths]
+        [x.join() for x in ths]
+    dt = time.perf_counter() - t
+    return n / dt, n, dt
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU implementation of the path.  The reference is
+    Python + numba and cannot travel to the GPU box, so this times oracle/ (its C port, validated
+    bit-for-bit against recordings of the reference) on the box's host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = len(ALPHAS)          # the only parallelism the algorithm admits: independent instances
+    sample = args.ref_sample_edges
+    st, neg = load_workload(n_edges=min(sample, 7_833_140))
+    vals = []
+    for _ in range(max(1, min(args.warmup, 1))):
+        cpu_port_throughput(st, neg, min(sample, 100_000), threads)
+    t_all = 0.0
+    for _ in range(args.steps):
+        v, n, dt = cpu_port_throughput(st, neg, sample, threads)
+        vals.append(v); t_all += dt
+    value = float(np.mean(vals))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * t_all / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"{WORKLOAD}-shaped synthetic stream, streaming T-PPR topk={K}, alpha {ALPHAS}, beta {BETAS}, bs={BS}",
+                   "sample": f"first {sample} edges per step"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": f"first {sample} edges of the workload, bs={BS}, with negatives; one thread per (alpha,beta) instance"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from zebra_b200.finder import tppr_finder
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    # every rank streams its own replica of the workload (different seed): weak scaling, no exchange
+    st, neg = load_workload(n_edges=args.edges, seed=None if rank == 0 else 1005 + 100 * rank)
+    E, N = st.n_edges, st.shape.table_nodes
+    f = tppr_finder(N, K, len(ALPHAS), ALPHAS, BETAS, device=dev)
+    plan = f.make_plan(st.src, st.dst, neg, st.ts, st.eidx, BS)
+    window = args.batches_per_launch
+    out = plan.alloc_out(window)
+    n_launch = (plan.n_batches + window - 1) // window
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        f.reset_tppr()
+        plan.run(0, plan.n_batches, window, out=out, out_slots=window)
+
+    for _ in range(args.warmup):
+        step()
+    f.sync_check()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    l0 = f.counters()["launches"]
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ev[0].record()
+    for _ in range(args.steps):
+        step()
+    ev[1].record()
+    barrier()
+    f.sync_check()
+    ms = ev[0].elapsed_time(ev[1])
+    launches = f.counters()["launches"] - l0
+    tie_prunes = f.counters()["tie_prunes"]
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- e2e: the reference-facing call, host buffers in and out, per batch ----
+    nb_e2e = min(args.e2e_batches, plan.n_batches)
+    batches = []
+    for b in range(nb_e2e):
+        lo, hi = b * BS, min(E, (b + 1) * BS)
+        batches.append((np.concatenate([st.src[lo:hi], st.dst[lo:hi], neg[lo:hi]]).astype(np.int32),
+                        np.concatenate([st.ts[lo:hi]] * 3), st.eidx[lo:hi]))
+    f.reset_tppr()
+    for b in batches[:50]:
+        f.streaming_topk(*b)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        f.reset_tppr()
+        for b in batches:
+            f.streaming_topk(*b)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    e2e_edges = sum(len(b[2]) for b in batches)
+    h2d = sum(((len(b[2]) + 7) // 8 * 8) * 36 for b in batches)
+    d2h = sum(len(ALPHAS) * 16 * 3 * len(b[2]) * K for b in batches)
+
+    t = torch.tensor([ms, e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, e2e_s = float(t[0]), float(t[1])
+    if rank == 0:
+        peak, peak_src = peaks()
+        value = world * E * args.steps / (ms * 1e-3)
+        per_launch_ms = ms / max(launches, 1)
+        alg_per_launch = E * bytes_per_edge() / n_launch
+        achieved = alg_per_launch / (per_launch_ms * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"{WORKLOAD}-shaped synthetic stream ({st.shape.n_nodes} nodes, {E} edges/GPU), streaming T-PPR "
+                                   f"topk={K}, alpha {ALPHAS}, beta {BETAS}, bs={BS}, negatives included",
+                       "step": "reset tables + stream the whole span once",
+                       "batches_per_launch": window, "parallelism": f"replicas x{world}" if world > 1 else "single GPU",
+                       "l2": f"table {2 * N * 512 / 1e6:.0f} MB + outputs exceed the 126 MB L2 (inputs larger than L2)",
+                       "tie_path_prunes_last_step": tie_prunes},
+            "e2e": {"value": world * e2e_edges * args.steps / e2e_s, "unit": UNIT,
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "step": f"first {nb_e2e} batches through tppr_finder.streaming_topk (numpy in/out)"},
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": args.traffic, "peak_source": peak_src, "kernel": "tppr_span_kernel",
+                         "bytes_per_edge": bytes_per_edge(), "launch_ms": per_launch_ms},
+        }
+        if not args.no_cpu and world == 1:
+            v, n, dt = cpu_port_throughput(st, neg, args.cpu_sample_edges, 1)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
+                                    "sample": f"first {n} edges of the workload, bs={BS}, with negatives ({dt:.1f} s)"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--edges", type=int, default=None, help="truncate the stream (debug only)")
+    ap.add_argument("--batches-per-launch", type=int, default=64)
+    ap.add_argument("--e2e-batches", type=int, default=4000)
+    ap.add_argument("--cpu-sample-edges", type=int, default=1_000_000)
+    ap.add_argument("--ref-sample-edges", type=int, default=1_000_000)
+    ap.add_argument("--traffic", type=float, default=None, help="ncu dram bytes per launch, if captured")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -27,6 +27,7 @@ extern "C" {
 #endif
 
 typedef struct zebra_tppr zebra_tppr_t;
+typedef struct zebra_plan zebra_plan_t;
 
 /* ---- lifetime: replaces tppr_finder.__init__ (utils/util.py:393-400) ------------------------ */
 
@@ -84,6 +85,31 @@ int zebra_tppr_stream(zebra_tppr_t *h, const int32_t *host_nodes, const double *
 int zebra_tppr_update_only(zebra_tppr_t *h, const int64_t *host_src, const int64_t *host_dst,
                            const double *host_ts, const int64_t *host_eidx, int64_t n_edges,
                            void *stream);
+
+/* ---- resident spans ("plans") -----------------------------------------------------------------
+ * T-PPR state depends only on the edge stream, never on the model (utils/util.py:495-574 reads
+ * nothing but nodes, timestamps and edge ids), so a whole chronological span — an epoch's train
+ * split, a validation pass with its seeded negatives (evaluation/evaluation.py:9-10) — can be
+ * prepared once, kept resident in HBM and replayed batch by batch without any host->device
+ * traffic.  Results are identical to calling zebra_tppr_stream once per batch of `batch_size`
+ * edges: several batches may share one kernel launch because the dependency tickets, not the
+ * batch boundary, order the updates.
+ *
+ *   host_src/dst/neg  int32 [n] each (neg may be NULL unless rows_per_edge == 3)
+ *   plan_run          runs batches [first_batch, first_batch + n_batches) in order; a plan must be
+ *                     started at batch 0 (which restarts the dependency counters) and run to its
+ *                     end before other spans are streamed on the handle.  Batch b writes its rows,
+ *                     in the per-batch layout of zebra_tppr_stream, to slot
+ *                     (b - first_batch) % out_slots of dev_out; a slot holds
+ *                     zebra_tppr_out_bytes(h, batch_size, rows_per_edge) bytes.  Asynchronous.
+ */
+int zebra_tppr_plan_create(zebra_tppr_t *h, const int32_t *host_src, const int32_t *host_dst,
+                           const int32_t *host_neg, const double *host_ts, const int64_t *host_eidx,
+                           int64_t n, int32_t rows_per_edge, int64_t batch_size, zebra_plan_t **out);
+int zebra_tppr_plan_destroy(zebra_plan_t *plan);
+int64_t zebra_tppr_plan_batches(const zebra_plan_t *plan);
+int zebra_tppr_plan_run(zebra_tppr_t *h, zebra_plan_t *plan, int64_t first_batch, int64_t n_batches,
+                        int64_t batches_per_launch, void *dev_out, int64_t out_slots, void *stream);
 
 /* Debug / test access: copy the vectors of `n_ids` nodes of instance `inst` to host arrays
  * (counts int32[n_ids], eidx int32[n_ids*k], node int32[n_ids*k], ts f64[n_ids*k],

@@ -190,3 +190,36 @@ def test_errors_are_loud():
     # empty batch
     o = f.streaming_topk(np.zeros(0, np.int32), np.zeros(0), np.zeros(0, np.int64))
     assert o[0][0].shape == (0, 5)
+
+
+@pytest.mark.parametrize("per_launch", [1, 7, 64])
+def test_resident_plan_equals_per_batch_calls(per_launch):
+    """A resident plan replayed with several batches per launch == one streaming_topk call per batch."""
+    import torch
+    st = synth.make_stream("reddit", n_edges=12_345)
+    bs = 200
+    neg = synth.make_negatives(st, bs)
+    N = st.shape.table_nodes
+    al, be = [0.1, 0.1], [0.5, 0.95]
+    f = _finder(N, 20, 2, al, be)
+    o = oracle.OracleFinder(N, 20, 2, al, be)
+    plan = f.make_plan(st.src, st.dst, neg, st.ts, st.eidx, bs)
+    nb = plan.n_batches
+    assert nb == (12_345 + bs - 1) // bs
+    out = plan.run(0, nb, per_launch, out_slots=nb)
+    f.sync_check()
+    for b in range(nb):
+        lo, hi = b * bs, min(st.n_edges, (b + 1) * bs)
+        nodes = np.concatenate([st.src[lo:hi], st.dst[lo:hi], neg[lo:hi]]).astype(np.int32)
+        ref = o.streaming_topk(nodes, np.concatenate([st.ts[lo:hi]] * 3), st.eidx[lo:hi])
+        got = plan.views(out, b, 0, nb)
+        for q in range(4):
+            for j in range(2):
+                assert np.array_equal(got[q][j].cpu().numpy(), ref[q][j]), (b, q, j)
+    # the handle keeps working with ordinary calls after the plan finished
+    lo, hi = 0, 200
+    nodes = np.concatenate([st.src[lo:hi], st.dst[lo:hi], neg[lo:hi]]).astype(np.int32)
+    a = f.streaming_topk(nodes, np.concatenate([st.ts[lo:hi]] * 3), st.eidx[lo:hi])
+    r = o.streaming_topk(nodes, np.concatenate([st.ts[lo:hi]] * 3), st.eidx[lo:hi])
+    assert all(np.array_equal(a[q][j], r[q][j]) for q in range(4) for j in range(2))
+    assert f.counters()["timeouts"] == 0

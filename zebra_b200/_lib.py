@@ -21,6 +21,10 @@ SIGNATURES = {
     "zebra_tppr_out_bytes": (C.c_size_t, [_VP, _I64, _I32]),
     "zebra_tppr_stream": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _I32, _I32, _VP, _VP, _VP]),
     "zebra_tppr_update_only": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _I64, _VP]),
+    "zebra_tppr_plan_create": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _I64, _I32, _I64, C.POINTER(_VP)]),
+    "zebra_tppr_plan_destroy": (C.c_int, [_VP]),
+    "zebra_tppr_plan_batches": (_I64, [_VP]),
+    "zebra_tppr_plan_run": (C.c_int, [_VP, _VP, _I64, _I64, _I64, _VP, _I64, _VP]),
     "zebra_tppr_read_state": (C.c_int, [_VP, _I32, _VP, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "zebra_tppr_sync_check": (C.c_int, [_VP, _VP]),
     "zebra_tppr_counters": (C.c_int, [_VP, _VP]),

@@ -68,6 +68,18 @@ struct zebra_tppr {
     bool timed = false;
     int max_blocks = 0;
     int64_t launches = 0, last_items = 0, last_ties = 0, timeouts = 0;
+    struct zebra_plan *plan_active = nullptr;   // a plan is part-way through its batches
+    int64_t plan_next = 0;
+};
+
+// A span prepared once and kept resident in HBM (edge records + dependency thresholds).
+struct zebra_plan {
+    zebra_tppr *h = nullptr;
+    int64_t n = 0, batch_size = 0, n_batches = 0;
+    int32_t rows_per_edge = 0;
+    char *dev = nullptr;
+    size_t cap = 0;
+    std::vector<uint32_t> fin_acc, fin_lastw;   // host mirrors after the whole plan has run
 };
 
 namespace {
@@ -95,16 +107,13 @@ int ensure_staging(zebra_tppr *h, Staging &s, size_t edges)
 // Access thresholds: a writer waits for every earlier access of the node, a reader for the last
 // earlier writer.  A negative equal to src or dst is served from the writer's registers.
 template <typename NodeT>
-int prepare_chunk(zebra_tppr *h, Staging &s, const NodeT *src, const NodeT *dst, const NodeT *neg, const double *ts,
-                  const int64_t *eidx, int64_t m)
+int fill_soa(int64_t N, uint32_t *acc, uint32_t *lastw, char *host, size_t cap, const NodeT *src, const NodeT *dst,
+             const NodeT *neg, const double *ts, const int64_t *eidx, int64_t m)
 {
-    const size_t cap = (static_cast<size_t>(m) + 7) & ~static_cast<size_t>(7);   // SoA stride of this launch
-    int32_t *o_src = reinterpret_cast<int32_t *>(s.host);
+    int32_t *o_src = reinterpret_cast<int32_t *>(host);
     int32_t *o_dst = o_src + cap, *o_neg = o_dst + cap, *o_e = o_neg + cap;
     uint32_t *t_s = reinterpret_cast<uint32_t *>(o_e + cap), *t_d = t_s + cap, *t_n = t_d + cap;
     double *o_ts = reinterpret_cast<double *>(t_n + cap);
-    uint32_t *acc = h->acc.data(), *lastw = h->lastw.data();
-    const int64_t N = h->num_nodes;
     for (int64_t i = 0; i < m; ++i) {   // validate before touching the mirrors
         const int64_t a = src[i], b = dst[i], g = neg ? static_cast<int64_t>(neg[i]) : a;
         const int64_t e = eidx[i];
@@ -128,38 +137,60 @@ int prepare_chunk(zebra_tppr *h, Staging &s, const NodeT *src, const NodeT *dst,
     return 0;
 }
 
-int launch_chunk(zebra_tppr *h, Staging &s, int64_t m, int64_t n_total, int64_t i_offset, int32_t rows_per_edge,
-                 int32_t inst_mask, char *out, cudaStream_t st)
+struct BatchOut {
+    int64_t batch_size = 0, first_batch = 0, out_slots = 1, slot_bytes = 0;
+};
+
+// Launches the span kernel over m edges whose SoA arrays (stride `cap`) start at `dev`+`lo`.
+template <typename NodeT>
+int prepare_chunk(zebra_tppr *h, Staging &s, const NodeT *src, const NodeT *dst, const NodeT *neg, const double *ts,
+                  const int64_t *eidx, int64_t m)
 {
-    const size_t cap = (static_cast<size_t>(m) + 7) & ~static_cast<size_t>(7);
-    CU(cudaMemcpyAsync(s.dev, s.host, cap * kEdgeBytes, cudaMemcpyHostToDevice, st));
-    if (i_offset == 0) CU(cudaEventRecord(h->ev0, st));
+    const size_t cap = (static_cast<size_t>(m) + 7) & ~static_cast<size_t>(7);   // SoA stride of this launch
+    return fill_soa<NodeT>(h->num_nodes, h->acc.data(), h->lastw.data(), s.host, cap, src, dst, neg, ts, eidx, m);
+}
+
+int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_t m, int64_t n_total, int64_t i_offset,
+                  int32_t rows_per_edge, int32_t inst_mask, char *out, const BatchOut &bo, cudaStream_t st)
+{
     zebra::SpanParams p;
     memset(&p, 0, sizeof p);
     p.n_chunk = m; p.n_total = n_total; p.i_offset = i_offset; p.rows_total = static_cast<int64_t>(rows_per_edge) * n_total;
     p.k = h->k; p.n_tppr = h->n_tppr; p.rows_per_edge = rows_per_edge; p.inst_mask = inst_mask; p.stride = h->stride;
     p.ticket_base = h->ticket_base;
-    p.src = reinterpret_cast<const int32_t *>(s.dev);
-    p.dst = p.src + cap; p.neg = p.dst + cap; p.eidx = p.neg + cap;
-    p.thr_s = reinterpret_cast<const uint32_t *>(p.eidx + cap); p.thr_d = p.thr_s + cap; p.thr_n = p.thr_d + cap;
-    p.ts = reinterpret_cast<const double *>(p.thr_n + cap);
+    const int32_t *a0 = reinterpret_cast<const int32_t *>(dev);
+    p.src = a0 + lo; p.dst = a0 + cap + lo; p.neg = a0 + 2 * cap + lo; p.eidx = a0 + 3 * cap + lo;
+    const uint32_t *t0 = reinterpret_cast<const uint32_t *>(a0 + 4 * cap);
+    p.thr_s = t0 + lo; p.thr_d = t0 + cap + lo; p.thr_n = t0 + 2 * cap + lo;
+    p.ts = reinterpret_cast<const double *>(t0 + 3 * cap) + lo;
     for (int j = 0; j < h->n_tppr; ++j) {
         p.tables[j] = h->tables[j];
         p.done[j] = h->done + static_cast<size_t>(j) * h->num_nodes;
         p.alpha[j] = h->alpha[j]; p.beta[j] = h->beta[j];
     }
     p.out = out; p.ticket = h->ticket; p.status = h->status;
+    p.batch_size = bo.batch_size; p.first_batch = bo.first_batch; p.out_slots = bo.out_slots; p.slot_bytes = bo.slot_bytes;
     const int64_t items = m * h->n_tppr;
     int blocks = static_cast<int>(std::min<int64_t>((items + zebra::kWarpsPerBlock - 1) / zebra::kWarpsPerBlock, h->max_blocks));
     if (blocks < 1) blocks = 1;
     zebra::tppr_span_kernel<<<blocks, zebra::kWarpsPerBlock * 32, 0, st>>>(p);
     CU(cudaGetLastError());
-    CU(cudaEventRecord(s.free_ev, st));
-    s.pending = true;
     // every warp of the grid draws exactly one ticket past the end
     h->ticket_base += static_cast<uint32_t>(items) + static_cast<uint32_t>(blocks) * zebra::kWarpsPerBlock;
     h->launches++;
     h->last_items += items;
+    return 0;
+}
+
+int launch_chunk(zebra_tppr *h, Staging &s, int64_t m, int64_t n_total, int64_t i_offset, int32_t rows_per_edge,
+                 int32_t inst_mask, char *out, cudaStream_t st)
+{
+    const size_t cap = (static_cast<size_t>(m) + 7) & ~static_cast<size_t>(7);
+    CU(cudaMemcpyAsync(s.dev, s.host, cap * kEdgeBytes, cudaMemcpyHostToDevice, st));
+    if (i_offset == 0) CU(cudaEventRecord(h->ev0, st));
+    if (launch_kernel(h, s.dev, cap, 0, m, n_total, i_offset, rows_per_edge, inst_mask, out, BatchOut(), st)) return 1;
+    CU(cudaEventRecord(s.free_ev, st));
+    s.pending = true;
     return 0;
 }
 
@@ -181,6 +212,7 @@ int run_span(zebra_tppr *h, const NodeT *src, const NodeT *dst, const NodeT *neg
 {
     for (int j = 0; j < h->n_tppr; ++j)
         if (!h->tables[j]) return fail("zebra_tppr_bind_tables has not been called");
+    if (h->plan_active) return fail("a plan is part-way through its batches; finish it before streaming other spans");
     CU(cudaSetDevice(h->device));
     CU(cudaMemsetAsync(h->status + 1, 0, 3 * sizeof(int32_t), st));   // [0] (time-out) is sticky
     h->last_items = 0;
@@ -288,6 +320,7 @@ int zebra_tppr_reset_tickets(zebra_tppr_t *h, void *stream)
     CU(cudaMemsetAsync(h->done, 0, sizeof(uint32_t) * h->num_nodes * h->n_tppr, st));
     std::fill(h->acc.begin(), h->acc.end(), 0u);
     std::fill(h->lastw.begin(), h->lastw.end(), 0u);
+    h->plan_active = nullptr;
     return 0;
 }
 
@@ -377,6 +410,98 @@ int zebra_tppr_read_state(zebra_tppr_t *h, int32_t inst, const int64_t *host_ids
     if (e == cudaSuccess) e = cudaStreamSynchronize(st);
     cudaFree(d);
     if (e != cudaSuccess) return fail("read_state failed: %s", cudaGetErrorString(e));
+    return 0;
+}
+
+int zebra_tppr_plan_create(zebra_tppr_t *h, const int32_t *host_src, const int32_t *host_dst, const int32_t *host_neg,
+                           const double *host_ts, const int64_t *host_eidx, int64_t n, int32_t rows_per_edge,
+                           int64_t batch_size, zebra_plan_t **out)
+{
+    if (!h || !out) return fail("null argument");
+    *out = nullptr;
+    if (n <= 0 || batch_size <= 0) return fail("plan needs n > 0 and batch_size > 0");
+    if (rows_per_edge != 0 && rows_per_edge != 2 && rows_per_edge != 3) return fail("rows_per_edge must be 0, 2 or 3");
+    if (!host_src || !host_dst || !host_ts || !host_eidx || (rows_per_edge == 3 && !host_neg)) return fail("null input");
+    CU(cudaSetDevice(h->device));
+    zebra_plan *pl = new zebra_plan();
+    pl->h = h; pl->n = n; pl->batch_size = batch_size; pl->rows_per_edge = rows_per_edge;
+    pl->n_batches = (n + batch_size - 1) / batch_size;
+    pl->cap = (static_cast<size_t>(n) + 7) & ~static_cast<size_t>(7);
+    pl->fin_acc.assign(static_cast<size_t>(h->num_nodes), 0u);
+    pl->fin_lastw.assign(static_cast<size_t>(h->num_nodes), 0u);
+    std::vector<char> host(pl->cap * kEdgeBytes);
+    if (fill_soa<int32_t>(h->num_nodes, pl->fin_acc.data(), pl->fin_lastw.data(), host.data(), pl->cap, host_src, host_dst,
+                          rows_per_edge == 3 ? host_neg : nullptr, host_ts, host_eidx, n)) {
+        delete pl;
+        return 1;
+    }
+    cudaError_t e = cudaMalloc(&pl->dev, pl->cap * kEdgeBytes);
+    if (e == cudaSuccess) e = cudaMemcpy(pl->dev, host.data(), pl->cap * kEdgeBytes, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        if (pl->dev) cudaFree(pl->dev);
+        delete pl;
+        return fail("plan upload failed: %s", cudaGetErrorString(e));
+    }
+    *out = pl;
+    return 0;
+}
+
+int zebra_tppr_plan_destroy(zebra_plan_t *pl)
+{
+    if (!pl) return 0;
+    if (pl->h && pl->h->plan_active == pl) pl->h->plan_active = nullptr;
+    if (pl->dev) { cudaSetDevice(pl->h->device); cudaDeviceSynchronize(); cudaFree(pl->dev); }
+    delete pl;
+    return 0;
+}
+
+int64_t zebra_tppr_plan_batches(const zebra_plan_t *pl) { return pl ? pl->n_batches : 0; }
+
+int zebra_tppr_plan_run(zebra_tppr_t *h, zebra_plan_t *pl, int64_t first_batch, int64_t n_batches,
+                        int64_t batches_per_launch, void *dev_out, int64_t out_slots, void *stream)
+{
+    if (!h || !pl || pl->h != h) return fail("plan does not belong to this handle");
+    if (n_batches <= 0) return 0;
+    if (batches_per_launch <= 0) return fail("batches_per_launch must be positive");
+    if (first_batch < 0 || first_batch + n_batches > pl->n_batches) return fail("batch range out of the plan");
+    for (int j = 0; j < h->n_tppr; ++j)
+        if (!h->tables[j]) return fail("zebra_tppr_bind_tables has not been called");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    CU(cudaSetDevice(h->device));
+    if (first_batch == 0) {
+        // plan thresholds count from zero: restart the dependency counters
+        CU(cudaMemsetAsync(h->done, 0, sizeof(uint32_t) * h->num_nodes * h->n_tppr, st));
+        h->plan_active = pl;
+        h->plan_next = 0;
+    }
+    if (h->plan_active != pl || h->plan_next != first_batch)
+        return fail("plan batches must run in order starting from 0 (next expected %lld)", (long long)h->plan_next);
+    if (pl->rows_per_edge) {
+        if (!dev_out || out_slots <= 0) return fail("plan with output rows needs dev_out and out_slots");
+        if (out_slots < std::min(batches_per_launch, n_batches))
+            return fail("out_slots must cover one launch window");
+    }
+    BatchOut bo;
+    bo.batch_size = pl->batch_size; bo.first_batch = first_batch; bo.out_slots = std::max<int64_t>(out_slots, 1);
+    bo.slot_bytes = static_cast<int64_t>(zebra_tppr_out_bytes(h, pl->batch_size, pl->rows_per_edge));
+    CU(cudaMemsetAsync(h->status + 1, 0, 3 * sizeof(int32_t), st));
+    h->last_items = 0;
+    CU(cudaEventRecord(h->ev0, st));
+    const int64_t last = first_batch + n_batches;
+    for (int64_t b = first_batch; b < last; b += batches_per_launch) {
+        const int64_t be = std::min(last, b + batches_per_launch);
+        const int64_t lo = b * pl->batch_size, hi = std::min(pl->n, be * pl->batch_size);
+        if (launch_kernel(h, pl->dev, pl->cap, lo, hi - lo, pl->n, lo, pl->rows_per_edge, (1 << h->n_tppr) - 1,
+                          static_cast<char *>(dev_out), bo, st)) return 1;
+    }
+    CU(cudaEventRecord(h->ev1, st));
+    h->timed = true;
+    h->plan_next = last;
+    if (last == pl->n_batches) {
+        h->acc = pl->fin_acc;
+        h->lastw = pl->fin_lastw;
+        h->plan_active = nullptr;
+    }
     return 0;
 }
 

@@ -33,6 +33,10 @@ struct SpanParams {
     uint32_t *done[kMaxInst];
     double alpha[kMaxInst], beta[kMaxInst];
     char *out;              // [n_tppr][4][rows_total*k] 4-byte elements, or nullptr
+    // batch-structured output (plan mode): batch_size > 0 => edge g = i_offset + i belongs to batch
+    // b = g / batch_size and its rows go to slot (b - first_batch) % out_slots of `out`, laid out
+    // as the reference lays out that batch: [n_tppr][4][rows_per_edge*nb*k], nb = edges in batch b
+    int64_t batch_size, first_batch, out_slots, slot_bytes;
     uint32_t *ticket;
     int32_t *status;        // [0] spin time-out flag, [1] exact-tie prunes (statistics)
 };
@@ -86,12 +90,10 @@ __device__ __forceinline__ unsigned long long order_bits(double v)
 }
 
 // utils/util.py:447-469: one output row in dict order; dt = f32(t_now - f64(f32(ts))).
-__device__ __forceinline__ void emit_row(const SpanParams &p, int j, int64_t row, const VecR &v, double t_now,
-                                         int lane)
+__device__ __forceinline__ void emit_row(const SpanParams &p, char *base, size_t plane, int64_t row, const VecR &v,
+                                         double t_now, int lane)
 {
     if (lane >= p.k) return;
-    size_t plane = static_cast<size_t>(p.rows_total) * p.k;
-    char *base = p.out + static_cast<size_t>(j) * plane * 16;
     size_t o = static_cast<size_t>(row) * p.k + lane;
     int node = 0, eidx = 0;
     float dt = 0.f, w = 0.f;
@@ -372,18 +374,28 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
         const int e = p.eidx[i];
 
         if (p.rows_per_edge >= 2) {
-            const int64_t row = p.i_offset + i;
-            emit_row(p, j, row, S, t, lane);
-            emit_row(p, j, row + p.n_total, D, t, lane);
+            int64_t row = p.i_offset + i, nrow = p.n_total;
+            char *obase = p.out;
+            if (p.batch_size > 0) {
+                const int64_t b = row / p.batch_size;
+                row -= b * p.batch_size;
+                nrow = p.n_total - b * p.batch_size;
+                if (nrow > p.batch_size) nrow = p.batch_size;
+                obase += static_cast<size_t>((b - p.first_batch) % p.out_slots) * p.slot_bytes;
+            }
+            const size_t plane = static_cast<size_t>(nrow) * p.rows_per_edge * k;
+            obase += static_cast<size_t>(j) * plane * 16;
+            emit_row(p, obase, plane, row, S, t, lane);
+            emit_row(p, obase, plane, row + nrow, D, t, lane);
             if (has_neg) {
                 if (neg_own) {
                     const VecR G = load_vec(table + static_cast<size_t>(gN) * p.stride, k, lane);
-                    emit_row(p, j, row + 2 * p.n_total, G, t, lane);
+                    emit_row(p, obase, plane, row + 2 * nrow, G, t, lane);
                     __threadfence();               // the read of G is complete before it is released
                     __syncwarp();
                     if (lane == 0) atomicAdd(done + gN, 1u);
                 } else {
-                    emit_row(p, j, row + 2 * p.n_total, gN == sN ? S : D, t, lane);
+                    emit_row(p, obase, plane, row + 2 * nrow, gN == sN ? S : D, t, lane);
                 }
             }
         }

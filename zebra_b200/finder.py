@@ -153,6 +153,11 @@ class tppr_finder:  # noqa: N801  (name kept from the reference)
                                                  self._stream_ptr()))
         self._val_tables = self._snapshot(self._tables)
 
+    # ---- resident spans (include/zebra_tppr.h "plans") ----
+    def make_plan(self, src, dst, neg, timestamps, edge_idxs, batch_size, rows_per_edge=3):
+        """Prepare a whole chronological span once and keep it resident in HBM."""
+        return StreamPlan(self, src, dst, neg, timestamps, edge_idxs, batch_size, rows_per_edge)
+
     # ---- introspection (tests, INTEGRATION.md) ----
     def state(self, inst, nodes):
         """Vectors of `nodes` in instance `inst`: list of (eidx, node, ts, score, norm) in slot order."""
@@ -182,5 +187,74 @@ class tppr_finder:  # noqa: N801  (name kept from the reference)
             if getattr(self, "_h", None):
                 self._L.zebra_tppr_destroy(self._h)
                 self._h = None
+        except Exception:
+            pass
+
+
+class StreamPlan:
+    """A span resident on the device; `run` replays batches [first, first+n) without host traffic.
+
+    Batch b's rows land in slot (b - first) % out_slots of the returned buffer, each slot laid out
+    exactly like one `streaming_topk` call on that batch; `views(buf, b, first)` slices it."""
+
+    def __init__(self, finder, src, dst, neg, timestamps, edge_idxs, batch_size, rows_per_edge):
+        self.f = finder
+        self.rows_per_edge = int(rows_per_edge)
+        self.batch_size = int(batch_size)
+        src = np.ascontiguousarray(src, dtype=np.int32)
+        dst = np.ascontiguousarray(dst, dtype=np.int32)
+        neg = None if neg is None else np.ascontiguousarray(neg, dtype=np.int32)
+        ts = np.ascontiguousarray(timestamps, dtype=np.float64)
+        eidx = np.ascontiguousarray(edge_idxs, dtype=np.int64)
+        self.n = len(src)
+        h = C.c_void_p()
+        with torch.cuda.device(finder.device):
+            check(finder._L.zebra_tppr_plan_create(finder._h, _ptr(src), _ptr(dst), _ptr(neg), _ptr(ts), _ptr(eidx), self.n,
+                                                   self.rows_per_edge, self.batch_size, C.byref(h)))
+        self._p = h
+        self.n_batches = int(finder._L.zebra_tppr_plan_batches(h))
+        self.slot_bytes = int(finder._L.zebra_tppr_out_bytes(finder._h, self.batch_size, self.rows_per_edge))
+
+    def alloc_out(self, out_slots):
+        return torch.empty(max(1, out_slots * self.slot_bytes), dtype=torch.uint8, device=self.f.device)
+
+    def run(self, first=0, n_batches=None, batches_per_launch=1, out=None, out_slots=None):
+        n_batches = self.n_batches - first if n_batches is None else n_batches
+        if out_slots is None:
+            out_slots = min(batches_per_launch, n_batches)
+        if out is None and self.rows_per_edge:
+            out = self.alloc_out(out_slots)
+        f = self.f
+        with torch.cuda.device(f.device):
+            check(f._L.zebra_tppr_plan_run(f._h, self._p, first, n_batches, batches_per_launch,
+                                           _ptr(out) if self.rows_per_edge else None, out_slots, f._stream_ptr()))
+        return out
+
+    def batch_edges(self, b):
+        return min(self.batch_size, self.n - b * self.batch_size)
+
+    def views(self, out, b, first=0, out_slots=None):
+        """The four lists of n_tppr [rows,k] tensors of batch b inside `out`."""
+        out_slots = out.numel() // self.slot_bytes if out_slots is None else out_slots
+        slot = (b - first) % out_slots
+        nb, k = self.batch_edges(b), self.f.k
+        rows = self.rows_per_edge * nb
+        plane = rows * k
+        base0 = slot * self.slot_bytes
+        res = ([], [], [], [])
+        for j in range(self.f.n_tppr):
+            base = base0 + j * plane * 16
+            for q, dt in enumerate((torch.int32, torch.int32, torch.float32, torch.float32)):
+                res[q].append(out[base + q * plane * 4: base + (q + 1) * plane * 4].view(dt).view(rows, k))
+        return res
+
+    def close(self):
+        if getattr(self, "_p", None):
+            self.f._L.zebra_tppr_plan_destroy(self._p)
+            self._p = None
+
+    def __del__(self):
+        try:
+            self.close()
         except Exception:
             pass
