@@ -1,0 +1,27 @@
+#!/bin/bash
+# One gpurun call: GPU parity tests, perf probe, bench (ours + reference arm), ncu launch list + full capture.
+# Usage (from the repo root on the GPU box): bash tools/gpu_check.sh [tests|bench|ncu ...]
+set -u
+mkdir -p gpurun_out
+WHAT="${*:-tests probe bench ncu}"
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/gpu.txt 2>&1
+lscpu | head -20 > gpurun_out/lscpu.txt 2>&1
+for w in $WHAT; do
+case $w in
+tests)
+  timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
+  tail -5 gpurun_out/pytest_gpu.log ;;
+probe)
+  timeout 600 python tools/perf_probe.py > gpurun_out/probe.log 2>&1; echo "probe rc=$?"; cat gpurun_out/probe.log ;;
+bench)
+  timeout 900 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"; cat gpurun_out/bench.json; tail -3 gpurun_out/bench.err
+  timeout 600 python bench.py --impl reference --steps 1 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"; cat gpurun_out/bench_ref.json ;;
+ncu)
+  CMD="python bench.py --edges 400000 --steps 1 --warmup 1 --no-cpu --e2e-batches 10"
+  timeout 600 $CMD > gpurun_out/ncu_plain.log 2>&1 &&
+  timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launches.log 2>&1
+  echo "ncu launches rc=$?"
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:tppr_span -s 40 -c 2 -f -o gpurun_out/prof $CMD > gpurun_out/ncu_full.log 2>&1
+  echo "ncu full rc=$?"; tail -3 gpurun_out/ncu_full.log ;;
+esac
+done
