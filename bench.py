@@ -230,7 +230,7 @@ def run_ours(args):
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     e2e_edges = sum(len(b[2]) for b in batches)
-    h2d = sum(((len(b[2]) + 7) // 8 * 8) * 36 for b in batches)
+    h2d = sum(((len(b[2]) + 7) // 8 * 8) * 48 for b in batches)
     d2h = sum(len(ALPHAS) * 16 * 3 * len(b[2]) * K for b in batches)
 
     t = torch.tensor([ms, e2e_s], dtype=torch.float64, device=dev)
@@ -251,7 +251,7 @@ def run_ours(args):
                                    f"topk={K}, alpha {ALPHAS}, beta {BETAS}, bs={BS}, negatives included",
                        "step": "reset tables + stream the whole span once",
                        "batches_per_launch": window, "parallelism": f"replicas x{world}" if world > 1 else "single GPU",
-                       "l2": f"table {2 * N * 512 / 1e6:.0f} MB + outputs exceed the 126 MB L2 (inputs larger than L2)",
+                       "l2": f"tables {len(ALPHAS) * N * f._record_bytes / 1e6:.0f} MB + outputs exceed the 126 MB L2 (inputs larger than L2)",
                        "tie_path_prunes_last_step": tie_prunes},
             "e2e": {"value": world * e2e_edges * args.steps / e2e_s, "unit": UNIT,
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

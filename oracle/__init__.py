@@ -186,9 +186,9 @@ class OracleNeighborFinder:
 
 
 def stats():
-    o = np.zeros(3, np.int64)
+    o = np.zeros(4, np.int64)
     lib().zo_stats_get(_p(o))
-    return {"prunes": int(o[0]), "prunes_with_tie": int(o[1]), "boundary_ties": int(o[2])}
+    return {"prunes": int(o[0]), "prunes_with_tie": int(o[1]), "boundary_ties": int(o[2]), "relevant_ties": int(o[3])}
 
 
 def stats_reset():

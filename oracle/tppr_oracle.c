@@ -48,6 +48,7 @@ typedef struct {
     int64_t prunes;          /* updates where |T| > k */
     int64_t prunes_with_tie; /* ... and two candidates had exactly equal scores */
     int64_t boundary_ties;   /* ... and the k-th and (k+1)-th largest were equal */
+    int64_t relevant_ties;   /* ... and a tied pair includes a survivor (order/selection depends on the sort) */
 } zo_stats;
 
 static zo_stats g_stats;
@@ -99,9 +100,10 @@ int32_t zo_table_get(const zo_table *t, int64_t v, int64_t *eidx, int64_t *node,
     return c;
 }
 
-void zo_stats_get(int64_t *out3)
+void zo_stats_get(int64_t *out4)
 {
-    out3[0] = g_stats.prunes; out3[1] = g_stats.prunes_with_tie; out3[2] = g_stats.boundary_ties;
+    out4[0] = g_stats.prunes; out4[1] = g_stats.prunes_with_tie; out4[2] = g_stats.boundary_ties;
+    out4[3] = g_stats.relevant_ties;
 }
 void zo_stats_reset(void) { memset(&g_stats, 0, sizeof g_stats); }
 
@@ -254,6 +256,8 @@ static void update_one(const zo_table *tb, double alpha, double beta, int64_t s1
         for (int32_t j = 1; j < T->n; ++j) if (T->score[S[j]] == T->score[S[j - 1]]) { tie = 1; break; }
         if (tie) g_stats.prunes_with_tie++;
         if (T->score[S[T->n - k]] == T->score[S[T->n - k - 1]]) g_stats.boundary_ties++;
+        for (int32_t j = T->n - k; j < T->n; ++j)
+            if (T->score[S[j]] == T->score[S[j - 1]]) { g_stats.relevant_ties++; break; }
     }
     out->n = k;
     for (int32_t j = 0; j < k; ++j) {

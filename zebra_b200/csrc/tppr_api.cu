@@ -10,7 +10,9 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <climits>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -52,8 +54,10 @@ struct zebra_tppr {
     int32_t k = 0, n_tppr = 0, stride = 0, device = 0;
     double alpha[zebra::kMaxInst], beta[zebra::kMaxInst];
     char *tables[zebra::kMaxInst] = {};
-    uint32_t *done = nullptr;                 // [n_tppr][num_nodes]
-    std::vector<uint32_t> acc, lastw;         // host mirror: accesses issued / count at last write
+    int32_t *rcnt = nullptr;                  // [n_tppr][num_nodes] negative reads finished, not yet consumed by a writer
+    std::vector<int32_t> lastw, rhead, rnext; // host scratch of the dependency pass (all -1 between passes)
+    std::vector<uint32_t> rcount;             // host scratch: negative reads of a node since its last write
+    uint32_t epoch = 0;                       // tag epoch the bound tables were last written in
     uint32_t *ticket = nullptr;
     uint32_t ticket_base = 0;
     int32_t *status = nullptr;                // device [4]
@@ -79,15 +83,20 @@ struct zebra_plan {
     int32_t rows_per_edge = 0;
     char *dev = nullptr;
     size_t cap = 0;
-    std::vector<uint32_t> fin_acc, fin_lastw;   // host mirrors after the whole plan has run
+    uint32_t seq0 = 0;                          // tag base of the run in progress
 };
 
 namespace {
 
-size_t record_bytes(int k) { return (static_cast<size_t>(24) * k + 16 + 127) / 128 * 128; }
+size_t record_bytes(int k) { return zebra::record_stride(k); }
 
-// bytes per edge in a staging slot: src,dst,neg,eidx,thr_s,thr_d,thr_n (4 B each) + ts (8 B)
-constexpr size_t kEdgeBytes = 7 * 4 + 8;
+// bytes per edge in a staging slot: src,dst,neg,eidx,prev_s,prev_d,prev_n,rthr_s,rthr_d,flags (4 B each) + ts (8 B)
+constexpr size_t kEdgeBytes = 10 * 4 + 8;
+
+// Tags are edge sequence numbers drawn from one process-wide counter, so a table written through one
+// handle can be bound to another.  Tag 0 is what a zero-filled table carries.
+std::mutex g_seq_mu;
+uint32_t g_seq = 1, g_epoch = 0;
 
 int ensure_staging(zebra_tppr *h, Staging &s, size_t edges)
 {
@@ -103,36 +112,74 @@ int ensure_staging(zebra_tppr *h, Staging &s, size_t edges)
     return 0;
 }
 
-// Fills one staging slot for edges [lo, lo+m) of the span and advances the host mirrors.
-// Access thresholds: a writer waits for every earlier access of the node, a reader for the last
-// earlier writer.  A negative equal to src or dst is served from the writer's registers.
+// Fills one staging slot for m edges and derives their dependencies (one forward and one backward
+// pass, host scratch only — no state survives the call):
+//   prev_x   index (within these m edges) of the previous edge that wrote endpoint x, -1 = none;
+//   rthr_x   negative-sample reads of x's current version that must finish before it is overwritten;
+//   flags    kFlagSignal  : this edge's negative read is waited for by a later writer;
+//            kFlagDstFirst: dst is written again sooner than src -> update it first.
+// A negative equal to src or dst is served from the writer's registers.
 template <typename NodeT>
-int fill_soa(int64_t N, uint32_t *acc, uint32_t *lastw, char *host, size_t cap, const NodeT *src, const NodeT *dst,
-             const NodeT *neg, const double *ts, const int64_t *eidx, int64_t m)
+int fill_soa(zebra_tppr *h, char *host, size_t cap, const NodeT *src, const NodeT *dst, const NodeT *neg,
+             const double *ts, const int64_t *eidx, int64_t m)
 {
+    const int64_t N = h->num_nodes;
     int32_t *o_src = reinterpret_cast<int32_t *>(host);
     int32_t *o_dst = o_src + cap, *o_neg = o_dst + cap, *o_e = o_neg + cap;
-    uint32_t *t_s = reinterpret_cast<uint32_t *>(o_e + cap), *t_d = t_s + cap, *t_n = t_d + cap;
-    double *o_ts = reinterpret_cast<double *>(t_n + cap);
-    for (int64_t i = 0; i < m; ++i) {   // validate before touching the mirrors
+    int32_t *p_s = o_e + cap, *p_d = p_s + cap, *p_n = p_d + cap;
+    uint32_t *r_s = reinterpret_cast<uint32_t *>(p_n + cap), *r_d = r_s + cap, *flg = r_d + cap;
+    double *o_ts = reinterpret_cast<double *>(flg + cap);
+    for (int64_t i = 0; i < m; ++i) {   // validate before touching the scratch
         const int64_t a = src[i], b = dst[i], g = neg ? static_cast<int64_t>(neg[i]) : a;
         const int64_t e = eidx[i];
         if (a < 0 || a >= N || b < 0 || b >= N || g < 0 || g >= N)
             return fail("node id out of range at edge %lld (num_nodes=%lld)", (long long)i, (long long)N);
         if (e < 0 || e > 0x7fffffffLL) return fail("edge id %lld does not fit int32", (long long)e);
     }
+    int32_t *lastw = h->lastw.data(), *rhead = h->rhead.data();
+    uint32_t *rcount = h->rcount.data();
+    if (h->rnext.size() < static_cast<size_t>(m)) h->rnext.resize(static_cast<size_t>(m));
+    int32_t *rnext = h->rnext.data();
     for (int64_t i = 0; i < m; ++i) {
-        const int64_t a = src[i], b = dst[i], g = neg ? static_cast<int64_t>(neg[i]) : a;
-        const int64_t e = eidx[i];
-        o_src[i] = static_cast<int32_t>(a); o_dst[i] = static_cast<int32_t>(b); o_neg[i] = static_cast<int32_t>(g);
-        o_e[i] = static_cast<int32_t>(e);
+        const int32_t a = static_cast<int32_t>(src[i]), b = static_cast<int32_t>(dst[i]);
+        const int32_t g = neg ? static_cast<int32_t>(neg[i]) : a;
+        o_src[i] = a; o_dst[i] = b; o_neg[i] = g;
+        o_e[i] = static_cast<int32_t>(eidx[i]);
         o_ts[i] = ts[i];
-        uint32_t thn = 0;
-        if (neg && g != a && g != b) { thn = lastw[g]; acc[g]++; }
-        t_n[i] = thn;
-        t_s[i] = acc[a]; lastw[a] = ++acc[a];
-        if (b != a) { t_d[i] = acc[b]; lastw[b] = ++acc[b]; }
-        else t_d[i] = 0;
+        flg[i] = 0;
+        if (neg && g != a && g != b) {
+            p_n[i] = lastw[g];
+            rnext[i] = rhead[g]; rhead[g] = static_cast<int32_t>(i); rcount[g]++;
+        } else {
+            p_n[i] = -1;
+        }
+        p_s[i] = lastw[a]; r_s[i] = rcount[a];
+        if (rcount[a]) {
+            for (int32_t r = rhead[a]; r >= 0; r = rnext[r]) flg[r] |= zebra::kFlagSignal;
+            rhead[a] = -1; rcount[a] = 0;
+        }
+        lastw[a] = static_cast<int32_t>(i);
+        if (b != a) {
+            p_d[i] = lastw[b]; r_d[i] = rcount[b];
+            if (rcount[b]) {
+                for (int32_t r = rhead[b]; r >= 0; r = rnext[r]) flg[r] |= zebra::kFlagSignal;
+                rhead[b] = -1; rcount[b] = 0;
+            }
+            lastw[b] = static_cast<int32_t>(i);
+        } else {
+            p_d[i] = -1; r_d[i] = 0;
+        }
+    }
+    // backward: which endpoint is written again first (lastw doubles as "next write", INT_MAX = never)
+    for (int64_t i = 0; i < m; ++i) { lastw[o_src[i]] = INT_MAX; lastw[o_dst[i]] = INT_MAX; }
+    for (int64_t i = m - 1; i >= 0; --i) {
+        const int32_t a = o_src[i], b = o_dst[i];
+        if (a != b && lastw[b] < lastw[a]) flg[i] |= zebra::kFlagDstFirst;
+        lastw[a] = static_cast<int32_t>(i); lastw[b] = static_cast<int32_t>(i);
+    }
+    for (int64_t i = 0; i < m; ++i) {
+        lastw[o_src[i]] = -1; lastw[o_dst[i]] = -1;
+        rhead[o_neg[i]] = -1; rcount[o_neg[i]] = 0;
     }
     return 0;
 }
@@ -141,31 +188,58 @@ struct BatchOut {
     int64_t batch_size = 0, first_batch = 0, out_slots = 1, slot_bytes = 0;
 };
 
-// Launches the span kernel over m edges whose SoA arrays (stride `cap`) start at `dev`+`lo`.
+// Reserves n consecutive tags.  When the 32-bit sequence is about to wrap, it restarts at 1 and every
+// handle zeroes the tags of its bound tables before its next launch.
+int alloc_seq(zebra_tppr *h, int64_t n, cudaStream_t st, uint32_t *base)
+{
+    uint32_t epoch;
+    {
+        std::lock_guard<std::mutex> lk(g_seq_mu);
+        if (static_cast<uint64_t>(g_seq) + static_cast<uint64_t>(n) >= 0xF0000000ull) { g_seq = 1; ++g_epoch; }
+        *base = g_seq;
+        g_seq += static_cast<uint32_t>(n);
+        epoch = g_epoch;
+    }
+    if (h->epoch != epoch) {
+        const int per = 2 * h->k + 1;
+        const int64_t total = h->num_nodes * per;
+        for (int j = 0; j < h->n_tppr; ++j)
+            zebra::tppr_retag_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(h->tables[j], h->stride, h->k,
+                                                                                                h->num_nodes);
+        CU(cudaGetLastError());
+        h->epoch = epoch;
+    }
+    return 0;
+}
+
 template <typename NodeT>
 int prepare_chunk(zebra_tppr *h, Staging &s, const NodeT *src, const NodeT *dst, const NodeT *neg, const double *ts,
                   const int64_t *eidx, int64_t m)
 {
     const size_t cap = (static_cast<size_t>(m) + 7) & ~static_cast<size_t>(7);   // SoA stride of this launch
-    return fill_soa<NodeT>(h->num_nodes, h->acc.data(), h->lastw.data(), s.host, cap, src, dst, neg, ts, eidx, m);
+    return fill_soa<NodeT>(h, s.host, cap, src, dst, neg, ts, eidx, m);
 }
 
+// Launches the span kernel over m edges whose SoA arrays (stride `cap`) start at `dev`+`lo`.
 int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_t m, int64_t n_total, int64_t i_offset,
-                  int32_t rows_per_edge, int32_t inst_mask, char *out, const BatchOut &bo, cudaStream_t st)
+                  int32_t rows_per_edge, int32_t inst_mask, char *out, const BatchOut &bo, uint32_t seq0, int64_t tag_offset,
+                  cudaStream_t st)
 {
     zebra::SpanParams p;
     memset(&p, 0, sizeof p);
-    p.n_chunk = m; p.n_total = n_total; p.i_offset = i_offset; p.rows_total = static_cast<int64_t>(rows_per_edge) * n_total;
+    p.n_chunk = m; p.n_total = n_total; p.i_offset = i_offset;
     p.k = h->k; p.n_tppr = h->n_tppr; p.rows_per_edge = rows_per_edge; p.inst_mask = inst_mask; p.stride = h->stride;
     p.ticket_base = h->ticket_base;
+    p.seq0 = seq0; p.tag_offset = tag_offset;
     const int32_t *a0 = reinterpret_cast<const int32_t *>(dev);
     p.src = a0 + lo; p.dst = a0 + cap + lo; p.neg = a0 + 2 * cap + lo; p.eidx = a0 + 3 * cap + lo;
-    const uint32_t *t0 = reinterpret_cast<const uint32_t *>(a0 + 4 * cap);
-    p.thr_s = t0 + lo; p.thr_d = t0 + cap + lo; p.thr_n = t0 + 2 * cap + lo;
+    p.prev_s = a0 + 4 * cap + lo; p.prev_d = a0 + 5 * cap + lo; p.prev_n = a0 + 6 * cap + lo;
+    const uint32_t *t0 = reinterpret_cast<const uint32_t *>(a0 + 7 * cap);
+    p.rthr_s = t0 + lo; p.rthr_d = t0 + cap + lo; p.flags = t0 + 2 * cap + lo;
     p.ts = reinterpret_cast<const double *>(t0 + 3 * cap) + lo;
     for (int j = 0; j < h->n_tppr; ++j) {
         p.tables[j] = h->tables[j];
-        p.done[j] = h->done + static_cast<size_t>(j) * h->num_nodes;
+        p.rcnt[j] = h->rcnt + static_cast<size_t>(j) * h->num_nodes;
         p.alpha[j] = h->alpha[j]; p.beta[j] = h->beta[j];
     }
     p.out = out; p.ticket = h->ticket; p.status = h->status;
@@ -186,9 +260,11 @@ int launch_chunk(zebra_tppr *h, Staging &s, int64_t m, int64_t n_total, int64_t 
                  int32_t inst_mask, char *out, cudaStream_t st)
 {
     const size_t cap = (static_cast<size_t>(m) + 7) & ~static_cast<size_t>(7);
+    uint32_t seq0 = 0;
+    if (alloc_seq(h, m, st, &seq0)) return 1;
     CU(cudaMemcpyAsync(s.dev, s.host, cap * kEdgeBytes, cudaMemcpyHostToDevice, st));
     if (i_offset == 0) CU(cudaEventRecord(h->ev0, st));
-    if (launch_kernel(h, s.dev, cap, 0, m, n_total, i_offset, rows_per_edge, inst_mask, out, BatchOut(), st)) return 1;
+    if (launch_kernel(h, s.dev, cap, 0, m, n_total, i_offset, rows_per_edge, inst_mask, out, BatchOut(), seq0, 0, st)) return 1;
     CU(cudaEventRecord(s.free_ev, st));
     s.pending = true;
     return 0;
@@ -256,10 +332,12 @@ int zebra_tppr_create(zebra_tppr_t **out, int64_t num_nodes, int32_t k, int32_t 
     h->num_nodes = num_nodes; h->k = k; h->n_tppr = n_tppr; h->device = device;
     h->stride = static_cast<int32_t>(record_bytes(k));
     for (int j = 0; j < n_tppr; ++j) { h->alpha[j] = alpha_list[j]; h->beta[j] = beta_list[j]; }
-    h->acc.assign(static_cast<size_t>(num_nodes), 0u);
-    h->lastw.assign(static_cast<size_t>(num_nodes), 0u);
-    CU(cudaMalloc(&h->done, sizeof(uint32_t) * num_nodes * n_tppr));
-    CU(cudaMemset(h->done, 0, sizeof(uint32_t) * num_nodes * n_tppr));
+    h->lastw.assign(static_cast<size_t>(num_nodes), -1);
+    h->rhead.assign(static_cast<size_t>(num_nodes), -1);
+    h->rcount.assign(static_cast<size_t>(num_nodes), 0u);
+    CU(cudaMalloc(&h->rcnt, sizeof(int32_t) * num_nodes * n_tppr));
+    CU(cudaMemset(h->rcnt, 0, sizeof(int32_t) * num_nodes * n_tppr));
+    { std::lock_guard<std::mutex> lk(g_seq_mu); h->epoch = g_epoch; }
     CU(cudaMalloc(&h->ticket, sizeof(uint32_t)));
     CU(cudaMemset(h->ticket, 0, sizeof(uint32_t)));
     CU(cudaMalloc(&h->status, 4 * sizeof(int32_t)));
@@ -285,7 +363,7 @@ int zebra_tppr_destroy(zebra_tppr_t *h)
         if (s.dev) cudaFree(s.dev);
         if (s.free_ev) cudaEventDestroy(s.free_ev);
     }
-    if (h->done) cudaFree(h->done);
+    if (h->rcnt) cudaFree(h->rcnt);
     if (h->ticket) cudaFree(h->ticket);
     if (h->status) cudaFree(h->status);
     if (h->status_host) cudaFreeHost(h->status_host);
@@ -317,9 +395,7 @@ int zebra_tppr_reset_tickets(zebra_tppr_t *h, void *stream)
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     CU(cudaSetDevice(h->device));
     CU(cudaStreamSynchronize(st));
-    CU(cudaMemsetAsync(h->done, 0, sizeof(uint32_t) * h->num_nodes * h->n_tppr, st));
-    std::fill(h->acc.begin(), h->acc.end(), 0u);
-    std::fill(h->lastw.begin(), h->lastw.end(), 0u);
+    CU(cudaMemsetAsync(h->rcnt, 0, sizeof(int32_t) * h->num_nodes * h->n_tppr, st));
     h->plan_active = nullptr;
     return 0;
 }
@@ -427,11 +503,10 @@ int zebra_tppr_plan_create(zebra_tppr_t *h, const int32_t *host_src, const int32
     pl->h = h; pl->n = n; pl->batch_size = batch_size; pl->rows_per_edge = rows_per_edge;
     pl->n_batches = (n + batch_size - 1) / batch_size;
     pl->cap = (static_cast<size_t>(n) + 7) & ~static_cast<size_t>(7);
-    pl->fin_acc.assign(static_cast<size_t>(h->num_nodes), 0u);
-    pl->fin_lastw.assign(static_cast<size_t>(h->num_nodes), 0u);
+    if (n >= 0x70000000LL) { delete pl; return fail("plan too long"); }
     std::vector<char> host(pl->cap * kEdgeBytes);
-    if (fill_soa<int32_t>(h->num_nodes, pl->fin_acc.data(), pl->fin_lastw.data(), host.data(), pl->cap, host_src, host_dst,
-                          rows_per_edge == 3 ? host_neg : nullptr, host_ts, host_eidx, n)) {
+    if (fill_soa<int32_t>(h, host.data(), pl->cap, host_src, host_dst, rows_per_edge == 3 ? host_neg : nullptr, host_ts,
+                          host_eidx, n)) {
         delete pl;
         return 1;
     }
@@ -469,8 +544,9 @@ int zebra_tppr_plan_run(zebra_tppr_t *h, zebra_plan_t *pl, int64_t first_batch, 
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     CU(cudaSetDevice(h->device));
     if (first_batch == 0) {
-        // plan thresholds count from zero: restart the dependency counters
-        CU(cudaMemsetAsync(h->done, 0, sizeof(uint32_t) * h->num_nodes * h->n_tppr, st));
+        // a run abandoned part-way may have left unconsumed read counts behind
+        if (h->plan_active) CU(cudaMemsetAsync(h->rcnt, 0, sizeof(int32_t) * h->num_nodes * h->n_tppr, st));
+        if (alloc_seq(h, pl->n, st, &pl->seq0)) return 1;
         h->plan_active = pl;
         h->plan_next = 0;
     }
@@ -492,16 +568,12 @@ int zebra_tppr_plan_run(zebra_tppr_t *h, zebra_plan_t *pl, int64_t first_batch, 
         const int64_t be = std::min(last, b + batches_per_launch);
         const int64_t lo = b * pl->batch_size, hi = std::min(pl->n, be * pl->batch_size);
         if (launch_kernel(h, pl->dev, pl->cap, lo, hi - lo, pl->n, lo, pl->rows_per_edge, (1 << h->n_tppr) - 1,
-                          static_cast<char *>(dev_out), bo, st)) return 1;
+                          static_cast<char *>(dev_out), bo, pl->seq0, lo, st)) return 1;
     }
     CU(cudaEventRecord(h->ev1, st));
     h->timed = true;
     h->plan_next = last;
-    if (last == pl->n_batches) {
-        h->acc = pl->fin_acc;
-        h->lastw = pl->fin_lastw;
-        h->plan_active = nullptr;
-    }
+    if (last == pl->n_batches) h->plan_active = nullptr;
     return 0;
 }
 

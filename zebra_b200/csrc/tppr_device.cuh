@@ -2,8 +2,15 @@
 //
 // One warp owns one work item = (edge i, instance j) of a chronological span.  Items are claimed
 // in stream order from a global ticket, so every dependency of an item is held by a warp that is
-// already running: per-node completion counters (`done`) replace the barrier between the
-// reference's conflict-free "waves" with point-to-point waits (dataflow over the same DAG).
+// already running; the barrier between the reference's conflict-free "waves" becomes point-to-point
+// dataflow over the same DAG.
+//
+// Synchronisation is carried by the data itself.  A node record is a header and 2k 16-byte chunks,
+// every one of which ends in a 32-bit tag = sequence number of the edge that wrote it.  A reader
+// knows which edge wrote the version it needs (the host passes the index of the previous writer of
+// each endpoint) and simply re-reads the record until every chunk carries that tag: one L2 round
+// trip from the writer's stores to the reader's registers, no fence on the writer, no flag.
+// Writers wait only for the (rare) negative-sample readers of the version they overwrite.
 //
 // Semantics restated from the reference (LuckyLYM/Zebra utils/util.py:447-469, 495-574); the
 // arithmetic is IEEE fp64 with separate multiply and add roundings (build with -fmad=false; the
@@ -17,20 +24,29 @@ namespace zebra {
 constexpr int kMaxInst = 8;
 constexpr int kWarpsPerBlock = 8;
 constexpr unsigned kFull = 0xffffffffu;
+constexpr uint32_t kNear = 192;          // edges: closer than this to our turn -> poll the whole record
+
+// record layout: hdr {f64 norm, i32 count, u32 tag} | A[k] {f64 score, i32 eidx, u32 tag} |
+//                B[k] {f64 ts, i32 node, u32 tag} | pad to 128 B
+__host__ __device__ inline size_t record_stride(int k) { return (static_cast<size_t>(32) * k + 16 + 127) / 128 * 128; }
+
+enum : uint32_t { kFlagSignal = 1u, kFlagDstFirst = 2u };
 
 struct SpanParams {
     int64_t n_chunk;        // edges in this launch
     int64_t n_total;        // edges of the whole span (row stride of the output)
     int64_t i_offset;       // index of this launch's first edge inside the span
-    int64_t rows_total;     // rows_per_edge * n_total
     int32_t k, n_tppr, rows_per_edge, inst_mask;
     int32_t stride;         // bytes per node record
     uint32_t ticket_base;
-    const int32_t *src, *dst, *neg, *eidx;
-    const uint32_t *thr_s, *thr_d, *thr_n;
+    uint32_t seq0;          // tag of launch-local edge i = seq0 + tag_offset + i; a reader expects seq0 + prev
+    int64_t tag_offset;     // index base of the prev_* arrays relative to this launch's first edge
+    const int32_t *src, *dst, *neg, *eidx;          // indexed by launch-local edge
+    const int32_t *prev_s, *prev_d, *prev_n;        // span index of the previous writer, -1 = none
+    const uint32_t *rthr_s, *rthr_d, *flags;        // negative reads to wait for before overwriting
     const double *ts;
     char *tables[kMaxInst];
-    uint32_t *done[kMaxInst];
+    int32_t *rcnt[kMaxInst];                        // [num_nodes] completed-but-unconsumed negative reads
     double alpha[kMaxInst], beta[kMaxInst];
     char *out;              // [n_tppr][4][rows_total*k] 4-byte elements, or nullptr
     // batch-structured output (plan mode): batch_size > 0 => edge g = i_offset + i belongs to batch
@@ -56,25 +72,52 @@ struct VecR {
     double norm;
 };
 
-__device__ __forceinline__ uint32_t ld_acquire(const uint32_t *p)
+__device__ __forceinline__ uint4 ld_chunk(const char *p)
 {
-    uint32_t v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    uint4 v;
+    asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
     return v;
 }
 
-__device__ __forceinline__ VecR load_vec(const char *rec, int k, int lane)
+__device__ __forceinline__ void st_chunk(char *p, double d, int i, uint32_t tag)
 {
-    VecR v;
-    int l = lane < k ? lane : k - 1;
-    int2 kk = __ldcg(reinterpret_cast<const int2 *>(rec) + l);
-    v.e = kk.x; v.n = kk.y;
-    v.ts = __ldcg(reinterpret_cast<const double *>(rec + 8 * k) + l);
-    v.sc = __ldcg(reinterpret_cast<const double *>(rec + 16 * k) + l);
-    v.norm = __ldcg(reinterpret_cast<const double *>(rec + 24 * k));
-    v.cnt = __ldcg(reinterpret_cast<const int *>(rec + 24 * k + 8));
+    const unsigned long long b = static_cast<unsigned long long>(__double_as_longlong(d));
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(static_cast<uint32_t>(b)),
+                 "r"(static_cast<uint32_t>(b >> 32)), "r"(i), "r"(tag) : "memory");
+}
+
+__device__ __forceinline__ double chunk_f64(const uint4 &c)
+{
+    return __longlong_as_double(static_cast<long long>((static_cast<unsigned long long>(c.y) << 32) | c.x));
+}
+
+__device__ __forceinline__ int32_t ld_relaxed_s32(const int32_t *p)
+{
+    int32_t v;
+    asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+
+// One attempt to read a whole record.  `any`: the record has no writer earlier in this span, so it
+// is stable and any self-consistent content is the wanted version; otherwise every chunk must carry
+// `expect`.  `cur` returns the header tag seen (progress estimate for the back-off).
+__device__ __forceinline__ bool try_load(const char *rec, int k, int lane, bool any, uint32_t expect, VecR &v, uint32_t &cur)
+{
+    const int l = lane < k ? lane : k - 1;
+    const uint4 h = ld_chunk(rec);
+    const uint4 a = ld_chunk(rec + 16 + 16 * l);
+    const uint4 b = ld_chunk(rec + 16 + 16 * (k + l));
+    cur = h.w;
+    const uint32_t want = any ? h.w : expect;
+    const int cnt = static_cast<int>(h.z);
+    const bool ok = h.w == want && (lane >= cnt || (a.w == want && b.w == want));
+    v.sc = chunk_f64(a); v.e = static_cast<int>(a.z);
+    v.ts = chunk_f64(b); v.n = static_cast<int>(b.z);
+    v.norm = chunk_f64(h); v.cnt = cnt;
+    return __all_sync(kFull, ok);
+}
+
+__device__ __forceinline__ uint32_t ld_tag(const char *rec) { return ld_chunk(rec).w; }
 
 __device__ __forceinline__ unsigned long long pack_key(int e, int n)
 {
@@ -107,7 +150,6 @@ __device__ __forceinline__ void emit_row(const SpanParams &p, char *base, size_t
     reinterpret_cast<float *>(base + plane * 8)[o] = dt;
     reinterpret_cast<float *>(base + plane * 12)[o] = w;
 }
-
 // One partition step of numba.misc.quicksort (median of three, pivot stashed at `high`, Hoare
 // scan) on the permutation R over values V, computed warp-wide from two stopper bitmaps instead
 // of a sequential scan.  Returns the pivot's final position.
@@ -191,11 +233,19 @@ __device__ __forceinline__ void qs_partition_phase(WarpScratch &s, int n, int la
     __syncwarp();
 }
 
+
+__device__ __forceinline__ void st_entry(char *rec, int k, int pos, int e, int n, double ts, double sc, uint32_t tag)
+{
+    st_chunk(rec + 16 + 16 * pos, sc, e, tag);
+    st_chunk(rec + 16 + 16 * (k + pos), ts, n, tag);
+}
+
 // New vector of one endpoint from the OLD vectors of itself (A) and its peer (B)
-// (utils/util.py:509-559), written straight into the endpoint's record.
-__device__ __forceinline__ void update_endpoint(const SpanParams &p, WarpScratch &s, const VecR &A, const VecR &B,
+// (utils/util.py:509-559), written straight into the endpoint's record with tag `tag`.
+// `rwait` > 0: that many negative-sample reads of the old version must have finished first.
+__device__ __forceinline__ bool update_endpoint(const SpanParams &p, WarpScratch &s, const VecR &A, const VecR &B,
                                                 int peer_id, int e_new, double t_new, double alpha, double beta,
-                                                char *rec, int lane)
+                                                char *rec, uint32_t tag, int32_t *rcnt, uint32_t rwait, int lane)
 {
     const int k = p.k;
     const int c1 = A.cnt;
@@ -259,15 +309,10 @@ __device__ __forceinline__ void update_endpoint(const SpanParams &p, WarpScratch
         ++n;
     }
     const bool valid0 = lane < c1;
+    int pos0 = lane;
+    bool keep0 = valid0, keep1 = valid1;
 
-    int2 *keys = reinterpret_cast<int2 *>(rec);
-    double *tsp = reinterpret_cast<double *>(rec + 8 * k);
-    double *scp = reinterpret_cast<double *>(rec + 16 * k);
-    if (n <= k) {
-        // no prune: A's keys keep their slots, only their scores change
-        if (valid0) scp[lane] = vA;
-        if (valid1) { keys[pos1] = make_int2(e1, n1); tsp[pos1] = ts1; scp[pos1] = v1; }
-    } else {
+    if (n > k) {
         // ---- keep the k largest, re-inserted in ascending order (util.py:553-559) ----
         const unsigned long long b0 = order_bits(vA);
         const unsigned long long b1 = order_bits(v1);
@@ -276,15 +321,18 @@ __device__ __forceinline__ void update_endpoint(const SpanParams &p, WarpScratch
         if (valid1) s.V[pos1] = b1;
         __syncwarp();
         int r0 = 0, r1 = 0;
-        bool tie = false;
+        bool eq0 = false, eq1 = false;
         for (int q = 0; q < n; ++q) {
             const unsigned long long vq = s.V[q];
             r0 += (vq < b0) || (vq == b0 && q < lane);
             r1 += (vq < b1) || (vq == b1 && q < pos1);
-            tie |= (valid0 && vq == b0 && q != lane) || (valid1 && vq == b1 && q != pos1);
+            eq0 |= vq == b0 && q != lane;
+            eq1 |= vq == b1 && q != pos1;
         }
-        if (__any_sync(kFull, tie)) {
-            // exact numba argsort order among tied scores
+        const int cut = n - k;
+        // a tie only matters if one of the tied candidates survives under the stable order: then
+        // the survivor set or its slot order depends on numba's (unstable) argsort
+        if (__any_sync(kFull, (valid0 && eq0 && r0 >= cut) || (valid1 && eq1 && r1 >= cut))) {
             qs_partition_phase(s, n, lane);
             const int P0 = valid0 ? s.P[lane] : 0, P1 = valid1 ? s.P[pos1] : 0;
             r0 = 0; r1 = 0;
@@ -296,20 +344,35 @@ __device__ __forceinline__ void update_endpoint(const SpanParams &p, WarpScratch
             }
             if (lane == 0) atomicAdd(p.status + 1, 1);
         }
-        const int cut = n - k;
-        if (valid0 && r0 >= cut) { keys[r0 - cut] = make_int2(A.e, A.n); tsp[r0 - cut] = A.ts; scp[r0 - cut] = vA; }
-        if (valid1 && r1 >= cut) { keys[r1 - cut] = make_int2(e1, n1); tsp[r1 - cut] = ts1; scp[r1 - cut] = v1; }
+        keep0 = valid0 && r0 >= cut; pos0 = r0 - cut;
+        keep1 = valid1 && r1 >= cut; pos1 = r1 - cut;
         n = k;
     }
-    if (lane == 0) {
-        *reinterpret_cast<double *>(rec + 24 * k) = new_norm;
-        *reinterpret_cast<int *>(rec + 24 * k + 8) = n;
+
+    // ---- the version being overwritten may still have negative-sample readers ----
+    bool ok = true;
+    if (rwait != 0) {
+        unsigned spins = 0;
+        while (ld_relaxed_s32(rcnt) < static_cast<int32_t>(rwait)) {
+            if ((++spins & 0xff) == 0) {
+                if (*reinterpret_cast<volatile int32_t *>(p.status) != 0 || spins > (1u << 21)) { ok = false; break; }
+            }
+            __nanosleep(64);
+        }
+        if (lane == 0) atomicSub(rcnt, static_cast<int32_t>(rwait));
     }
+    if (keep0) st_entry(rec, k, pos0, A.e, A.n, A.ts, vA, tag);
+    if (keep1) st_entry(rec, k, pos1, e1, n1, ts1, v1, tag);
+    __syncwarp();
+    if (lane == 0) st_chunk(rec, new_norm, n, tag);
+    return ok;
 }
 
-__device__ __forceinline__ bool reached(uint32_t done, uint32_t thr)
+// how long to sleep before looking again at a record whose wanted version is `dist` edges away
+__device__ __forceinline__ unsigned backoff_ns(uint32_t dist)
 {
-    return static_cast<int32_t>(done - thr) >= 0;
+    const unsigned ns = dist * 8u;
+    return ns > 4000u ? 4000u : ns;
 }
 
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
@@ -320,6 +383,7 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
     WarpScratch &s = scratch[threadIdx.x >> 5];
     const unsigned long long total = static_cast<unsigned long long>(p.n_chunk) * p.n_tppr;
     const int k = p.k;
+    const uint32_t tag_base = p.seq0 + static_cast<uint32_t>(p.tag_offset);   // tag of launch-local edge 0
 
     for (;;) {
         uint32_t tk = 0;
@@ -333,45 +397,95 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
         const int gN = has_neg ? p.neg[i] : sN;
         const bool loop = sN == dN;
         const bool neg_own = has_neg && gN != sN && gN != dN;
-        uint32_t *done = p.done[j];
+        const uint32_t flags = p.flags[i];
+        int32_t *rcnt = p.rcnt[j];
 
-        if (!((p.inst_mask >> j) & 1)) {
-            // instance not selected: keep its counters in step with the shared thresholds
-            if (lane == 0) {
-                atomicAdd(done + sN, 1u);
-                if (!loop) atomicAdd(done + dN, 1u);
-                if (neg_own) atomicAdd(done + gN, 1u);
-            }
-            continue;
-        }
+        if (!((p.inst_mask >> j) & 1)) continue;   // instance not selected: its tables are not touched
 
-        // ---- wait for the producers of the three vectors (and earlier readers of src/dst) ----
-        const uint32_t ths = p.thr_s[i], thd = p.thr_d[i], thn = neg_own ? p.thr_n[i] : 0u;
-        bool okS = false, okD = loop, okG = !neg_own;
-        unsigned spins = 0;
-        for (;;) {
-            uint32_t a = 0, b = 0, c = 0;
-            if (!okS) a = ld_acquire(done + sN);
-            if (!okD) b = ld_acquire(done + dN);
-            if (!okG) c = ld_acquire(done + gN);
-            okS = okS || reached(a, ths);
-            okD = okD || reached(b, thd);
-            okG = okG || reached(c, thn);
-            if (okS && okD && okG) break;
-            if ((++spins & 0x3ff) == 0) {
-                if (*reinterpret_cast<volatile int32_t *>(p.status) != 0) break;
-                if (spins > (1u << 22)) { atomicExch(p.status, 1); break; }
-            }
-            __nanosleep(20);
-        }
-
+        const int32_t pS = p.prev_s[i], pD = loop ? -1 : p.prev_d[i], pG = neg_own ? p.prev_n[i] : -1;
         char *table = p.tables[j];
         char *recS = table + static_cast<size_t>(sN) * p.stride;
         char *recD = table + static_cast<size_t>(dN) * p.stride;
-        const VecR S = load_vec(recS, k, lane);
-        const VecR D = loop ? S : load_vec(recD, k, lane);
+        const char *recG = table + static_cast<size_t>(gN) * p.stride;
+        const uint32_t my_tag = tag_base + static_cast<uint32_t>(i);
+
+        // ---- read the three vectors; wait for the producers of src and dst (the chain) ----
+        VecR S, D, G;
+        uint32_t curS = 0, curD = 0, curG = 0;
+        bool okS = try_load(recS, k, lane, pS < 0, p.seq0 + static_cast<uint32_t>(pS), S, curS);
+        bool okD = loop ? true : try_load(recD, k, lane, pD < 0, p.seq0 + static_cast<uint32_t>(pD), D, curD);
+        bool okG = neg_own ? try_load(recG, k, lane, pG < 0, p.seq0 + static_cast<uint32_t>(pG), G, curG) : true;
+        bool alive = true;
+        unsigned spins = 0;
+        while (!(okS && okD)) {
+            // distance (in edges) of the farther unsatisfied producer from the version visible now
+            uint32_t dist = 0;
+            if (!okS) {
+                const uint32_t d = curS - tag_base, pe = static_cast<uint32_t>(pS - p.tag_offset);
+                dist = (d < static_cast<uint32_t>(p.n_chunk) && d <= pe) ? pe - d : pe + 1;
+            }
+            if (!okD) {
+                const uint32_t d = curD - tag_base, pe = static_cast<uint32_t>(pD - p.tag_offset);
+                const uint32_t dd = (d < static_cast<uint32_t>(p.n_chunk) && d <= pe) ? pe - d : pe + 1;
+                dist = dd > dist ? dd : dist;
+            }
+            if (dist > kNear) {
+                // far from our turn: sleep, then look at the header tags only
+                __nanosleep(backoff_ns(dist));
+                if (!okS) curS = ld_tag(recS);
+                if (!okD) curD = ld_tag(recD);
+                const bool nearS = okS || curS == p.seq0 + static_cast<uint32_t>(pS);
+                const bool nearD = okD || curD == p.seq0 + static_cast<uint32_t>(pD);
+                if (!(nearS && nearD)) {
+                    if ((++spins & 0xff) == 0) {
+                        if (*reinterpret_cast<volatile int32_t *>(p.status) != 0) { alive = false; break; }
+                        if (spins > (1u << 20)) { atomicExch(p.status, 1); alive = false; break; }
+                    }
+                    continue;
+                }
+            } else {
+                __nanosleep(32);
+            }
+            if (!okS) okS = try_load(recS, k, lane, false, p.seq0 + static_cast<uint32_t>(pS), S, curS);
+            if (!okD) okD = try_load(recD, k, lane, false, p.seq0 + static_cast<uint32_t>(pD), D, curD);
+            if (!okG) okG = try_load(recG, k, lane, false, p.seq0 + static_cast<uint32_t>(pG), G, curG);
+            if ((++spins & 0xff) == 0) {
+                if (*reinterpret_cast<volatile int32_t *>(p.status) != 0) { alive = false; break; }
+                if (spins > (1u << 22)) { atomicExch(p.status, 1); alive = false; break; }
+            }
+        }
+        if (!alive) continue;
+        if (loop) D = S;
+        if (okG && neg_own && (flags & kFlagSignal) && lane == 0) atomicAdd(rcnt + gN, 1);
+        bool sigG = okG;
+
         const double t = p.ts[i];
         const int e = p.eidx[i];
+        const double alpha = p.alpha[j], beta = p.beta[j];
+        const uint32_t rwS = p.rthr_s[i], rwD = loop ? 0u : p.rthr_d[i];
+
+        // ---- the hotter endpoint first: its next writer is the one most likely to be waiting ----
+        bool ok = true;
+        if ((flags & kFlagDstFirst) && !loop) {
+            ok &= update_endpoint(p, s, D, S, sN, e, t, alpha, beta, recD, my_tag, rcnt + dN, rwD, lane);
+            ok &= update_endpoint(p, s, S, D, dN, e, t, alpha, beta, recS, my_tag, rcnt + sN, rwS, lane);
+        } else {
+            ok &= update_endpoint(p, s, S, D, dN, e, t, alpha, beta, recS, my_tag, rcnt + sN, rwS, lane);
+            if (!loop) ok &= update_endpoint(p, s, D, S, sN, e, t, alpha, beta, recD, my_tag, rcnt + dN, rwD, lane);
+        }
+        if (!ok) { atomicExch(p.status, 1); continue; }
+
+        // ---- off the chain: the negative's vector (if it was not ready yet) and the output rows ----
+        while (!okG) {
+            __nanosleep(64);
+            okG = try_load(recG, k, lane, false, p.seq0 + static_cast<uint32_t>(pG), G, curG);
+            if ((++spins & 0xff) == 0) {
+                if (*reinterpret_cast<volatile int32_t *>(p.status) != 0) break;
+                if (spins > (1u << 22)) { atomicExch(p.status, 1); break; }
+            }
+        }
+        if (!okG) continue;
+        if (!sigG && neg_own && (flags & kFlagSignal) && lane == 0) atomicAdd(rcnt + gN, 1);
 
         if (p.rows_per_edge >= 2) {
             int64_t row = p.i_offset + i, nrow = p.n_total;
@@ -387,28 +501,7 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
             obase += static_cast<size_t>(j) * plane * 16;
             emit_row(p, obase, plane, row, S, t, lane);
             emit_row(p, obase, plane, row + nrow, D, t, lane);
-            if (has_neg) {
-                if (neg_own) {
-                    const VecR G = load_vec(table + static_cast<size_t>(gN) * p.stride, k, lane);
-                    emit_row(p, obase, plane, row + 2 * nrow, G, t, lane);
-                    __threadfence();               // the read of G is complete before it is released
-                    __syncwarp();
-                    if (lane == 0) atomicAdd(done + gN, 1u);
-                } else {
-                    emit_row(p, obase, plane, row + 2 * nrow, gN == sN ? S : D, t, lane);
-                }
-            }
-        }
-
-        const double alpha = p.alpha[j], beta = p.beta[j];
-        update_endpoint(p, s, S, D, dN, e, t, alpha, beta, recS, lane);
-        if (!loop) update_endpoint(p, s, D, S, sN, e, t, alpha, beta, recD, lane);
-
-        __threadfence();
-        __syncwarp();
-        if (lane == 0) {
-            atomicAdd(done + sN, 1u);
-            if (!loop) atomicAdd(done + dN, 1u);
+            if (has_neg) emit_row(p, obase, plane, row + 2 * nrow, neg_own ? G : (gN == sN ? S : D), t, lane);
         }
     }
 }
@@ -422,15 +515,28 @@ __global__ void tppr_read_state_kernel(const char *table, int32_t stride, int32_
     const char *rec = table + static_cast<size_t>(ids[a]) * stride;
     int l = threadIdx.x;
     if (l < k) {
-        int2 kk = reinterpret_cast<const int2 *>(rec)[l];
-        eidx[a * k + l] = kk.x; node[a * k + l] = kk.y;
-        ts[a * k + l] = reinterpret_cast<const double *>(rec + 8 * k)[l];
-        score[a * k + l] = reinterpret_cast<const double *>(rec + 16 * k)[l];
+        const uint4 ca = *reinterpret_cast<const uint4 *>(rec + 16 + 16 * l);
+        const uint4 cb = *reinterpret_cast<const uint4 *>(rec + 16 + 16 * (k + l));
+        eidx[a * k + l] = static_cast<int32_t>(ca.z); node[a * k + l] = static_cast<int32_t>(cb.z);
+        ts[a * k + l] = chunk_f64(cb);
+        score[a * k + l] = chunk_f64(ca);
     }
     if (l == 0) {
-        norm[a] = *reinterpret_cast<const double *>(rec + 24 * k);
-        counts[a] = *reinterpret_cast<const int *>(rec + 24 * k + 8);
+        const uint4 h = *reinterpret_cast<const uint4 *>(rec);
+        norm[a] = chunk_f64(h);
+        counts[a] = static_cast<int32_t>(h.z);
     }
+}
+
+// Sets every tag of a table to zero (used when the 32-bit edge sequence wraps).
+__global__ void tppr_retag_kernel(char *table, int32_t stride, int32_t k, int64_t num_nodes)
+{
+    const int64_t idx = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const int per = 2 * k + 1;
+    const int64_t node = idx / per;
+    if (node >= num_nodes) return;
+    const int c = static_cast<int>(idx - node * per);
+    *reinterpret_cast<uint32_t *>(table + static_cast<size_t>(node) * stride + 16 * c + 12) = 0u;
 }
 
 }  // namespace zebra
