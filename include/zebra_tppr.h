@@ -127,6 +127,10 @@ int zebra_tppr_sync_check(zebra_tppr_t *h, void *stream);
  * the exact tie path, [2] kernel launches so far on this handle, [3] spin time-outs (must be 0). */
 int zebra_tppr_counters(zebra_tppr_t *h, int64_t *out4);
 
+/* Developer builds (-DZEBRA_PROFILE) accumulate clock64 cycles per kernel phase; this reads and
+ * clears the 16 sums (all zero in a normal build).  Synchronises the device. */
+int zebra_tppr_profile(zebra_tppr_t *h, uint64_t *out16);
+
 /* Device time of the last span kernel(s) in milliseconds (CUDA events on `stream`); -1 if none. */
 double zebra_tppr_last_kernel_ms(zebra_tppr_t *h);
 

@@ -42,24 +42,31 @@ def bulk(name, n_edges=None):
         dt = time.perf_counter() - t
         print(f"{name} bulk update-only E={E}: {E/dt/1e6:.2f} M edges/s wall, kernel-span {f.last_kernel_ms():.1f} ms -> {E/f.last_kernel_ms()/1e3:.2f} M edges/s, GB/s alg={E*2*1976/f.last_kernel_ms()/1e6:.1f} {f.counters()}", flush=True)
 
-def star(n_edges=100000, n_nodes=200000):
+def star(n_edges=100000, n_nodes=200000, pool=None, insts=((1, [0.1], [0.5]), (1, [0.1], [0.95]), (2, [0.1, 0.1], [0.5, 0.95]))):
     """Every edge touches node 1: throughput = 1 / (latency of one step of a hub chain)."""
     rng = np.random.default_rng(0)
     src = np.ones(n_edges, np.int64)
-    dst = rng.integers(2, n_nodes, n_edges).astype(np.int64)
+    dst = rng.integers(2, pool or n_nodes, n_edges).astype(np.int64)
     ts = np.arange(n_edges, dtype=np.float64)
     eidx = np.arange(1, n_edges + 1, dtype=np.int64)
-    for n_t, al, be in ((1, [0.1], [0.5]), (1, [0.1], [0.95]), (2, [0.1, 0.1], [0.5, 0.95])):
+    for n_t, al, be in insts:
         f = tppr_finder(n_nodes, 20, n_t, al, be)
         f.compute_val_tppr(src[:1000], dst[:1000], ts[:1000], eidx[:1000])
         f.reset_tppr()
         f.compute_val_tppr(src, dst, ts, eidx)
         ms = f.last_kernel_ms()
-        print(f"star chain n_tppr={n_t} beta={be}: {ms*1e3/n_edges:.2f} us per hub step ({n_edges/ms/1e3:.2f} M edges/s) {f.counters()}", flush=True)
+        pr = f.profile()
+        if pr.any():
+            names = ["claim+load", "wait", "upd_hot", "upd_2nd", "emit", "", "", "", "u.dup", "u.pos", "u.rank", "u.tie", "u.store"]
+            print("   cycles/item:", {nm: round(float(v) / (n_edges * n_t), 1) for nm, v in zip(names, pr) if nm})
+        print(f"star chain pool={pool} n_tppr={n_t} beta={be}: {ms*1e3/n_edges:.2f} us per hub step ({n_edges/ms/1e3:.2f} M edges/s) {f.counters()}", flush=True)
 
 
 if __name__ == "__main__":
-    star()
+    star(insts=((1, [0.1], [0.5]), (1, [0.1], [0.95])))
+    star(pool=2000, insts=((1, [0.1], [0.5]), (1, [0.1], [0.95])))
+    if os.environ.get("ZEBRA_TPPR_LIB") or "--star" in sys.argv:
+        sys.exit(0)
     per_batch("wikipedia", 157474)
     per_batch("reddit", 200000)
     per_batch("wikitalk", 400000)

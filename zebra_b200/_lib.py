@@ -28,6 +28,7 @@ SIGNATURES = {
     "zebra_tppr_read_state": (C.c_int, [_VP, _I32, _VP, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "zebra_tppr_sync_check": (C.c_int, [_VP, _VP]),
     "zebra_tppr_counters": (C.c_int, [_VP, _VP]),
+    "zebra_tppr_profile": (C.c_int, [_VP, _VP]),
     "zebra_tppr_last_kernel_ms": (_D, [_VP]),
     "zebra_last_error": (C.c_char_p, []),
     "zebra_build_info": (C.c_char_p, []),
@@ -37,7 +38,7 @@ SIGNATURES = {
 def lib():
     global _lib
     if _lib is None:
-        so = _build.SO
+        so = os.environ.get("ZEBRA_TPPR_LIB") or _build.SO     # developer override (e.g. the -DZEBRA_PROFILE build)
         if not os.path.exists(so):
             so = _build.build()
         L = C.CDLL(so)

@@ -58,10 +58,13 @@ struct zebra_tppr {
     std::vector<int32_t> lastw, rhead, rnext; // host scratch of the dependency pass (all -1 between passes)
     std::vector<uint32_t> rcount;             // host scratch: negative reads of a node since its last write
     uint32_t epoch = 0;                       // tag epoch the bound tables were last written in
+    zebra::DecayStep *decay[zebra::kMaxInst] = {};   // device: update factors by update count
+    int32_t decay_len[zebra::kMaxInst] = {}, decay_fixed[zebra::kMaxInst] = {};
     uint32_t *ticket = nullptr;
     uint32_t ticket_base = 0;
     int32_t *status = nullptr;                // device [4]
     int32_t *status_host = nullptr;           // pinned [4]
+    unsigned long long *prof = nullptr;       // device [16] phase cycle sums (ZEBRA_PROFILE builds only)
     Staging stg[2];
     int stg_next = 0;
     char *out_dev = nullptr;
@@ -241,8 +244,9 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
         p.tables[j] = h->tables[j];
         p.rcnt[j] = h->rcnt + static_cast<size_t>(j) * h->num_nodes;
         p.alpha[j] = h->alpha[j]; p.beta[j] = h->beta[j];
+        p.decay[j] = h->decay[j]; p.decay_len[j] = h->decay_len[j]; p.decay_fixed[j] = h->decay_fixed[j];
     }
-    p.out = out; p.ticket = h->ticket; p.status = h->status;
+    p.out = out; p.ticket = h->ticket; p.status = h->status; p.prof = h->prof;
     p.batch_size = bo.batch_size; p.first_batch = bo.first_batch; p.out_slots = bo.out_slots; p.slot_bytes = bo.slot_bytes;
     const int64_t items = m * h->n_tppr;
     int blocks = static_cast<int>(std::min<int64_t>((items + zebra::kWarpsPerBlock - 1) / zebra::kWarpsPerBlock, h->max_blocks));
@@ -338,11 +342,31 @@ int zebra_tppr_create(zebra_tppr_t **out, int64_t num_nodes, int32_t k, int32_t 
     CU(cudaMalloc(&h->rcnt, sizeof(int32_t) * num_nodes * n_tppr));
     CU(cudaMemset(h->rcnt, 0, sizeof(int32_t) * num_nodes * n_tppr));
     { std::lock_guard<std::mutex> lk(g_seq_mu); h->epoch = g_epoch; }
+    for (int j = 0; j < n_tppr; ++j) {
+        // tabulate the norm recurrence up to its floating-point fixed point (or a cap; beyond a capped
+        // table the kernel divides as the reference does)
+        constexpr int kCap = 1 << 16;
+        std::vector<zebra::DecayStep> tab;
+        double norm = 0.0;
+        int fixed = 0;
+        while (static_cast<int>(tab.size()) < kCap) {
+            const zebra::DecayStep d = zebra::decay_step(norm, h->alpha[j], h->beta[j]);
+            tab.push_back(d);
+            if (d.new_norm == norm) { fixed = 1; break; }
+            norm = d.new_norm;
+        }
+        h->decay_len[j] = static_cast<int32_t>(tab.size());
+        h->decay_fixed[j] = fixed;
+        CU(cudaMalloc(&h->decay[j], tab.size() * sizeof(zebra::DecayStep)));
+        CU(cudaMemcpy(h->decay[j], tab.data(), tab.size() * sizeof(zebra::DecayStep), cudaMemcpyHostToDevice));
+    }
     CU(cudaMalloc(&h->ticket, sizeof(uint32_t)));
     CU(cudaMemset(h->ticket, 0, sizeof(uint32_t)));
     CU(cudaMalloc(&h->status, 4 * sizeof(int32_t)));
     CU(cudaMemset(h->status, 0, 4 * sizeof(int32_t)));
     CU(cudaMallocHost(&h->status_host, 4 * sizeof(int32_t)));
+    CU(cudaMalloc(&h->prof, 16 * sizeof(unsigned long long)));
+    CU(cudaMemset(h->prof, 0, 16 * sizeof(unsigned long long)));
     CU(cudaEventCreate(&h->ev0));
     CU(cudaEventCreate(&h->ev1));
     int per_sm = 0, sms = 0;
@@ -364,9 +388,11 @@ int zebra_tppr_destroy(zebra_tppr_t *h)
         if (s.free_ev) cudaEventDestroy(s.free_ev);
     }
     if (h->rcnt) cudaFree(h->rcnt);
+    for (auto d : h->decay) if (d) cudaFree(d);
     if (h->ticket) cudaFree(h->ticket);
     if (h->status) cudaFree(h->status);
     if (h->status_host) cudaFreeHost(h->status_host);
+    if (h->prof) cudaFree(h->prof);
     if (h->out_dev) cudaFree(h->out_dev);
     if (h->out_pinned) cudaFreeHost(h->out_pinned);
     if (h->ev0) cudaEventDestroy(h->ev0);
@@ -587,6 +613,16 @@ int zebra_tppr_counters(zebra_tppr_t *h, int64_t *out4)
 {
     if (!h || !out4) return fail("null argument");
     out4[0] = h->last_items; out4[1] = h->last_ties; out4[2] = h->launches; out4[3] = h->timeouts;
+    return 0;
+}
+
+int zebra_tppr_profile(zebra_tppr_t *h, uint64_t *out16)
+{
+    if (!h || !out16) return fail("null argument");
+    CU(cudaSetDevice(h->device));
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(out16, h->prof, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    CU(cudaMemset(h->prof, 0, 16 * sizeof(unsigned long long)));
     return 0;
 }
 

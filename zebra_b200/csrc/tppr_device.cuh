@@ -21,6 +21,17 @@
 
 namespace zebra {
 
+#ifndef ZEBRA_ABLATE
+#define ZEBRA_ABLATE 0   // developer timing builds only: bit 0 no duplicate scan, bit 1 no rank loop, bit 2 no tie path
+#endif
+#ifdef ZEBRA_PROFILE
+#define ZP_DECL long long zp_t0 = clock64(), zp_t1
+#define ZP_MARK(slot) do { zp_t1 = clock64(); if (lane == 0) atomicAdd(reinterpret_cast<unsigned long long *>(p.prof) + (slot), static_cast<unsigned long long>(zp_t1 - zp_t0)); zp_t0 = zp_t1; } while (0)
+#else
+#define ZP_DECL
+#define ZP_MARK(slot)
+#endif
+
 constexpr int kMaxInst = 8;
 constexpr int kWarpsPerBlock = 8;
 constexpr unsigned kFull = 0xffffffffu;
@@ -31,6 +42,31 @@ constexpr uint32_t kNear = 192;          // edges: closer than this to our turn 
 __host__ __device__ inline size_t record_stride(int k) { return (static_cast<size_t>(32) * k + 16 + 127) / 128 * 128; }
 
 enum : uint32_t { kFlagSignal = 1u, kFlagDstFirst = 2u };
+
+// The norm of a node depends only on how many updates it has seen (norm <- norm*beta + beta,
+// utils/util.py:522,574), so the factors of its next update are tabulated per update count instead
+// of being divided out on the dependency chain.  Entry m serves the update that takes a node from m
+// to m+1 updates; the recurrence reaches a floating-point fixed point, where the table ends.
+struct DecayStep { double new_norm, s1, s2, w_new; };
+constexpr int kCountBits = 6;            // header word: entries in use | update count << 6 (saturating)
+constexpr int kMaxUpdates = (1 << 26) - 1;
+
+__host__ __device__ inline DecayStep decay_step(double norm, double alpha, double beta)
+{
+    DecayStep d;
+#ifdef __CUDA_ARCH__
+    d.new_norm = __dadd_rn(__dmul_rn(norm, beta), beta);
+    d.s1 = __dmul_rn(__ddiv_rn(norm, d.new_norm), beta);
+    d.s2 = __dmul_rn(__ddiv_rn(beta, d.new_norm), __dsub_rn(1.0, alpha));
+    d.w_new = (alpha != 0.0) ? __dmul_rn(d.s2, alpha) : d.s2;
+#else
+    d.new_norm = norm * beta + beta;          // host build uses -ffp-contract=off: same roundings
+    d.s1 = norm / d.new_norm * beta;
+    d.s2 = beta / d.new_norm * (1.0 - alpha);
+    d.w_new = (alpha != 0.0) ? d.s2 * alpha : d.s2;
+#endif
+    return d;
+}
 
 struct SpanParams {
     int64_t n_chunk;        // edges in this launch
@@ -48,6 +84,9 @@ struct SpanParams {
     char *tables[kMaxInst];
     int32_t *rcnt[kMaxInst];                        // [num_nodes] completed-but-unconsumed negative reads
     double alpha[kMaxInst], beta[kMaxInst];
+    const DecayStep *decay[kMaxInst];               // per-instance table of update factors by update count
+    int32_t decay_len[kMaxInst];                    // entries; the last one is the fixed point if decay_fixed
+    int32_t decay_fixed[kMaxInst];
     char *out;              // [n_tppr][4][rows_total*k] 4-byte elements, or nullptr
     // batch-structured output (plan mode): batch_size > 0 => edge g = i_offset + i belongs to batch
     // b = g / batch_size and its rows go to slot (b - first_batch) % out_slots of `out`, laid out
@@ -55,22 +94,35 @@ struct SpanParams {
     int64_t batch_size, first_batch, out_slots, slot_bytes;
     uint32_t *ticket;
     int32_t *status;        // [0] spin time-out flag, [1] exact-tie prunes (statistics)
+    unsigned long long *prof;   // [8] cycle sums per phase (ZEBRA_PROFILE builds)
 };
 
-struct WarpScratch {
-    unsigned long long V[64];   // candidate scores (fp64 bit patterns; non-negative => integer order)
-    unsigned char R[64];        // position -> candidate (numba quicksort working permutation)
+struct alignas(16) WarpScratch {
+    unsigned long long V[64];   // candidate scores by candidate index (fp64 bit patterns in integer order)
+    unsigned long long W[64];   // the same by sort position (numba quicksort working array)
+    unsigned long long K[32];   // peer keys of the duplicate scan
+    unsigned long long XV[32], YV[32];   // swap exchange: values
+    unsigned char R[64];        // position -> candidate (working permutation)
     unsigned char P[64];        // candidate -> position
-    unsigned char X[32], Y[32]; // swap exchange
-    unsigned char stk[16];      // (low, high) stack
+    unsigned char XI[32], YI[32];        // swap exchange: candidates
 };
 
 struct VecR {
     int e, n;        // key parts 0,1 of this lane's entry
     double ts, sc;   // key part 2, value
     int cnt;         // entries in use
+    int upd;         // updates seen (saturating)
     double norm;
 };
+
+// field-wise select: keeps the vectors in registers (a reference chosen at run time would not)
+__device__ __forceinline__ VecR vsel(bool c, const VecR &a, const VecR &b)
+{
+    VecR r;
+    r.e = c ? a.e : b.e; r.n = c ? a.n : b.n; r.ts = c ? a.ts : b.ts; r.sc = c ? a.sc : b.sc;
+    r.cnt = c ? a.cnt : b.cnt; r.upd = c ? a.upd : b.upd; r.norm = c ? a.norm : b.norm;
+    return r;
+}
 
 __device__ __forceinline__ uint4 ld_chunk(const char *p)
 {
@@ -109,11 +161,11 @@ __device__ __forceinline__ bool try_load(const char *rec, int k, int lane, bool 
     const uint4 b = ld_chunk(rec + 16 + 16 * (k + l));
     cur = h.w;
     const uint32_t want = any ? h.w : expect;
-    const int cnt = static_cast<int>(h.z);
+    const int cnt = static_cast<int>(h.z & ((1u << kCountBits) - 1));
     const bool ok = h.w == want && (lane >= cnt || (a.w == want && b.w == want));
     v.sc = chunk_f64(a); v.e = static_cast<int>(a.z);
     v.ts = chunk_f64(b); v.n = static_cast<int>(b.z);
-    v.norm = chunk_f64(h); v.cnt = cnt;
+    v.norm = chunk_f64(h); v.cnt = cnt; v.upd = static_cast<int>(h.z >> kCountBits);
     return __all_sync(kFull, ok);
 }
 
@@ -151,24 +203,25 @@ __device__ __forceinline__ void emit_row(const SpanParams &p, char *base, size_t
     reinterpret_cast<float *>(base + plane * 12)[o] = w;
 }
 // One partition step of numba.misc.quicksort (median of three, pivot stashed at `high`, Hoare
-// scan) on the permutation R over values V, computed warp-wide from two stopper bitmaps instead
-// of a sequential scan.  Returns the pivot's final position.
+// scan) on positions [low, high] of the working permutation: R[p] = candidate at position p,
+// W[p] = its value.  Computed warp-wide from two stopper bitmaps instead of a sequential scan;
+// two warp barriers and three shared-memory latencies per step.  Returns the pivot's position.
 __device__ __forceinline__ int qs_partition(WarpScratch &s, int low, int high, int lane)
 {
-    int mid = (low + high) >> 1;
+    const int mid = (low + high) >> 1;
+    const int p0 = lane, p1 = lane + 32;
     int rl = s.R[low], rm = s.R[mid], rh = s.R[high];
-    unsigned long long vl = s.V[rl], vm = s.V[rm], vh = s.V[rh];
+    unsigned long long vl = s.W[low], vm = s.W[mid], vh = s.W[high];
+    int r0 = s.R[p0], r1 = s.R[p1];
+    unsigned long long v0 = s.W[p0], v1 = s.W[p1];
     if (vm < vl) { int t = rl; rl = rm; rm = t; unsigned long long u = vl; vl = vm; vm = u; }
     if (vh < vm) { int t = rh; rh = rm; rm = t; unsigned long long u = vh; vh = vm; vm = u; }
     if (vm < vl) { int t = rl; rl = rm; rm = t; unsigned long long u = vl; vl = vm; vm = u; }
     const unsigned long long pivot = vm;
-    __syncwarp();
-    if (lane == 0) { s.R[low] = rl; s.R[mid] = rh; s.R[high] = rm; }
-    __syncwarp();
-    const int p0 = lane, p1 = lane + 32;
+    // what the scan sees: low <- smallest, mid <- largest, high <- pivot (excluded from the scan)
+    if (p0 == low) { r0 = rl; v0 = vl; } else if (p0 == mid) { r0 = rh; v0 = vh; }
+    if (p1 == low) { r1 = rl; v1 = vl; } else if (p1 == mid) { r1 = rh; v1 = vh; }
     const bool in0 = p0 >= low && p0 < high, in1 = p1 >= low && p1 < high;
-    const int r0 = s.R[p0], r1 = s.R[p1];
-    const unsigned long long v0 = s.V[r0 & 63], v1 = s.V[r1 & 63];
     const bool L0 = in0 && !(v0 < pivot), L1 = in1 && !(v1 < pivot);   // i stops here
     const bool Q0 = in0 && !(pivot < v0), Q1 = in1 && !(pivot < v1);   // j stops here
     const unsigned long long Lm = __ballot_sync(kFull, L0) | (static_cast<unsigned long long>(__ballot_sync(kFull, L1)) << 32);
@@ -177,62 +230,71 @@ __device__ __forceinline__ int qs_partition(WarpScratch &s, int low, int high, i
     const int qa0 = __popcll(Qm >> (p0 + 1)), qa1 = (p1 == 63) ? 0 : __popcll(Qm >> (p1 + 1));
     const bool swL0 = L0 && qa0 > lb0, swL1 = L1 && qa1 > lb1;
     const bool swQ0 = Q0 && lb0 > qa0, swQ1 = Q1 && lb1 > qa1;
-    if (swL0) s.X[lb0] = r0;
-    if (swL1) s.X[lb1] = r1;
-    if (swQ0) s.Y[qa0] = r0;
-    if (swQ1) s.Y[qa1] = r1;
+    if (swL0) { s.XI[lb0] = r0; s.XV[lb0] = v0; }
+    if (swL1) { s.XI[lb1] = r1; s.XV[lb1] = v1; }
+    if (swQ0) { s.YI[qa0] = r0; s.YV[qa0] = v0; }
+    if (swQ1) { s.YI[qa1] = r1; s.YV[qa1] = v1; }
     const int M = __popc(__ballot_sync(kFull, swL0)) + __popc(__ballot_sync(kFull, swL1));
-    __syncwarp();
-    if (swL0) s.R[p0] = s.Y[lb0];
-    if (swL1) s.R[p1] = s.Y[lb1];
-    if (swQ0) s.R[p0] = s.X[qa0];
-    if (swQ1) s.R[p1] = s.X[qa1];
     // first unswapped left stopper (rank M) and the last swapped right stopper (rank M-1)
     const unsigned long long lM = __ballot_sync(kFull, L0 && lb0 == M) |
                                   (static_cast<unsigned long long>(__ballot_sync(kFull, L1 && lb1 == M)) << 32);
     const unsigned long long qM = __ballot_sync(kFull, Q0 && qa0 == M - 1) |
                                   (static_cast<unsigned long long>(__ballot_sync(kFull, Q1 && qa1 == M - 1)) << 32);
-    int bound = (M > 0 && qM) ? (__ffsll(static_cast<long long>(qM)) - 1) : high;
+    const int bound = (M > 0 && qM) ? (__ffsll(static_cast<long long>(qM)) - 1) : high;
     int i = lM ? (__ffsll(static_cast<long long>(lM)) - 1) : 64;
     if (bound < i) i = bound;
     __syncwarp();
-    if (lane == 0) { unsigned char t = s.R[i]; s.R[i] = s.R[high]; s.R[high] = t; }
+    if (swL0) { r0 = s.YI[lb0]; v0 = s.YV[lb0]; }
+    if (swL1) { r1 = s.YI[lb1]; v1 = s.YV[lb1]; }
+    if (swQ0) { r0 = s.XI[qa0]; v0 = s.XV[qa0]; }
+    if (swQ1) { r1 = s.XI[qa1]; v1 = s.XV[qa1]; }
+    // the pivot lands on i, the element that was there moves to `high`
+    if (in0) {
+        if (p0 == i) { s.R[high] = r0; s.W[high] = v0; s.R[p0] = rm; s.W[p0] = pivot; }
+        else { s.R[p0] = r0; s.W[p0] = v0; }
+    } else if (p0 == high && i == high) { s.R[p0] = rm; s.W[p0] = pivot; }
+    if (in1) {
+        if (p1 == i) { s.R[high] = r1; s.W[high] = v1; s.R[p1] = rm; s.W[p1] = pivot; }
+        else { s.R[p1] = r1; s.W[p1] = v1; }
+    } else if (p1 == high && i == high) { s.R[p1] = rm; s.W[p1] = pivot; }
     __syncwarp();
     return i;
 }
 
-// Runs the partition phase of numba's argsort on n candidates; afterwards a stable sort of the
-// permuted sequence equals numba's final order (its insertion sort on segments < 16 is stable).
+// Runs the partition phase of numba's argsort on the n candidates in V; afterwards a stable sort of
+// the permuted sequence (R, W) equals numba's final order (its insertion sort on segments < 16 is
+// stable).  Leaves P[candidate] = position.
 __device__ __forceinline__ void qs_partition_phase(WarpScratch &s, int n, int lane)
 {
-    if (lane < n) s.R[lane] = lane;
-    if (lane + 32 < n) s.R[lane + 32] = lane + 32;
-    else s.R[lane + 32] = 0;
+    s.R[lane] = lane; s.R[lane + 32] = lane + 32;
+    s.W[lane] = s.V[lane]; s.W[lane + 32] = s.V[lane + 32];
     __syncwarp();
-    int sp = 0;
+    // pending (low, high) ranges, packed low<<8|high; numba pushes the larger side, so with n <= 63
+    // and ranges shorter than 16 never pushed-and-split again more than twice, four slots suffice
+    int sp = 0, k0 = 0, k1 = 0, k2 = 0, k3 = 0;
     int low = 0, high = n - 1;
     for (;;) {
         while (high - low >= 15) {
-            int i = qs_partition(s, low, high, lane);
+            const int i = qs_partition(s, low, high, lane);
+            int push = -1;
             if (high - i > i - low) {
-                if (high > i) { if (lane == 0) { s.stk[2 * sp] = i + 1; s.stk[2 * sp + 1] = high; } ++sp; }
+                if (high > i) push = ((i + 1) << 8) | high;
                 high = i - 1;
             } else {
-                if (i > low) { if (lane == 0) { s.stk[2 * sp] = low; s.stk[2 * sp + 1] = i - 1; } ++sp; }
+                if (i > low) push = (low << 8) | (i - 1);
                 low = i + 1;
             }
+            if (push >= 0) { k3 = k2; k2 = k1; k1 = k0; k0 = push; ++sp; }
         }
         if (sp == 0) break;
         --sp;
-        __syncwarp();
-        low = s.stk[2 * sp]; high = s.stk[2 * sp + 1];
+        low = k0 >> 8; high = k0 & 0xff;
+        k0 = k1; k1 = k2; k2 = k3;
     }
-    __syncwarp();
     if (lane < n) s.P[s.R[lane]] = lane;
     if (lane + 32 < n) s.P[s.R[lane + 32]] = lane + 32;
     __syncwarp();
 }
-
 
 __device__ __forceinline__ void st_entry(char *rec, int k, int pos, int e, int n, double ts, double sc, uint32_t tag)
 {
@@ -243,58 +305,72 @@ __device__ __forceinline__ void st_entry(char *rec, int k, int pos, int e, int n
 // New vector of one endpoint from the OLD vectors of itself (A) and its peer (B)
 // (utils/util.py:509-559), written straight into the endpoint's record with tag `tag`.
 // `rwait` > 0: that many negative-sample reads of the old version must have finished first.
+// This function is the step of every hub's dependency chain: it is written for the latency of a
+// single warp (independent shared-memory loads, unrolled compare loops), not for throughput.
 __device__ __forceinline__ bool update_endpoint(const SpanParams &p, WarpScratch &s, const VecR &A, const VecR &B,
-                                                int peer_id, int e_new, double t_new, double alpha, double beta,
+                                                int peer_id, int e_new, double t_new, int j,
                                                 char *rec, uint32_t tag, int32_t *rcnt, uint32_t rwait, int lane)
 {
+    ZP_DECL;
     const int k = p.k;
     const int c1 = A.cnt;
     const int c2 = (B.norm != 0.0) ? B.cnt : 0;
-    const double new_norm = __dadd_rn(__dmul_rn(A.norm, beta), beta);
-    const double s1c = __dmul_rn(__ddiv_rn(A.norm, new_norm), beta);
-    const double s2c = __dmul_rn(__ddiv_rn(beta, new_norm), __dsub_rn(1.0, alpha));
+    DecayStep ds;
+    {
+        const int len = p.decay_len[j];
+        int m = A.upd;
+        if (m >= len && p.decay_fixed[j]) m = len - 1;
+        if (m < len) {
+            const double2 *t2 = reinterpret_cast<const double2 *>(p.decay[j] + m);
+            const double2 x = __ldg(t2), y = __ldg(t2 + 1);
+            ds.new_norm = x.x; ds.s1 = x.y; ds.s2 = y.x; ds.w_new = y.y;
+        } else {
+            ds = decay_step(A.norm, p.alpha[j], p.beta[j]);
+        }
+    }
+    const double new_norm = ds.new_norm, s1c = ds.s1, s2c = ds.s2;
     double vA = __dmul_rn(A.sc, s1c);
     double vB = __dmul_rn(B.sc, s2c);
     const unsigned long long keyA = pack_key(A.e, A.n), keyB = pack_key(B.e, B.n);
 
-    // ---- duplicate keys between A and B: all-pairs equality through match.any ----
-    bool dupB = false;
-    const int chunk = 32 - c1;
-    const unsigned ownmask = c1 ? (kFull >> (32 - c1)) : 0u;
-    for (int base = 0; c1 > 0 && base < c2; base += chunk) {
-        const int srcl = base + lane - c1;
-        const bool present = lane >= c1 && srcl < c2;
-        const int sl = present ? srcl : lane;
-        const unsigned long long pk = __shfl_sync(kFull, keyB, sl);
-        const double pts = __shfl_sync(kFull, B.ts, sl);
-        const double padd = __shfl_sync(kFull, vB, sl);
-        const unsigned long long mykey = lane < c1 ? keyA : (present ? pk : pack_key(-1 - lane, -1));
-        const double myts = lane < c1 ? A.ts : pts;
-        const unsigned m = __match_any_sync(kFull, mykey);
-        unsigned cand = lane < c1 ? (m & ~ownmask) : (present ? (m & ownmask) : 0u);
-        int partner = -1;
+    // ---- duplicate keys between A and B: every A lane scans the peer's keys in shared memory ----
+    unsigned dupmask = 0;          // peer entries whose key A already holds
+    if (c1 > 0 && c2 > 0 && !(ZEBRA_ABLATE & 1)) {
+        __syncwarp();
+        s.K[lane] = lane < c2 ? keyB : 0xffffffffffffffffull;   // (eidx -1, node -1) never occurs
+        __syncwarp();
+        unsigned cand = 0;
+        const ulonglong2 *K2 = reinterpret_cast<const ulonglong2 *>(s.K);
+#pragma unroll 4
+        for (int q = 0; q < (c2 + 1) >> 1; ++q) {
+            const ulonglong2 kk = K2[q];
+            cand |= (kk.x == keyA ? 1u : 0u) << (2 * q);
+            cand |= (kk.y == keyA ? 1u : 0u) << (2 * q + 1);
+        }
+        if (lane >= c1) cand = 0;
+        // keys are (eidx, node, ts): confirm the timestamp of the (rare) candidates
+        int hit = -1;
         while (__any_sync(kFull, cand != 0)) {
-            const int t = cand ? (__ffs(cand) - 1) : lane;
-            const double ots = __shfl_sync(kFull, myts, t);
+            const int t = cand ? (__ffs(cand) - 1) : 0;
+            const double ots = __shfl_sync(kFull, B.ts, t);
             if (cand) {
-                if (ots == myts) { partner = t; cand = 0; }
+                if (ots == A.ts) { hit = t; cand = 0; }
                 else cand &= cand - 1;
             }
         }
-        const double got = __shfl_sync(kFull, padd, partner >= 0 ? partner : lane);
-        if (lane < c1 && partner >= 0) vA = __dadd_rn(vA, got);
-        const bool inround = lane >= base && lane < base + chunk && lane < c2;
-        const int pf = __shfl_sync(kFull, partner, inround ? (c1 + lane - base) : lane);
-        if (inround && pf >= 0) dupB = true;
+        const double got = __shfl_sync(kFull, vB, hit >= 0 ? hit : 0);
+        if (hit >= 0) vA = __dadd_rn(vA, got);
+        dupmask = __reduce_or_sync(kFull, hit >= 0 ? (1u << hit) : 0u);
     }
+    ZP_MARK(8);
 
     // ---- insertion-order positions: A's entries, then B's new keys, then the new key ----
-    const bool ndB = lane < c2 && !dupB;
+    const bool ndB = lane < c2 && !((dupmask >> lane) & 1u);
     const unsigned ndmask = __ballot_sync(kFull, ndB);
     int n = c1 + __popc(ndmask);
     int pos1 = c1 + __popc(ndmask & ((1u << lane) - 1));
     const unsigned long long keyN = pack_key(e_new, peer_id);
-    const double w_new = (alpha != 0.0) ? __dmul_rn(s2c, alpha) : s2c;
+    const double w_new = ds.w_new;
     const bool hitA = lane < c1 && keyA == keyN && A.ts == t_new;
     const bool hitB = ndB && keyB == keyN && B.ts == t_new;
     const bool replaced = __any_sync(kFull, hitA || hitB);
@@ -311,6 +387,7 @@ __device__ __forceinline__ bool update_endpoint(const SpanParams &p, WarpScratch
     const bool valid0 = lane < c1;
     int pos0 = lane;
     bool keep0 = valid0, keep1 = valid1;
+    ZP_MARK(9);
 
     if (n > k) {
         // ---- keep the k largest, re-inserted in ascending order (util.py:553-559) ----
@@ -319,31 +396,41 @@ __device__ __forceinline__ bool update_endpoint(const SpanParams &p, WarpScratch
         __syncwarp();
         if (valid0) s.V[lane] = b0;
         if (valid1) s.V[pos1] = b1;
+        if (lane == 0) s.V[n] = 0xffffffffffffffffull;   // pair loads may touch one filler: above every score
         __syncwarp();
+        // rank = number of candidates strictly below; equal scores share a rank, which shows up as
+        // a hole in the set of occupied ranks
         int r0 = 0, r1 = 0;
-        bool eq0 = false, eq1 = false;
-        for (int q = 0; q < n; ++q) {
-            const unsigned long long vq = s.V[q];
-            r0 += (vq < b0) || (vq == b0 && q < lane);
-            r1 += (vq < b1) || (vq == b1 && q < pos1);
-            eq0 |= vq == b0 && q != lane;
-            eq1 |= vq == b1 && q != pos1;
+        const ulonglong2 *V2 = reinterpret_cast<const ulonglong2 *>(s.V);
+#pragma unroll 4
+        for (int q = 0; q < (((ZEBRA_ABLATE & 2) ? 0 : n + 1) >> 1); ++q) {
+            const ulonglong2 vv = V2[q];
+            r0 += vv.x < b0; r1 += vv.x < b1;
+            r0 += vv.y < b0; r1 += vv.y < b1;
         }
         const int cut = n - k;
-        // a tie only matters if one of the tied candidates survives under the stable order: then
-        // the survivor set or its slot order depends on numba's (unstable) argsort
-        if (__any_sync(kFull, (valid0 && eq0 && r0 >= cut) || (valid1 && eq1 && r1 >= cut))) {
+        if (ZEBRA_ABLATE & 2) { r0 = lane; r1 = pos1; }
+        const unsigned long long mine = (valid0 ? 1ull << r0 : 0ull) | (valid1 ? 1ull << r1 : 0ull);
+        const unsigned long long occ = __reduce_or_sync(kFull, static_cast<unsigned>(mine)) |
+                                       (static_cast<unsigned long long>(__reduce_or_sync(kFull, static_cast<unsigned>(mine >> 32))) << 32);
+        ZP_MARK(10);
+        // a group of equal scores only matters if it can reach the surviving ranks [cut, n): then the
+        // survivor set or its slot order depends on numba's (unstable) argsort
+        const unsigned long long surv = ((1ull << k) - 1) << cut;
+        if ((occ & surv) != surv && !(ZEBRA_ABLATE & 4)) {
             qs_partition_phase(s, n, lane);
+            // rank among equals = order of their positions after the partition phase
             const int P0 = valid0 ? s.P[lane] : 0, P1 = valid1 ? s.P[pos1] : 0;
-            r0 = 0; r1 = 0;
-            for (int q = 0; q < n; ++q) {
-                const unsigned long long vq = s.V[q];
-                const int Pq = s.P[q];
-                r0 += (vq < b0) || (vq == b0 && Pq < P0);
-                r1 += (vq < b1) || (vq == b1 && Pq < P1);
+            const ulonglong2 *W2 = reinterpret_cast<const ulonglong2 *>(s.W);
+#pragma unroll 4
+            for (int q = 0; q < (n + 1) >> 1; ++q) {
+                const ulonglong2 ww = W2[q];
+                r0 += (ww.x == b0) && (2 * q < P0); r1 += (ww.x == b1) && (2 * q < P1);
+                r0 += (ww.y == b0) && (2 * q + 1 < P0); r1 += (ww.y == b1) && (2 * q + 1 < P1);
             }
             if (lane == 0) atomicAdd(p.status + 1, 1);
         }
+        ZP_MARK(11);
         keep0 = valid0 && r0 >= cut; pos0 = r0 - cut;
         keep1 = valid1 && r1 >= cut; pos1 = r1 - cut;
         n = k;
@@ -364,7 +451,9 @@ __device__ __forceinline__ bool update_endpoint(const SpanParams &p, WarpScratch
     if (keep0) st_entry(rec, k, pos0, A.e, A.n, A.ts, vA, tag);
     if (keep1) st_entry(rec, k, pos1, e1, n1, ts1, v1, tag);
     __syncwarp();
-    if (lane == 0) st_chunk(rec, new_norm, n, tag);
+    const int upd = A.upd < kMaxUpdates ? A.upd + 1 : kMaxUpdates;
+    if (lane == 0) st_chunk(rec, new_norm, n | (upd << kCountBits), tag);
+    ZP_MARK(12);
     return ok;
 }
 
@@ -390,6 +479,7 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
         if (lane == 0) tk = atomicAdd(p.ticket, 1u) - p.ticket_base;
         tk = __shfl_sync(kFull, tk, 0);
         if (tk >= total) break;
+        ZP_DECL;
         const int64_t i = tk / p.n_tppr;
         const int j = tk - i * p.n_tppr;
         const int sN = p.src[i], dN = p.dst[i];
@@ -417,6 +507,7 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
         bool okG = neg_own ? try_load(recG, k, lane, pG < 0, p.seq0 + static_cast<uint32_t>(pG), G, curG) : true;
         bool alive = true;
         unsigned spins = 0;
+        ZP_MARK(0);
         while (!(okS && okD)) {
             // distance (in edges) of the farther unsatisfied producer from the version visible now
             uint32_t dist = 0;
@@ -443,8 +534,6 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
                     }
                     continue;
                 }
-            } else {
-                __nanosleep(32);
             }
             if (!okS) okS = try_load(recS, k, lane, false, p.seq0 + static_cast<uint32_t>(pS), S, curS);
             if (!okD) okD = try_load(recD, k, lane, false, p.seq0 + static_cast<uint32_t>(pD), D, curD);
@@ -455,23 +544,27 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
             }
         }
         if (!alive) continue;
-        if (loop) D = S;
+        ZP_MARK(1);
+        if (loop) D = vsel(true, S, S);
+        if (!neg_own) G = vsel(gN == sN, S, D);    // a negative equal to an endpoint: its OLD vector
         if (okG && neg_own && (flags & kFlagSignal) && lane == 0) atomicAdd(rcnt + gN, 1);
         bool sigG = okG;
 
         const double t = p.ts[i];
         const int e = p.eidx[i];
-        const double alpha = p.alpha[j], beta = p.beta[j];
         const uint32_t rwS = p.rthr_s[i], rwD = loop ? 0u : p.rthr_d[i];
 
         // ---- the hotter endpoint first: its next writer is the one most likely to be waiting ----
+        // (one copy of the update code, run twice: the kernel is bound by instruction fetch otherwise)
+        const bool df = (flags & kFlagDstFirst) && !loop;
         bool ok = true;
-        if ((flags & kFlagDstFirst) && !loop) {
-            ok &= update_endpoint(p, s, D, S, sN, e, t, alpha, beta, recD, my_tag, rcnt + dN, rwD, lane);
-            ok &= update_endpoint(p, s, S, D, dN, e, t, alpha, beta, recS, my_tag, rcnt + sN, rwS, lane);
-        } else {
-            ok &= update_endpoint(p, s, S, D, dN, e, t, alpha, beta, recS, my_tag, rcnt + sN, rwS, lane);
-            if (!loop) ok &= update_endpoint(p, s, D, S, sN, e, t, alpha, beta, recD, my_tag, rcnt + dN, rwD, lane);
+#pragma unroll 1
+        for (int h = 0; h < (loop ? 1 : 2); ++h) {
+            const bool isD = (h == 0) ? df : !df;
+            const VecR A = vsel(isD, D, S), B = vsel(isD, S, D);
+            ok &= update_endpoint(p, s, A, B, isD ? sN : dN, e, t, j, isD ? recD : recS, my_tag,
+                                  rcnt + (isD ? dN : sN), isD ? rwD : rwS, lane);
+            ZP_MARK(2 + h);
         }
         if (!ok) { atomicExch(p.status, 1); continue; }
 
@@ -501,8 +594,9 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
             obase += static_cast<size_t>(j) * plane * 16;
             emit_row(p, obase, plane, row, S, t, lane);
             emit_row(p, obase, plane, row + nrow, D, t, lane);
-            if (has_neg) emit_row(p, obase, plane, row + 2 * nrow, neg_own ? G : (gN == sN ? S : D), t, lane);
+            if (has_neg) emit_row(p, obase, plane, row + 2 * nrow, G, t, lane);
         }
+        ZP_MARK(4);
     }
 }
 
@@ -524,7 +618,7 @@ __global__ void tppr_read_state_kernel(const char *table, int32_t stride, int32_
     if (l == 0) {
         const uint4 h = *reinterpret_cast<const uint4 *>(rec);
         norm[a] = chunk_f64(h);
-        counts[a] = static_cast<int32_t>(h.z);
+        counts[a] = static_cast<int32_t>(h.z & ((1u << kCountBits) - 1));
     }
 }
 

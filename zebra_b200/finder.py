@@ -179,6 +179,11 @@ class tppr_finder:  # noqa: N801  (name kept from the reference)
         check(self._L.zebra_tppr_counters(self._h, _ptr(o)))
         return {"items": int(o[0]), "tie_prunes": int(o[1]), "launches": int(o[2]), "timeouts": int(o[3])}
 
+    def profile(self):
+        o = np.zeros(16, np.uint64)
+        check(self._L.zebra_tppr_profile(self._h, _ptr(o)))
+        return o
+
     def last_kernel_ms(self):
         return float(self._L.zebra_tppr_last_kernel_ms(self._h))
 
