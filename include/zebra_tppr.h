@@ -28,6 +28,7 @@ extern "C" {
 
 typedef struct zebra_tppr zebra_tppr_t;
 typedef struct zebra_plan zebra_plan_t;
+typedef struct zebra_csr zebra_csr_t;
 
 /* ---- lifetime: replaces tppr_finder.__init__ (utils/util.py:393-400) ------------------------ */
 
@@ -133,6 +134,34 @@ int zebra_tppr_profile(zebra_tppr_t *h, uint64_t *out16);
 
 /* Device time of the last span kernel(s) in milliseconds (CUDA events on `stream`); -1 if none. */
 double zebra_tppr_last_kernel_ms(zebra_tppr_t *h);
+
+/* ---- pruning strategy: replaces NeighborFinder / get_neighbor_finder / find_before /
+ *      get_pruned_topk (utils/util.py:90-107, 144-154, 185-276) and the loop over instances in
+ *      GraphDiffusionEmbedding.pruning_topk (modules/embedding_module.py:280-297) ----------------
+ *
+ * zebra_csr_create uploads the static time-sorted adjacency: node v's entries are
+ * [indptr[v], indptr[v+1]) of adj_node / adj_eidx / adj_ts, sorted by timestamp (stable), exactly
+ * the three per-node arrays the reference's NeighborFinder holds.  num_nodes = number of rows of
+ * indptr minus one.
+ *
+ * zebra_prune_topk answers nq independent queries (node, time): pruned power iteration of `depth`
+ * levels over the `width` most recent strictly-earlier neighbours, dictionary accumulation in the
+ * reference's order, top-k by the reference's argsort.  k <= 32.
+ *   host_q_nodes int32[nq], host_q_ts f64[nq]
+ *   output (zebra_prune_out_bytes(nq,k) bytes): int32 nodes[nq*k] | int32 eidx[nq*k] | f32 dt[nq*k]
+ *   | f32 w[nq*k] | int32 filled[nq].  filled[i] = 0 marks a query with no earlier neighbour, whose
+ *   row the reference leaves untouched in the caller's arrays (utils/util.py:241-242); its row here
+ *   is zero.  dev_out may be NULL (internal buffer); host_out non-NULL makes the call synchronous.
+ */
+int zebra_csr_create(zebra_csr_t **out, const int64_t *host_indptr, const int32_t *host_adj_node,
+                     const int32_t *host_adj_eidx, const double *host_adj_ts, int64_t num_nodes,
+                     int64_t nnz, int32_t device);
+int zebra_csr_destroy(zebra_csr_t *csr);
+size_t zebra_prune_out_bytes(int64_t nq, int32_t k);
+int zebra_prune_topk(zebra_csr_t *csr, const int32_t *host_q_nodes, const double *host_q_ts, int64_t nq,
+                     int32_t width, int32_t depth, double alpha, double beta, int32_t k,
+                     void *dev_out, void *host_out, void *stream);
+int64_t zebra_prune_launches(const zebra_csr_t *csr);
 
 const char *zebra_last_error(void);
 const char *zebra_build_info(void);

@@ -30,6 +30,11 @@ SIGNATURES = {
     "zebra_tppr_counters": (C.c_int, [_VP, _VP]),
     "zebra_tppr_profile": (C.c_int, [_VP, _VP]),
     "zebra_tppr_last_kernel_ms": (_D, [_VP]),
+    "zebra_csr_create": (C.c_int, [C.POINTER(_VP), _VP, _VP, _VP, _VP, _I64, _I64, _I32]),
+    "zebra_csr_destroy": (C.c_int, [_VP]),
+    "zebra_prune_out_bytes": (C.c_size_t, [_I64, _I32]),
+    "zebra_prune_topk": (C.c_int, [_VP, _VP, _VP, _I64, _I32, _I32, _D, _D, _I32, _VP, _VP, _VP]),
+    "zebra_prune_launches": (_I64, [_VP]),
     "zebra_last_error": (C.c_char_p, []),
     "zebra_build_info": (C.c_char_p, []),
 }

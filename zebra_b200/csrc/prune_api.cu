@@ -1,0 +1,169 @@
+// prune_api.cu — C ABI of the pruning-strategy query (include/zebra_tppr.h, "pruned top-k").
+// Host work: upload the time-sorted adjacency once, stage the queries, launch, copy back.
+#include "common.cuh"
+#include "prune_device.cuh"
+#include "../../include/zebra_tppr.h"
+
+#include <algorithm>
+#include <cstring>
+
+using zebra::fail;
+
+struct zebra_csr {
+    int64_t num_nodes = 0, nnz = 0;
+    int32_t device = 0;
+    int64_t *indptr = nullptr;
+    int32_t *adj_node = nullptr, *adj_eidx = nullptr;
+    double *adj_ts = nullptr;
+    char *q_dev = nullptr;          // staged queries
+    char *q_host = nullptr;         // pinned
+    size_t q_cap = 0;
+    char *out_dev = nullptr;
+    size_t out_cap = 0;
+    char *scratch = nullptr;
+    size_t scratch_cap = 0;
+    int sms = 0;
+    int64_t launches = 0;
+};
+
+extern "C" {
+
+int zebra_csr_create(zebra_csr_t **out, const int64_t *host_indptr, const int32_t *host_adj_node,
+                     const int32_t *host_adj_eidx, const double *host_adj_ts, int64_t num_nodes, int64_t nnz,
+                     int32_t device)
+{
+    if (!out) return fail("null out pointer");
+    *out = nullptr;
+    if (num_nodes <= 0 || nnz < 0 || !host_indptr) return fail("bad adjacency arguments");
+    if (nnz > 0 && (!host_adj_node || !host_adj_eidx || !host_adj_ts)) return fail("null adjacency arrays");
+    if (host_indptr[0] != 0 || host_indptr[num_nodes] != nnz) return fail("indptr does not span the adjacency arrays");
+    for (int64_t v = 0; v < num_nodes; ++v)
+        if (host_indptr[v + 1] < host_indptr[v]) return fail("indptr is not monotone at node %lld", (long long)v);
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail("no CUDA device: libzebra_tppr has no CPU path (%s)", e == cudaSuccess ? "0 devices" : cudaGetErrorString(e));
+    if (device < 0 || device >= ndev) return fail("device %d out of range", device);
+    CU(cudaSetDevice(device));
+    zebra_csr *c = new zebra_csr();
+    c->num_nodes = num_nodes; c->nnz = nnz; c->device = device;
+    const size_t n1 = static_cast<size_t>(std::max<int64_t>(nnz, 1));
+    CU(cudaMalloc(&c->indptr, sizeof(int64_t) * (num_nodes + 1)));
+    CU(cudaMalloc(&c->adj_node, sizeof(int32_t) * n1));
+    CU(cudaMalloc(&c->adj_eidx, sizeof(int32_t) * n1));
+    CU(cudaMalloc(&c->adj_ts, sizeof(double) * n1));
+    CU(cudaMemcpy(c->indptr, host_indptr, sizeof(int64_t) * (num_nodes + 1), cudaMemcpyHostToDevice));
+    if (nnz) {
+        CU(cudaMemcpy(c->adj_node, host_adj_node, sizeof(int32_t) * nnz, cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(c->adj_eidx, host_adj_eidx, sizeof(int32_t) * nnz, cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(c->adj_ts, host_adj_ts, sizeof(double) * nnz, cudaMemcpyHostToDevice));
+    }
+    CU(cudaDeviceGetAttribute(&c->sms, cudaDevAttrMultiProcessorCount, device));
+    *out = c;
+    return 0;
+}
+
+int zebra_csr_destroy(zebra_csr_t *c)
+{
+    if (!c) return 0;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    cudaFree(c->indptr); cudaFree(c->adj_node); cudaFree(c->adj_eidx); cudaFree(c->adj_ts);
+    if (c->q_dev) cudaFree(c->q_dev);
+    if (c->q_host) cudaFreeHost(c->q_host);
+    if (c->out_dev) cudaFree(c->out_dev);
+    if (c->scratch) cudaFree(c->scratch);
+    delete c;
+    return 0;
+}
+
+size_t zebra_prune_out_bytes(int64_t nq, int32_t k) { return static_cast<size_t>(nq) * k * 16 + static_cast<size_t>(nq) * 4; }
+
+int zebra_prune_topk(zebra_csr_t *c, const int32_t *host_q_nodes, const double *host_q_ts, int64_t nq, int32_t width,
+                     int32_t depth, double alpha, double beta, int32_t k, void *dev_out, void *host_out, void *stream)
+{
+    if (!c) return fail("null adjacency handle");
+    if (nq < 0) return fail("negative query count");
+    if (k < 1 || k > 32) return fail("k=%d unsupported by the pruning kernel (1 <= k <= 32: one output slot per lane)", k);
+    if (width < 1 || depth < 1) return fail("width and depth must be positive");
+    if (nq == 0) return 0;
+    if (!host_q_nodes || !host_q_ts) return fail("null query arrays");
+    int64_t t_max = 0, lvl = 1;
+    for (int d = 0; d < depth; ++d) {
+        lvl *= width;
+        t_max += lvl;
+        if (t_max > (1 << 22)) return fail("width=%d depth=%d visits up to %lld states per query: too many", width, depth, (long long)t_max);
+    }
+    for (int64_t i = 0; i < nq; ++i)
+        if (host_q_nodes[i] < 0 || host_q_nodes[i] >= c->num_nodes)
+            return fail("query node %d out of range at %lld (num_nodes=%lld)", host_q_nodes[i], (long long)i, (long long)c->num_nodes);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    CU(cudaSetDevice(c->device));
+    const size_t qbytes = static_cast<size_t>(nq) * 12;
+    if (c->q_cap < qbytes) {
+        CU(cudaStreamSynchronize(st));
+        if (c->q_dev) CU(cudaFree(c->q_dev));
+        if (c->q_host) CU(cudaFreeHost(c->q_host));
+        c->q_cap = std::max<size_t>(qbytes * 2, 1 << 16);
+        CU(cudaMalloc(&c->q_dev, c->q_cap));
+        CU(cudaMallocHost(&c->q_host, c->q_cap));
+    } else {
+        CU(cudaStreamSynchronize(st));      // the previous call's upload must have drained the pinned buffer
+    }
+    double *hq_ts = reinterpret_cast<double *>(c->q_host);
+    int32_t *hq_n = reinterpret_cast<int32_t *>(hq_ts + nq);
+    memcpy(hq_ts, host_q_ts, sizeof(double) * nq);
+    memcpy(hq_n, host_q_nodes, sizeof(int32_t) * nq);
+    CU(cudaMemcpyAsync(c->q_dev, c->q_host, qbytes, cudaMemcpyHostToDevice, st));
+    const size_t ob = zebra_prune_out_bytes(nq, k);
+    char *outp = static_cast<char *>(dev_out);
+    if (!outp) {
+        if (c->out_cap < ob) {
+            CU(cudaStreamSynchronize(st));
+            if (c->out_dev) CU(cudaFree(c->out_dev));
+            c->out_cap = ob * 2;
+            CU(cudaMalloc(&c->out_dev, c->out_cap));
+        }
+        outp = c->out_dev;
+    }
+    // grid: enough warps to cover the queries, at most 8 blocks of 8 warps per SM
+    const int warps_per_block = 8;
+    int64_t blocks = std::min<int64_t>((nq + warps_per_block - 1) / warps_per_block, static_cast<int64_t>(c->sms) * 8);
+    const size_t per_warp = zebra::prune_scratch_bytes(t_max);
+    // very wide/deep queries: bound the work area to 2 GB by running fewer warps
+    while (blocks > 1 && per_warp * warps_per_block * static_cast<size_t>(blocks) > (2ull << 30)) blocks = (blocks + 1) / 2;
+    const size_t need = per_warp * warps_per_block * static_cast<size_t>(blocks);
+    if (c->scratch_cap < need) {
+        CU(cudaStreamSynchronize(st));
+        if (c->scratch) CU(cudaFree(c->scratch));
+        CU(cudaMalloc(&c->scratch, need));
+        c->scratch_cap = need;
+    }
+    zebra::PruneParams p;
+    memset(&p, 0, sizeof p);
+    p.indptr = c->indptr; p.adj_node = c->adj_node; p.adj_eidx = c->adj_eidx; p.adj_ts = c->adj_ts;
+    p.q_ts = reinterpret_cast<const double *>(c->q_dev);
+    p.q_nodes = reinterpret_cast<const int32_t *>(p.q_ts + nq);
+    p.nq = nq; p.num_nodes = c->num_nodes;
+    p.width = width; p.depth = depth; p.k = k; p.t_max = static_cast<int32_t>(t_max);
+    p.alpha = alpha; p.beta = beta;
+    const size_t plane = static_cast<size_t>(nq) * k;
+    p.o_node = reinterpret_cast<int32_t *>(outp);
+    p.o_eidx = p.o_node + plane;
+    p.o_dt = reinterpret_cast<float *>(p.o_eidx + plane);
+    p.o_w = p.o_dt + plane;
+    p.o_filled = reinterpret_cast<int32_t *>(p.o_w + plane);
+    p.scratch = c->scratch; p.scratch_per_warp = per_warp;
+    zebra::prune_topk_kernel<<<static_cast<unsigned>(blocks), warps_per_block * 32, 0, st>>>(p);
+    CU(cudaGetLastError());
+    c->launches++;
+    if (host_out) {
+        CU(cudaMemcpyAsync(host_out, outp, ob, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+    }
+    return 0;
+}
+
+int64_t zebra_prune_launches(const zebra_csr_t *c) { return c ? c->launches : 0; }
+
+}  // extern "C"

@@ -4,6 +4,7 @@
 // thresholds (one pass, two uint32 per node), (b) staging the span through pinned memory and
 // (c) launching the persistent span kernel.  All T-PPR arithmetic runs on the GPU; there is no
 // CPU fallback: without a CUDA device every entry point fails with an error.
+#include "common.cuh"
 #include "tppr_device.cuh"
 #include "../../include/zebra_tppr.h"
 
@@ -17,10 +18,10 @@
 #include <vector>
 
 namespace {
-
 thread_local std::string g_err;
+}
 
-int fail(const char *fmt, ...)
+int zebra::fail(const char *fmt, ...)
 {
     char buf[512];
     va_list ap;
@@ -31,11 +32,9 @@ int fail(const char *fmt, ...)
     return 1;
 }
 
-#define CU(call)                                                                                   \
-    do {                                                                                           \
-        cudaError_t _e = (call);                                                                   \
-        if (_e != cudaSuccess) return fail("%s failed: %s (%s:%d)", #call, cudaGetErrorString(_e), __FILE__, __LINE__); \
-    } while (0)
+namespace {
+
+using zebra::fail;
 
 constexpr int64_t kChunk = 1 << 18;  // edges per launch of a long span
 

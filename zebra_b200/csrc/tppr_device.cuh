@@ -127,14 +127,14 @@ __device__ __forceinline__ VecR vsel(bool c, const VecR &a, const VecR &b)
 __device__ __forceinline__ uint4 ld_chunk(const char *p)
 {
     uint4 v;
-    asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
     return v;
 }
 
 __device__ __forceinline__ void st_chunk(char *p, double d, int i, uint32_t tag)
 {
     const unsigned long long b = static_cast<unsigned long long>(__double_as_longlong(d));
-    asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(static_cast<uint32_t>(b)),
+    asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(static_cast<uint32_t>(b)),
                  "r"(static_cast<uint32_t>(b >> 32)), "r"(i), "r"(tag) : "memory");
 }
 
