@@ -163,6 +163,33 @@ int zebra_prune_topk(zebra_csr_t *csr, const int32_t *host_q_nodes, const double
                      void *dev_out, void *host_out, void *stream);
 int64_t zebra_prune_launches(const zebra_csr_t *csr);
 
+/* ---- neighbour gather: replaces the gather / concat / weight-normalisation half of
+ *      GraphDiffusionEmbedding.compute_embedding_tppr_ensemble (modules/embedding_module.py:236-271)
+ *      and TimeEncode.forward (model/time_encoding.py:23-28) -----------------------------------------
+ *
+ * One launch for all instances of a batch.  dev_topk is the output buffer of zebra_tppr_stream /
+ * zebra_tppr_plan_run for that batch ([n_tppr][4][rows*k] 4-byte planes: node, eidx, dt, w).
+ *   dev_x         f32 [n_tppr, rows*k, dim_mem+dim_edge+dim_time] = memory[node] | edge_feat[eidx] |
+ *                 cos(dt*time_w + time_b)               (torch.cat of :253,:257,:261 at :264)
+ *   dev_wn        f32 [n_tppr, rows, k] = w / sum_k w, zero where the sum is zero        (:268-271)
+ *   dev_src_rows  f32 [rows, dim_mem] = memory[dev_src_nodes] (:243-245), or both NULL
+ * The two nn.Linear projections and the weighted sum stay in torch (north_star).
+ * zebra_gather_bwd scatter-adds the memory-row part of the gradient (the only differentiable input:
+ * edge features and time encoder are frozen) into dev_gmemory [num_nodes, dim_mem].
+ * zebra_gather_check synchronises and reports an out-of-range id seen by any gather since the last
+ * check.  Everything else is asynchronous on `stream`.
+ */
+int zebra_gather_fwd(const void *dev_topk, int32_t n_tppr, int64_t rows, int32_t k, const float *dev_memory,
+                     int64_t num_nodes, int32_t dim_mem, const float *dev_edge_feat, int64_t n_edge_rows,
+                     int32_t dim_edge, const float *dev_time_w, const float *dev_time_b, int32_t dim_time,
+                     const int32_t *dev_src_nodes, float *dev_x, float *dev_wn, float *dev_src_rows,
+                     void *stream);
+int zebra_gather_bwd(const void *dev_topk, int32_t n_tppr, int64_t rows, int32_t k, const float *dev_gx,
+                     const float *dev_wn, const float *dev_gsrc, const int32_t *dev_src_nodes,
+                     float *dev_gmemory, int64_t num_nodes, int32_t dim_mem, int32_t dim_total,
+                     void *stream);
+int zebra_gather_check(void *stream);
+
 const char *zebra_last_error(void);
 const char *zebra_build_info(void);
 

@@ -39,3 +39,26 @@ def replay(finder, g):
         digs.append(digest([a for lst in out for a in lst]))
         outs[b] = [np.stack(x) for x in out]
     return np.stack(digs), outs
+
+
+EMBED_CASES = [("streaming", "wikipedia", 2400, 172), ("pruning", "mooc", 2400, 4), ("streaming", "su_small", 1200, 1)]
+
+
+def embedding_inputs(name, n_edges, d_e):
+    """Seeded inputs shared by tests/golden/make_golden_embedding.py (which feeds them to the reference
+    module) and the GPU parity test: stream, negatives, edge features [E+1,d_e], memory [N,100]."""
+    from zebra_b200 import synth
+    if name == "su_small":
+        st = synth.make_stream("superuser", n_edges=n_edges,
+                               shape=synth.StreamShape("su_small", 3000, 0, n_edges, 0, 30.0, 0.05, 0.3, 0.01))
+    else:
+        st = synth.make_stream(name, n_edges=n_edges)
+    neg = synth.make_negatives(st, 200)
+    N = st.shape.table_nodes
+    rng = np.random.default_rng(17)
+    ef = rng.standard_normal((n_edges + 1, d_e)).astype(np.float32)
+    ef[0] = 0
+    if d_e == 1:
+        ef[:] = 0                                   # the reference's zeros((E+1,1)) substitute (train.py:133-136)
+    memory = (rng.standard_normal((N, 100)) * 0.5).astype(np.float32)
+    return st, neg, N, ef, memory

@@ -1,0 +1,96 @@
+// gather_api.cu — C ABI of the fused neighbour gather (include/zebra_tppr.h, "neighbour gather").
+// Stateless: every pointer is caller-owned device memory; the call only enqueues kernels on `stream`.
+#include "common.cuh"
+#include "gather_device.cuh"
+#include "../../include/zebra_tppr.h"
+
+#include <cstdint>
+#include <cstring>
+
+using zebra::fail;
+
+namespace {
+bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+int32_t *g_status = nullptr;      // one device word per process: sticky out-of-range flag
+int g_status_dev = -1;
+
+int ensure_status()
+{
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    if (g_status && g_status_dev == dev) return 0;
+    CU(cudaMalloc(&g_status, sizeof(int32_t)));
+    CU(cudaMemset(g_status, 0, sizeof(int32_t)));
+    g_status_dev = dev;
+    return 0;
+}
+}  // namespace
+
+extern "C" {
+
+int zebra_gather_fwd(const void *dev_topk, int32_t n_tppr, int64_t rows, int32_t k, const float *dev_memory,
+                     int64_t num_nodes, int32_t dim_mem, const float *dev_edge_feat, int64_t n_edge_rows,
+                     int32_t dim_edge, const float *dev_time_w, const float *dev_time_b, int32_t dim_time,
+                     const int32_t *dev_src_nodes, float *dev_x, float *dev_wn, float *dev_src_rows, void *stream)
+{
+    if (!dev_topk || !dev_memory || !dev_edge_feat || !dev_time_w || !dev_time_b || !dev_x || !dev_wn)
+        return fail("null device pointer");
+    if (n_tppr < 1 || rows < 0 || k < 1 || dim_mem < 1 || dim_edge < 1 || dim_time < 1) return fail("bad gather shape");
+    if ((dev_src_rows != nullptr) != (dev_src_nodes != nullptr)) return fail("src_nodes and src_rows go together");
+    if (rows == 0) return 0;
+    if (ensure_status()) return 1;
+    zebra::GatherParams p;
+    memset(&p, 0, sizeof p);
+    p.topk = static_cast<const char *>(dev_topk); p.n_tppr = n_tppr; p.k = k; p.R = rows;
+    p.memory = dev_memory; p.edge_feat = dev_edge_feat; p.time_w = dev_time_w; p.time_b = dev_time_b;
+    p.num_nodes = num_nodes; p.n_edge_rows = n_edge_rows; p.Dm = dim_mem; p.De = dim_edge; p.Dt = dim_time;
+    p.src_nodes = dev_src_nodes; p.X = dev_x; p.wn = dev_wn; p.src_rows = dev_src_rows; p.status = g_status;
+    const bool vec = dim_mem % 4 == 0 && dim_edge % 4 == 0 && dim_time % 4 == 0 && aligned16(dev_memory) &&
+                     aligned16(dev_edge_feat) && aligned16(dev_time_w) && aligned16(dev_time_b) && aligned16(dev_x) &&
+                     (!dev_src_rows || aligned16(dev_src_rows));
+    const int64_t warps = static_cast<int64_t>(n_tppr) * rows * k + (dev_src_rows ? rows : 0);
+    const unsigned blocks = static_cast<unsigned>((warps + 7) / 8);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (vec) zebra::gather_fwd_kernel<true><<<blocks, 256, 0, st>>>(p);
+    else zebra::gather_fwd_kernel<false><<<blocks, 256, 0, st>>>(p);
+    CU(cudaGetLastError());
+    return 0;
+}
+
+int zebra_gather_bwd(const void *dev_topk, int32_t n_tppr, int64_t rows, int32_t k, const float *dev_gx,
+                     const float *dev_wn, const float *dev_gsrc, const int32_t *dev_src_nodes, float *dev_gmemory,
+                     int64_t num_nodes, int32_t dim_mem, int32_t dim_total, void *stream)
+{
+    if (!dev_topk || !dev_gx || !dev_wn || !dev_gmemory) return fail("null device pointer");
+    if ((dev_gsrc != nullptr) != (dev_src_nodes != nullptr)) return fail("src_nodes and g_src go together");
+    if (rows == 0) return 0;
+    zebra::GatherBwdParams p;
+    memset(&p, 0, sizeof p);
+    p.topk = static_cast<const char *>(dev_topk); p.n_tppr = n_tppr; p.k = k; p.R = rows;
+    p.gX = dev_gx; p.wn = dev_wn; p.g_src = dev_gsrc; p.src_nodes = dev_src_nodes; p.g_memory = dev_gmemory;
+    p.num_nodes = num_nodes; p.Dm = dim_mem; p.D = dim_total;
+    const bool vec = dim_mem % 4 == 0 && dim_total % 4 == 0 && aligned16(dev_gx) && aligned16(dev_gmemory) &&
+                     (!dev_gsrc || aligned16(dev_gsrc));
+    const int64_t warps = static_cast<int64_t>(n_tppr) * rows * k + (dev_gsrc ? rows : 0);
+    const unsigned blocks = static_cast<unsigned>((warps + 7) / 8);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (vec) zebra::gather_bwd_kernel<true><<<blocks, 256, 0, st>>>(p);
+    else zebra::gather_bwd_kernel<false><<<blocks, 256, 0, st>>>(p);
+    CU(cudaGetLastError());
+    return 0;
+}
+
+int zebra_gather_check(void *stream)
+{
+    if (ensure_status()) return 1;
+    int32_t v = 0;
+    CU(cudaMemcpyAsync(&v, g_status, sizeof v, cudaMemcpyDeviceToHost, static_cast<cudaStream_t>(stream)));
+    CU(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+    if (v != 0) {
+        CU(cudaMemset(g_status, 0, sizeof(int32_t)));
+        return fail("neighbour gather: a node id or edge id was out of range (row skipped)");
+    }
+    return 0;
+}
+
+}  // extern "C"

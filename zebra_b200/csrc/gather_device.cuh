@@ -1,0 +1,150 @@
+// gather_device.cuh — fused PPR-weighted top-k neighbour gather (sm_100a).
+//
+// Replaces, for all (alpha,beta) instances of one batch and in ONE launch, the per-instance chain of
+// torch launches in LuckyLYM/Zebra modules/embedding_module.py:236-271:
+//     memory[nodes_0]                                  (:243-245)  -> src_rows [R, Dm]
+//     memory[selected_nodes]                           (:253)      \
+//     edge_features[selected_edge_idxs]                (:257)       > X [n_tppr, R*k, Dm+De+Dt]
+//     time_encoder(selected_delta_time) = cos(dt*w+b)  (:261, model/time_encoding.py:23-28)
+//     torch.cat(...)                                   (:264)      /
+//     weights / weights.sum(1), zero where the sum is 0 (:268-271) -> wn [n_tppr, R, k]
+// The ids / edge ids / dt / weights are read straight from the span kernel's output buffer
+// ([n_tppr][4][R*k] 4-byte planes), so nothing leaves the GPU between the T-PPR update and the
+// torch projections.  Pure HBM streaming: one warp per output row, 128-bit loads and stores.
+// cosf is the accurate libdevice routine (arguments reach 1e6 and more: no fast-math).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace zebra {
+
+struct GatherParams {
+    const char *topk;          // [n_tppr][4][R*k]: int32 node | int32 eidx | f32 dt | f32 w
+    int32_t n_tppr, k;
+    int64_t R;                 // rows per instance (3n or 2n)
+    const float *memory;       // [num_nodes, Dm]
+    const float *edge_feat;    // [n_edge_rows, De]
+    const float *time_w, *time_b;   // [Dt]
+    int64_t num_nodes, n_edge_rows;
+    int32_t Dm, De, Dt;
+    const int32_t *src_nodes;  // [R] or nullptr
+    float *X;                  // [n_tppr, R*k, Dm+De+Dt]
+    float *wn;                 // [n_tppr, R, k]
+    float *src_rows;           // [R, Dm] or nullptr
+    int32_t *status;           // [0] set to 1 on an out-of-range id (row skipped)
+};
+
+template <bool VEC>
+__device__ __forceinline__ void copy_row(float *dst, const float *src, int n, int lane)
+{
+    if (VEC) {
+        const float4 *s4 = reinterpret_cast<const float4 *>(src);
+        float4 *d4 = reinterpret_cast<float4 *>(dst);
+        for (int c = lane; c < (n >> 2); c += 32) d4[c] = __ldg(s4 + c);
+    } else {
+        for (int c = lane; c < n; c += 32) dst[c] = __ldg(src + c);
+    }
+}
+
+template <bool VEC>
+__global__ void __launch_bounds__(256)
+gather_fwd_kernel(const GatherParams p)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t slots = static_cast<int64_t>(p.n_tppr) * p.R * p.k;
+    const int64_t plane = p.R * p.k;
+    const int D = p.Dm + p.De + p.Dt;
+    if (warp < slots) {
+        const int64_t j = warp / plane, o = warp - j * plane;
+        const char *base = p.topk + static_cast<size_t>(j) * plane * 16;
+        const int node = reinterpret_cast<const int32_t *>(base)[o];
+        const int eidx = reinterpret_cast<const int32_t *>(base + plane * 4)[o];
+        const float dt = reinterpret_cast<const float *>(base + plane * 8)[o];
+        float *x = p.X + static_cast<size_t>(warp) * D;
+        if (node < 0 || node >= p.num_nodes || eidx < 0 || eidx >= p.n_edge_rows) {
+            if (lane == 0) atomicExch(p.status, 1);
+        } else {
+            copy_row<VEC>(x, p.memory + static_cast<size_t>(node) * p.Dm, p.Dm, lane);
+            copy_row<VEC>(x + p.Dm, p.edge_feat + static_cast<size_t>(eidx) * p.De, p.De, lane);
+            float *xt = x + p.Dm + p.De;
+            if (VEC) {
+                for (int c = lane; c < (p.Dt >> 2); c += 32) {
+                    const float4 w = __ldg(reinterpret_cast<const float4 *>(p.time_w) + c);
+                    const float4 b = __ldg(reinterpret_cast<const float4 *>(p.time_b) + c);
+                    float4 r;
+                    r.x = cosf(__fadd_rn(__fmul_rn(dt, w.x), b.x)); r.y = cosf(__fadd_rn(__fmul_rn(dt, w.y), b.y));
+                    r.z = cosf(__fadd_rn(__fmul_rn(dt, w.z), b.z)); r.w = cosf(__fadd_rn(__fmul_rn(dt, w.w), b.w));
+                    reinterpret_cast<float4 *>(xt)[c] = r;
+                }
+            } else {
+                for (int c = lane; c < p.Dt; c += 32)
+                    xt[c] = cosf(__fadd_rn(__fmul_rn(dt, __ldg(p.time_w + c)), __ldg(p.time_b + c)));
+            }
+        }
+        // normalised weights: the warp of slot 0 of each row handles the row's k weights
+        const int64_t row = o / p.k;
+        if (o - row * p.k == 0) {
+            const float *w = reinterpret_cast<const float *>(base + plane * 12) + row * p.k;
+            float *out = p.wn + static_cast<size_t>(j) * plane + row * p.k;
+            float s = 0.f;
+            for (int c = 0; c < p.k; ++c) s = __fadd_rn(s, w[c]);       // left-to-right fp32 sum
+            for (int c = lane; c < p.k; c += 32) out[c] = (s == 0.f) ? 0.f : __fdiv_rn(w[c], s);
+        }
+    } else if (p.src_rows && warp < slots + p.R) {
+        const int64_t r = warp - slots;
+        const int node = p.src_nodes[r];
+        if (node < 0 || node >= p.num_nodes) { if (lane == 0) atomicExch(p.status, 1); }
+        else copy_row<VEC>(p.src_rows + static_cast<size_t>(r) * p.Dm, p.memory + static_cast<size_t>(node) * p.Dm, p.Dm, lane);
+    }
+}
+
+struct GatherBwdParams {
+    const char *topk;
+    int32_t n_tppr, k;
+    int64_t R;
+    const float *gX;           // [n_tppr, R*k, D] gradient of X (only the first Dm columns are used)
+    const float *wn;           // normalised weights: slots with weight 0 receive an exactly-zero gradient
+    const float *g_src;        // [R, Dm] or nullptr
+    const int32_t *src_nodes;
+    float *g_memory;           // [num_nodes, Dm], accumulated into
+    int64_t num_nodes;
+    int32_t Dm, D;
+};
+
+// Backward of the memory-row gathers (edge features and the time encoder are constants,
+// model/tgn_model.py:41, model/time_encoding.py:18-23): scatter-add rows of gX into g_memory.
+template <bool VEC>
+__global__ void __launch_bounds__(256)
+gather_bwd_kernel(const GatherBwdParams p)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t plane = p.R * p.k;
+    const int64_t slots = static_cast<int64_t>(p.n_tppr) * plane;
+    const float *g;
+    int node;
+    if (warp < slots) {
+        const int64_t j = warp / plane, o = warp - j * plane;
+        if (p.wn[warp] == 0.f) return;
+        node = reinterpret_cast<const int32_t *>(p.topk + static_cast<size_t>(j) * plane * 16)[o];
+        g = p.gX + static_cast<size_t>(warp) * p.D;
+    } else if (p.g_src && warp < slots + p.R) {
+        node = p.src_nodes[warp - slots];
+        g = p.g_src + static_cast<size_t>(warp - slots) * p.Dm;
+    } else {
+        return;
+    }
+    if (node < 0 || node >= p.num_nodes) return;
+    float *dst = p.g_memory + static_cast<size_t>(node) * p.Dm;
+    if (VEC) {
+        for (int c = lane; c < (p.Dm >> 2); c += 32) {
+            const float4 v = __ldg(reinterpret_cast<const float4 *>(g) + c);
+            asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dst + 4 * c), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+        }
+    } else {
+        for (int c = lane; c < p.Dm; c += 32) atomicAdd(dst + c, __ldg(g + c));
+    }
+}
+
+}  // namespace zebra

@@ -92,7 +92,7 @@ class tppr_finder:  # noqa: N801  (name kept from the reference)
     def _stream_ptr(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
-    def _run(self, source_nodes, timestamps, edge_idxs, rows_per_edge, inst, to_host):
+    def _launch(self, source_nodes, timestamps, edge_idxs, rows_per_edge, inst, to_host):
         nodes = np.ascontiguousarray(source_nodes, dtype=np.int32)
         ts = np.ascontiguousarray(timestamps, dtype=np.float64)
         eidx = np.ascontiguousarray(edge_idxs, dtype=np.int64)
@@ -110,6 +110,16 @@ class tppr_finder:  # noqa: N801  (name kept from the reference)
         with torch.cuda.device(self.device):
             check(self._L.zebra_tppr_stream(self._h, _ptr(nodes), _ptr(ts), _ptr(eidx), n, rows_per_edge, inst,
                                             _ptr(dev_out) if nbytes else None, _ptr(host), self._stream_ptr()))
+        return dev_out, host, rows, nbytes
+
+    def streaming_topk_raw(self, source_nodes, timestamps, edge_idxs, rows_per_edge=3):
+        """The span kernel's output left on the GPU as one uint8 buffer laid out [n_tppr][4][rows*k]
+        (int32 node | int32 eidx | f32 dt | f32 w): the input of the fused gather.  Asynchronous."""
+        dev_out, _, rows, _ = self._launch(source_nodes, timestamps, edge_idxs, rows_per_edge, -1, False)
+        return dev_out, rows
+
+    def _run(self, source_nodes, timestamps, edge_idxs, rows_per_edge, inst, to_host):
+        dev_out, host, rows, nbytes = self._launch(source_nodes, timestamps, edge_idxs, rows_per_edge, inst, to_host)
         plane = rows * self.k
         if to_host:
             buf = host.numpy()[:nbytes] if nbytes else np.zeros(0, np.uint8)
