@@ -175,15 +175,23 @@ def edge_features(stream: Stream, seed: int = 11) -> np.ndarray:
     return f
 
 
-def write_ml_format(stream: Stream, data_root: str, name: str | None = None) -> str:
-    """Write `{data_root}/{name}/ml_{name}.csv|.npy` as the reference loader expects."""
+def write_ml_format(stream: Stream, data_root: str, name: str | None = None, compact: bool = True) -> str:
+    """Write `{data_root}/{name}/ml_{name}.csv|.npy` as the reference loader expects.
+
+    The reference sizes its tables by the NUMBER of distinct node ids
+    (/root/reference/utils/data_processing.py:97-99, train.py:124), i.e. it assumes ids 1..n without
+    holes as its preprocessing produces; `compact` relabels the ids that occur, order-preserving."""
     name = name or stream.shape.name
     d = os.path.join(data_root, name)
     os.makedirs(d, exist_ok=True)
     E = stream.n_edges
+    src, dst = stream.src, stream.dst
+    if compact:
+        ids, inv = np.unique(np.concatenate([src, dst]), return_inverse=True)
+        src, dst = inv[:E] + 1, inv[E:] + 1
     with open(os.path.join(d, f"ml_{name}.csv"), "w") as fh:
         fh.write(",u,i,ts,label,idx\n")
-        rows = np.column_stack([np.arange(E), stream.src, stream.dst])
+        rows = np.column_stack([np.arange(E), src, dst])
         for r, t, e in zip(rows, stream.ts, stream.eidx):
             fh.write(f"{r[0]},{r[1]},{r[2]},{t},0,{e}\n")
     if stream.shape.edge_dim > 0:
