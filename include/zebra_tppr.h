@@ -28,6 +28,7 @@ extern "C" {
 
 typedef struct zebra_tppr zebra_tppr_t;
 typedef struct zebra_plan zebra_plan_t;
+typedef struct zebra_epoch zebra_epoch_t;
 typedef struct zebra_csr zebra_csr_t;
 
 /* ---- lifetime: replaces tppr_finder.__init__ (utils/util.py:393-400) ------------------------ */
@@ -38,8 +39,10 @@ int zebra_tppr_create(zebra_tppr_t **out, int64_t num_nodes, int32_t k, int32_t 
 int zebra_tppr_destroy(zebra_tppr_t *h);
 
 /* Bytes of ONE instance's table (num_nodes fixed-size records) and of one record.  Record
- * layout (little endian): { int32 eidx, int32 node }[k] | f64 ts[k] | f64 score[k] | f64 norm |
- * int32 count | pad to a multiple of 128 B.  A zero-filled table is the empty state. */
+ * layout (little endian, 16-byte chunks each ending in a 32-bit version tag):
+ * { f64 norm, int32 count|updates<<6, u32 tag } | { f64 score, int32 eidx, u32 tag }[k] |
+ * { f64 ts, int32 node, u32 tag }[k] | pad to a multiple of 128 B.  A zero-filled table is the
+ * empty state.  Read it with zebra_tppr_read_state rather than by hand. */
 size_t zebra_tppr_table_bytes(const zebra_tppr_t *h);
 size_t zebra_tppr_record_bytes(const zebra_tppr_t *h);
 
@@ -111,6 +114,34 @@ int zebra_tppr_plan_destroy(zebra_plan_t *plan);
 int64_t zebra_tppr_plan_batches(const zebra_plan_t *plan);
 int zebra_tppr_plan_run(zebra_tppr_t *h, zebra_plan_t *plan, int64_t first_batch, int64_t n_batches,
                         int64_t batches_per_launch, void *dev_out, int64_t out_slots, void *stream);
+
+/* ---- pipelined epochs: the train / validation / test loops of train.py:196-236 and
+ *      evaluation/evaluation.py:17-33 call streaming_topk once per batch of a span that is known
+ *      in full before the loop starts (the data split and the seeded negative sampler,
+ *      utils/util.py:69-86).  An epoch takes that span from HOST memory, cuts it into windows of
+ *      `batches_per_window` whole batches and pipelines, window by window: dependency pass on the
+ *      host, host->device copy of the edge records, span kernel, device->host copy of the rows into
+ *      pinned memory (second stream).  Two to three windows are in flight at any time.
+ *
+ *   epoch_begin   the five input arrays must stay valid until epoch_end.  Stages and launches the
+ *                 first two windows, returns immediately.
+ *   epoch_next    blocks until the next window's rows are in host memory and returns them:
+ *                 *host_rows -> *n_batches consecutive slots of zebra_tppr_epoch_slot_bytes() bytes,
+ *                 slot q = batch *first_batch + q in the per-batch layout of zebra_tppr_stream
+ *                 (identical bytes to calling zebra_tppr_stream once per batch).  The memory belongs
+ *                 to the library and is valid until the NEXT epoch_next / epoch_end call on the
+ *                 handle.  *n_batches = 0 marks the end.  rows_per_edge = 0: *host_rows is NULL.
+ *   epoch_end     waits for everything in flight and releases the epoch (the ring stays cached in
+ *                 the handle for the next epoch).
+ */
+int zebra_tppr_epoch_begin(zebra_tppr_t *h, const int32_t *host_src, const int32_t *host_dst,
+                           const int32_t *host_neg, const double *host_ts, const int64_t *host_eidx,
+                           int64_t n, int32_t rows_per_edge, int64_t batch_size,
+                           int64_t batches_per_window, void *stream, zebra_epoch_t **out);
+int zebra_tppr_epoch_next(zebra_epoch_t *epoch, void **host_rows, int64_t *first_batch,
+                          int64_t *n_batches);
+int zebra_tppr_epoch_end(zebra_epoch_t *epoch);
+int64_t zebra_tppr_epoch_slot_bytes(const zebra_epoch_t *epoch);
 
 /* Debug / test access: copy the vectors of `n_ids` nodes of instance `inst` to host arrays
  * (counts int32[n_ids], eidx int32[n_ids*k], node int32[n_ids*k], ts f64[n_ids*k],

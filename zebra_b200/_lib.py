@@ -25,6 +25,10 @@ SIGNATURES = {
     "zebra_tppr_plan_destroy": (C.c_int, [_VP]),
     "zebra_tppr_plan_batches": (_I64, [_VP]),
     "zebra_tppr_plan_run": (C.c_int, [_VP, _VP, _I64, _I64, _I64, _VP, _I64, _VP]),
+    "zebra_tppr_epoch_begin": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _I64, _I32, _I64, _I64, _VP, C.POINTER(_VP)]),
+    "zebra_tppr_epoch_next": (C.c_int, [_VP, C.POINTER(_VP), C.POINTER(_I64), C.POINTER(_I64)]),
+    "zebra_tppr_epoch_end": (C.c_int, [_VP]),
+    "zebra_tppr_epoch_slot_bytes": (_I64, [_VP]),
     "zebra_tppr_read_state": (C.c_int, [_VP, _I32, _VP, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "zebra_tppr_sync_check": (C.c_int, [_VP, _VP]),
     "zebra_tppr_counters": (C.c_int, [_VP, _VP]),

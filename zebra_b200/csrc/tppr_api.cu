@@ -76,6 +76,17 @@ struct zebra_tppr {
     int64_t launches = 0, last_items = 0, last_ties = 0, timeouts = 0;
     struct zebra_plan *plan_active = nullptr;   // a plan is part-way through its batches
     int64_t plan_next = 0;
+    struct zebra_epoch *epoch_active = nullptr; // a pipelined epoch is part-way through its windows
+    // window ring of the pipelined epoch path, kept across epochs (pinned allocations are slow)
+    struct EpochSlot {
+        Staging stg;                 // edge records of the window (pinned + device)
+        char *out_dev = nullptr;     // rows of the window on the device
+        char *out_host = nullptr;    // the same in pinned host memory
+        size_t out_cap = 0;
+        cudaEvent_t ev_kernel = nullptr, ev_copy = nullptr;
+        bool copy_pending = false;
+    } eslot[3];
+    cudaStream_t copy_stream = nullptr;
 };
 
 // A span prepared once and kept resident in HBM (edge records + dependency thresholds).
@@ -86,6 +97,21 @@ struct zebra_plan {
     char *dev = nullptr;
     size_t cap = 0;
     uint32_t seq0 = 0;                          // tag base of the run in progress
+};
+
+// A pipelined pass over a host-resident span: windows of whole batches are staged, computed and
+// copied back through a ring of three slots; the caller consumes window after window from pinned
+// host memory while later windows are in flight.
+struct zebra_epoch {
+    zebra_tppr *h = nullptr;
+    const int32_t *src = nullptr, *dst = nullptr, *neg = nullptr;   // caller memory, must outlive the epoch
+    const double *ts = nullptr;
+    const int64_t *eidx = nullptr;
+    int64_t n = 0, batch_size = 0, n_batches = 0, window = 0, n_windows = 0;
+    int32_t rows_per_edge = 0;
+    size_t slot_bytes = 0;          // one batch's rows
+    int64_t issued = 0, consumed = 0;
+    cudaStream_t st = nullptr;
 };
 
 namespace {
@@ -291,7 +317,7 @@ int run_span(zebra_tppr *h, const NodeT *src, const NodeT *dst, const NodeT *neg
 {
     for (int j = 0; j < h->n_tppr; ++j)
         if (!h->tables[j]) return fail("zebra_tppr_bind_tables has not been called");
-    if (h->plan_active) return fail("a plan is part-way through its batches; finish it before streaming other spans");
+    if (h->plan_active || h->epoch_active) return fail("a plan or epoch is part-way through its batches; finish it before streaming other spans");
     CU(cudaSetDevice(h->device));
     CU(cudaMemsetAsync(h->status + 1, 0, 3 * sizeof(int32_t), st));   // [0] (time-out) is sticky
     h->last_items = 0;
@@ -386,6 +412,16 @@ int zebra_tppr_destroy(zebra_tppr_t *h)
         if (s.dev) cudaFree(s.dev);
         if (s.free_ev) cudaEventDestroy(s.free_ev);
     }
+    for (auto &sl : h->eslot) {
+        if (sl.stg.host) cudaFreeHost(sl.stg.host);
+        if (sl.stg.dev) cudaFree(sl.stg.dev);
+        if (sl.stg.free_ev) cudaEventDestroy(sl.stg.free_ev);
+        if (sl.out_dev) cudaFree(sl.out_dev);
+        if (sl.out_host) cudaFreeHost(sl.out_host);
+        if (sl.ev_kernel) cudaEventDestroy(sl.ev_kernel);
+        if (sl.ev_copy) cudaEventDestroy(sl.ev_copy);
+    }
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->rcnt) cudaFree(h->rcnt);
     for (auto d : h->decay) if (d) cudaFree(d);
     if (h->ticket) cudaFree(h->ticket);
@@ -601,6 +637,141 @@ int zebra_tppr_plan_run(zebra_tppr_t *h, zebra_plan_t *pl, int64_t first_batch, 
     if (last == pl->n_batches) h->plan_active = nullptr;
     return 0;
 }
+
+/* ---- pipelined epoch ---- */
+
+static int epoch_issue(zebra_epoch *ep)
+{
+    zebra_tppr *h = ep->h;
+    const int64_t w = ep->issued;
+    zebra_tppr::EpochSlot &sl = h->eslot[w % 3];
+    const int64_t b0 = w * ep->window, b1 = std::min(ep->n_batches, b0 + ep->window);
+    const int64_t lo = b0 * ep->batch_size, hi = std::min(ep->n, b1 * ep->batch_size);
+    const int64_t m = hi - lo;
+    // the slot's previous window (w-3) has been handed to the caller and released, so its copy is done
+    if (sl.copy_pending) { CU(cudaEventSynchronize(sl.ev_copy)); sl.copy_pending = false; }
+    if (ensure_staging(h, sl.stg, static_cast<size_t>(ep->window * ep->batch_size) + 8)) return 1;
+    const size_t ob = static_cast<size_t>(ep->window) * ep->slot_bytes;
+    if (sl.out_cap < ob) {
+        if (sl.out_dev) CU(cudaFree(sl.out_dev));
+        if (sl.out_host) CU(cudaFreeHost(sl.out_host));
+        sl.out_dev = nullptr; sl.out_host = nullptr; sl.out_cap = 0;
+        if (ob) {
+            CU(cudaMalloc(&sl.out_dev, ob));
+            CU(cudaMallocHost(&sl.out_host, ob));
+        }
+        sl.out_cap = ob;
+    }
+    if (!sl.ev_kernel) {
+        CU(cudaEventCreateWithFlags(&sl.ev_kernel, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&sl.ev_copy, cudaEventDisableTiming));
+    }
+    const size_t cap = (static_cast<size_t>(m) + 7) & ~static_cast<size_t>(7);
+    if (fill_soa<int32_t>(h, sl.stg.host, cap, ep->src + lo, ep->dst + lo, ep->neg ? ep->neg + lo : nullptr, ep->ts + lo,
+                          ep->eidx + lo, m)) return 1;
+    uint32_t seq0 = 0;
+    if (alloc_seq(h, m, ep->st, &seq0)) return 1;
+    CU(cudaMemcpyAsync(sl.stg.dev, sl.stg.host, cap * kEdgeBytes, cudaMemcpyHostToDevice, ep->st));
+    if (w == 0) CU(cudaEventRecord(h->ev0, ep->st));
+    BatchOut bo;
+    bo.batch_size = ep->batch_size; bo.first_batch = b0; bo.out_slots = ep->window;
+    bo.slot_bytes = static_cast<int64_t>(ep->slot_bytes);
+    if (launch_kernel(h, sl.stg.dev, cap, 0, m, ep->n, lo, ep->rows_per_edge, (1 << h->n_tppr) - 1, sl.out_dev, bo, seq0, 0,
+                      ep->st)) return 1;
+    CU(cudaEventRecord(sl.ev_kernel, ep->st));
+    if (ep->rows_per_edge) {
+        CU(cudaStreamWaitEvent(h->copy_stream, sl.ev_kernel, 0));
+        CU(cudaMemcpyAsync(sl.out_host, sl.out_dev, static_cast<size_t>(b1 - b0) * ep->slot_bytes, cudaMemcpyDeviceToHost,
+                           h->copy_stream));
+        CU(cudaEventRecord(sl.ev_copy, h->copy_stream));
+        // no stream-side wait: this slot is staged again only after the caller has taken the window,
+        // i.e. after the host has synchronised on ev_copy
+    } else {
+        CU(cudaEventRecord(sl.ev_copy, ep->st));
+    }
+    sl.copy_pending = true;
+    if (w + 1 == ep->n_windows) { CU(cudaEventRecord(h->ev1, ep->st)); h->timed = true; }
+    ep->issued = w + 1;
+    return 0;
+}
+
+int zebra_tppr_epoch_begin(zebra_tppr_t *h, const int32_t *host_src, const int32_t *host_dst, const int32_t *host_neg,
+                           const double *host_ts, const int64_t *host_eidx, int64_t n, int32_t rows_per_edge,
+                           int64_t batch_size, int64_t batches_per_window, void *stream, zebra_epoch_t **out)
+{
+    if (!h || !out) return fail("null argument");
+    *out = nullptr;
+    if (n <= 0 || batch_size <= 0 || batches_per_window <= 0) return fail("epoch needs n, batch_size, batches_per_window > 0");
+    if (rows_per_edge != 0 && rows_per_edge != 2 && rows_per_edge != 3) return fail("rows_per_edge must be 0, 2 or 3");
+    if (!host_src || !host_dst || !host_ts || !host_eidx || (rows_per_edge == 3 && !host_neg)) return fail("null input");
+    if (batch_size * batches_per_window > (1 << 22)) return fail("window too long (max 2^22 edges)");
+    for (int j = 0; j < h->n_tppr; ++j)
+        if (!h->tables[j]) return fail("zebra_tppr_bind_tables has not been called");
+    if (h->plan_active || h->epoch_active) return fail("another plan or epoch is in progress on this handle");
+    CU(cudaSetDevice(h->device));
+    if (!h->copy_stream) CU(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    zebra_epoch *ep = new zebra_epoch();
+    ep->h = h; ep->src = host_src; ep->dst = host_dst; ep->neg = rows_per_edge == 3 ? host_neg : nullptr;
+    ep->ts = host_ts; ep->eidx = host_eidx; ep->n = n; ep->batch_size = batch_size; ep->rows_per_edge = rows_per_edge;
+    ep->n_batches = (n + batch_size - 1) / batch_size;
+    ep->window = std::min(batches_per_window, ep->n_batches);
+    ep->n_windows = (ep->n_batches + ep->window - 1) / ep->window;
+    ep->slot_bytes = zebra_tppr_out_bytes(h, batch_size, rows_per_edge);
+    ep->st = static_cast<cudaStream_t>(stream);
+    CU(cudaMemsetAsync(h->status + 1, 0, 3 * sizeof(int32_t), ep->st));
+    h->last_items = 0;
+    h->epoch_active = ep;
+    // two windows in flight before the caller asks for the first
+    for (int q = 0; q < 2 && ep->issued < ep->n_windows; ++q)
+        if (epoch_issue(ep)) { h->epoch_active = nullptr; delete ep; return 1; }
+    *out = ep;
+    return 0;
+}
+
+int zebra_tppr_epoch_next(zebra_epoch_t *ep, void **host_rows, int64_t *first_batch, int64_t *n_batches)
+{
+    if (!ep || !host_rows || !first_batch || !n_batches) return fail("null argument");
+    zebra_tppr *h = ep->h;
+    *host_rows = nullptr; *first_batch = 0; *n_batches = 0;
+    if (ep->consumed >= ep->n_windows) return 0;       // end of the epoch: n_batches = 0
+    CU(cudaSetDevice(h->device));
+    // keep the device busy: stage and launch the window after the next before blocking
+    if (ep->issued < ep->n_windows && ep->issued < ep->consumed + 3) {
+        // slot (issued % 3) was handed out at call consumed-1 and is released by this call
+        if (epoch_issue(ep)) return 1;
+    }
+    const int64_t w = ep->consumed;
+    zebra_tppr::EpochSlot &sl = h->eslot[w % 3];
+    CU(cudaEventSynchronize(sl.ev_copy));
+    sl.copy_pending = false;
+    const int64_t b0 = w * ep->window;
+    *first_batch = b0;
+    *n_batches = std::min(ep->n_batches, b0 + ep->window) - b0;
+    *host_rows = ep->rows_per_edge ? sl.out_host : nullptr;
+    ep->consumed = w + 1;
+    if (ep->consumed == ep->n_windows) {
+        CU(cudaMemcpyAsync(h->status_host, h->status, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, ep->st));
+        CU(cudaStreamSynchronize(ep->st));
+        h->last_ties = h->status_host[1];
+        if (h->status_host[0] != 0) { h->timeouts++; return fail("T-PPR span kernel: dependency wait timed out"); }
+    }
+    return 0;
+}
+
+int zebra_tppr_epoch_end(zebra_epoch_t *ep)
+{
+    if (!ep) return 0;
+    zebra_tppr *h = ep->h;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(ep->st);
+    if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
+    for (auto &sl : h->eslot) sl.copy_pending = false;
+    if (h->epoch_active == ep) h->epoch_active = nullptr;
+    delete ep;
+    return 0;
+}
+
+int64_t zebra_tppr_epoch_slot_bytes(const zebra_epoch_t *ep) { return ep ? static_cast<int64_t>(ep->slot_bytes) : 0; }
 
 int zebra_tppr_sync_check(zebra_tppr_t *h, void *stream)
 {

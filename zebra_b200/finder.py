@@ -163,6 +163,73 @@ class tppr_finder:  # noqa: N801  (name kept from the reference)
                                                  self._stream_ptr()))
         self._val_tables = self._snapshot(self._tables)
 
+    # ---- pipelined epochs (include/zebra_tppr.h "pipelined epochs") ----
+    def stream_epoch(self, src, dst, neg, timestamps, edge_idxs, batch_size, rows_per_edge=3, window=128,
+                     windows=False):
+        """Generator over the batches of a chronological span held in HOST memory.
+
+        Yields, batch after batch, exactly what `streaming_topk(cat[src_b,dst_b,neg_b], ts_b, eidx_b)`
+        (rows_per_edge=3) or `streaming_topk_no_fake` (2) would return for that batch — four lists of
+        n_tppr numpy arrays [rows,k] — while the library keeps later windows of `window` batches in
+        flight (host dependency pass, H2D, span kernel, D2H into pinned memory).  The arrays are views
+        of pinned library memory, valid until the generator is advanced past the end of their window
+        (copy them to keep them).  rows_per_edge=0 updates only and yields nothing (compute_val_tppr
+        semantics without the snapshot).  `windows=True` yields one (first_batch, nodes, eidx, dt, w)
+        tuple per window instead, each a list of n_tppr arrays [n_batches, rows, k] (full batches only;
+        a ragged last batch is yielded as its own window)."""
+        src = np.ascontiguousarray(src, dtype=np.int32)
+        dst = np.ascontiguousarray(dst, dtype=np.int32)
+        neg = None if neg is None else np.ascontiguousarray(neg, dtype=np.int32)
+        ts = np.ascontiguousarray(timestamps, dtype=np.float64)
+        eidx = np.ascontiguousarray(edge_idxs, dtype=np.int64)
+        n, bs, k, T = len(src), int(batch_size), self.k, self.n_tppr
+        if not (len(dst) == n and len(eidx) == n and len(ts) >= n and (neg is None or len(neg) == n)):
+            raise ValueError("src/dst/neg/timestamps/edge_idxs do not match")
+        if n == 0:
+            return
+        L = self._L
+        ep = C.c_void_p()
+        with torch.cuda.device(self.device):
+            check(L.zebra_tppr_epoch_begin(self._h, _ptr(src), _ptr(dst), _ptr(neg), _ptr(ts), _ptr(eidx), n, rows_per_edge,
+                                           bs, int(window), self._stream_ptr(), C.byref(ep)))
+        try:
+            slot = int(L.zebra_tppr_epoch_slot_bytes(ep))
+            rows_ptr, b0, nb = C.c_void_p(), C.c_int64(), C.c_int64()
+            R = rows_per_edge * bs
+            while True:
+                check(L.zebra_tppr_epoch_next(ep, C.byref(rows_ptr), C.byref(b0), C.byref(nb)))
+                if nb.value == 0:
+                    break
+                if not rows_per_edge:
+                    continue
+                first, cnt = b0.value, nb.value
+                raw = np.ctypeslib.as_array(C.cast(rows_ptr, C.POINTER(C.c_uint8)), shape=(cnt * slot,))
+                last_edges = min(bs, n - (first + cnt - 1) * bs)
+                full = cnt if last_edges == bs else cnt - 1
+                if full:
+                    wi = raw[:full * slot].view(np.int32).reshape(full, T, 4, R, k)
+                    wf = wi.view(np.float32)
+                    if windows:
+                        yield (first, [wi[:, j, 0] for j in range(T)], [wi[:, j, 1] for j in range(T)],
+                               [wf[:, j, 2] for j in range(T)], [wf[:, j, 3] for j in range(T)])
+                    else:
+                        for q in range(full):
+                            bi, bf = wi[q], wf[q]
+                            yield ([bi[j, 0] for j in range(T)], [bi[j, 1] for j in range(T)],
+                                   [bf[j, 2] for j in range(T)], [bf[j, 3] for j in range(T)])
+                if full < cnt:       # ragged last batch of the span: same layout with fewer rows
+                    r = rows_per_edge * last_edges
+                    ti = raw[full * slot: full * slot + T * 16 * r * k].view(np.int32).reshape(T, 4, r, k)
+                    tf = ti.view(np.float32)
+                    if windows:
+                        yield (first + full, [ti[None, j, 0] for j in range(T)], [ti[None, j, 1] for j in range(T)],
+                               [tf[None, j, 2] for j in range(T)], [tf[None, j, 3] for j in range(T)])
+                    else:
+                        yield ([ti[j, 0] for j in range(T)], [ti[j, 1] for j in range(T)],
+                               [tf[j, 2] for j in range(T)], [tf[j, 3] for j in range(T)])
+        finally:
+            L.zebra_tppr_epoch_end(ep)
+
     # ---- resident spans (include/zebra_tppr.h "plans") ----
     def make_plan(self, src, dst, neg, timestamps, edge_idxs, batch_size, rows_per_edge=3):
         """Prepare a whole chronological span once and keep it resident in HBM."""
