@@ -155,9 +155,10 @@ int zebra_tppr_read_state(zebra_tppr_t *h, int32_t inst, const int64_t *host_ids
  * asynchronous and does not check by itself. */
 int zebra_tppr_sync_check(zebra_tppr_t *h, void *stream);
 
-/* Counters of the last zebra_tppr_stream / update_only call: [0] work items, [1] prunes that took
- * the exact tie path, [2] kernel launches so far on this handle, [3] spin time-outs (must be 0). */
-int zebra_tppr_counters(zebra_tppr_t *h, int64_t *out4);
+/* Counters (8 entries) of the last zebra_tppr_stream / update_only / plan_run / epoch: [0] work
+ * items, [1] prunes that took the exact tie path, [2] kernel launches so far on this handle,
+ * [3] spin time-outs (must be 0), [4] prunes ranked by the sorted-merge fast path, [5..7] zero. */
+int zebra_tppr_counters(zebra_tppr_t *h, int64_t *out8);
 
 /* Developer builds (-DZEBRA_PROFILE) accumulate clock64 cycles per kernel phase; this reads and
  * clears the 16 sums (all zero in a normal build).  Synchronises the device. */

@@ -73,7 +73,7 @@ struct zebra_tppr {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool timed = false;
     int max_blocks = 0;
-    int64_t launches = 0, last_items = 0, last_ties = 0, timeouts = 0;
+    int64_t launches = 0, last_items = 0, last_ties = 0, last_merge = 0, timeouts = 0;
     struct zebra_plan *plan_active = nullptr;   // a plan is part-way through its batches
     int64_t plan_next = 0;
     struct zebra_epoch *epoch_active = nullptr; // a pipelined epoch is part-way through its windows
@@ -304,6 +304,7 @@ int check_status(zebra_tppr *h, cudaStream_t st)
     CU(cudaMemcpyAsync(h->status_host, h->status, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     h->last_ties = h->status_host[1];
+    h->last_merge = h->status_host[2];
     if (h->status_host[0] != 0) {
         h->timeouts++;
         return fail("T-PPR span kernel: dependency wait timed out (status=%d)", h->status_host[0]);
@@ -753,6 +754,7 @@ int zebra_tppr_epoch_next(zebra_epoch_t *ep, void **host_rows, int64_t *first_ba
         CU(cudaMemcpyAsync(h->status_host, h->status, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, ep->st));
         CU(cudaStreamSynchronize(ep->st));
         h->last_ties = h->status_host[1];
+        h->last_merge = h->status_host[2];
         if (h->status_host[0] != 0) { h->timeouts++; return fail("T-PPR span kernel: dependency wait timed out"); }
     }
     return 0;
@@ -779,10 +781,12 @@ int zebra_tppr_sync_check(zebra_tppr_t *h, void *stream)
     return check_status(h, static_cast<cudaStream_t>(stream));
 }
 
-int zebra_tppr_counters(zebra_tppr_t *h, int64_t *out4)
+int zebra_tppr_counters(zebra_tppr_t *h, int64_t *out8)
 {
-    if (!h || !out4) return fail("null argument");
-    out4[0] = h->last_items; out4[1] = h->last_ties; out4[2] = h->launches; out4[3] = h->timeouts;
+    if (!h || !out8) return fail("null argument");
+    for (int q = 0; q < 8; ++q) out8[q] = 0;
+    out8[0] = h->last_items; out8[1] = h->last_ties; out8[2] = h->launches; out8[3] = h->timeouts;
+    out8[4] = h->last_merge;
     return 0;
 }
 

@@ -93,18 +93,19 @@ struct SpanParams {
     // as the reference lays out that batch: [n_tppr][4][rows_per_edge*nb*k], nb = edges in batch b
     int64_t batch_size, first_batch, out_slots, slot_bytes;
     uint32_t *ticket;
-    int32_t *status;        // [0] spin time-out flag, [1] exact-tie prunes (statistics)
+    int32_t *status;        // [0] spin time-out flag, [1] exact-tie prunes, [2] merge-ranked prunes (statistics)
     unsigned long long *prof;   // [8] cycle sums per phase (ZEBRA_PROFILE builds)
 };
 
 struct alignas(16) WarpScratch {
     unsigned long long V[64];   // candidate scores by candidate index (fp64 bit patterns in integer order)
-    unsigned long long W[64];   // the same by sort position (numba quicksort working array)
     unsigned long long K[32];   // peer keys of the duplicate scan
-    unsigned long long XV[32], YV[32];   // swap exchange: values
-    unsigned char R[64];        // position -> candidate (working permutation)
-    unsigned char P[64];        // candidate -> position
-    unsigned char XI[32], YI[32];        // swap exchange: candidates
+    // exact-tie path: numba's quicksort is replayed on (rank << 8 | candidate) items, the rank (number
+    // of strictly smaller scores) being an order-isomorphic 6-bit stand-in for the fp64 score
+    unsigned Mlo[64], Mhi[64];  // per rank: bitmap of the sort positions holding a candidate of that rank
+    unsigned short Q[64];       // sort position -> item (numba quicksort working array)
+    unsigned short X[32], Y[32];   // swap exchange
+    unsigned char P[64];        // candidate -> sort position
 };
 
 struct VecR {
@@ -203,38 +204,38 @@ __device__ __forceinline__ void emit_row(const SpanParams &p, char *base, size_t
     reinterpret_cast<float *>(base + plane * 12)[o] = w;
 }
 // One partition step of numba.misc.quicksort (median of three, pivot stashed at `high`, Hoare
-// scan) on positions [low, high] of the working permutation: R[p] = candidate at position p,
-// W[p] = its value.  Computed warp-wide from two stopper bitmaps instead of a sequential scan;
-// two warp barriers and three shared-memory latencies per step.  Returns the pivot's position.
+// scan) on positions [low, high] of the working array Q (items rank << 8 | candidate, compared by
+// rank only).  Computed warp-wide from two stopper bitmaps instead of a sequential scan; two warp
+// barriers and three shared-memory latencies per step.  Returns the pivot's position.
 __device__ __forceinline__ int qs_partition(WarpScratch &s, int low, int high, int lane)
 {
     const int mid = (low + high) >> 1;
     const int p0 = lane, p1 = lane + 32;
-    int rl = s.R[low], rm = s.R[mid], rh = s.R[high];
-    unsigned long long vl = s.W[low], vm = s.W[mid], vh = s.W[high];
-    int r0 = s.R[p0], r1 = s.R[p1];
-    unsigned long long v0 = s.W[p0], v1 = s.W[p1];
-    if (vm < vl) { int t = rl; rl = rm; rm = t; unsigned long long u = vl; vl = vm; vm = u; }
-    if (vh < vm) { int t = rh; rh = rm; rm = t; unsigned long long u = vh; vh = vm; vm = u; }
-    if (vm < vl) { int t = rl; rl = rm; rm = t; unsigned long long u = vl; vl = vm; vm = u; }
-    const unsigned long long pivot = vm;
+    unsigned il = s.Q[low], im = s.Q[mid], ih = s.Q[high];
+    unsigned q0 = s.Q[p0], q1 = s.Q[p1];
+    if ((im >> 8) < (il >> 8)) { const unsigned t = il; il = im; im = t; }
+    if ((ih >> 8) < (im >> 8)) { const unsigned t = ih; ih = im; im = t; }
+    if ((im >> 8) < (il >> 8)) { const unsigned t = il; il = im; im = t; }
+    const unsigned pivot = im >> 8;
     // what the scan sees: low <- smallest, mid <- largest, high <- pivot (excluded from the scan)
-    if (p0 == low) { r0 = rl; v0 = vl; } else if (p0 == mid) { r0 = rh; v0 = vh; }
-    if (p1 == low) { r1 = rl; v1 = vl; } else if (p1 == mid) { r1 = rh; v1 = vh; }
+    if (p0 == low) q0 = il; else if (p0 == mid) q0 = ih;
+    if (p1 == low) q1 = il; else if (p1 == mid) q1 = ih;
     const bool in0 = p0 >= low && p0 < high, in1 = p1 >= low && p1 < high;
-    const bool L0 = in0 && !(v0 < pivot), L1 = in1 && !(v1 < pivot);   // i stops here
-    const bool Q0 = in0 && !(pivot < v0), Q1 = in1 && !(pivot < v1);   // j stops here
+    const bool L0 = in0 && (q0 >> 8) >= pivot, L1 = in1 && (q1 >> 8) >= pivot;   // i stops here
+    const bool Q0 = in0 && (q0 >> 8) <= pivot, Q1 = in1 && (q1 >> 8) <= pivot;   // j stops here
     const unsigned long long Lm = __ballot_sync(kFull, L0) | (static_cast<unsigned long long>(__ballot_sync(kFull, L1)) << 32);
     const unsigned long long Qm = __ballot_sync(kFull, Q0) | (static_cast<unsigned long long>(__ballot_sync(kFull, Q1)) << 32);
     const int lb0 = __popcll(Lm & ((1ull << p0) - 1)), lb1 = __popcll(Lm & ((1ull << p1) - 1));
     const int qa0 = __popcll(Qm >> (p0 + 1)), qa1 = (p1 == 63) ? 0 : __popcll(Qm >> (p1 + 1));
     const bool swL0 = L0 && qa0 > lb0, swL1 = L1 && qa1 > lb1;
     const bool swQ0 = Q0 && lb0 > qa0, swQ1 = Q1 && lb1 > qa1;
-    if (swL0) { s.XI[lb0] = r0; s.XV[lb0] = v0; }
-    if (swL1) { s.XI[lb1] = r1; s.XV[lb1] = v1; }
-    if (swQ0) { s.YI[qa0] = r0; s.YV[qa0] = v0; }
-    if (swQ1) { s.YI[qa1] = r1; s.YV[qa1] = v1; }
-    const int M = __popc(__ballot_sync(kFull, swL0)) + __popc(__ballot_sync(kFull, swL1));
+    if (swL0) s.X[lb0] = static_cast<unsigned short>(q0);
+    if (swL1) s.X[lb1] = static_cast<unsigned short>(q1);
+    if (swQ0) s.Y[qa0] = static_cast<unsigned short>(q0);
+    if (swQ1) s.Y[qa1] = static_cast<unsigned short>(q1);
+    // M = number of swaps; the swapped left stoppers are exactly those with lb < M
+    const unsigned long long swLm = __ballot_sync(kFull, swL0) | (static_cast<unsigned long long>(__ballot_sync(kFull, swL1)) << 32);
+    const int M = __popcll(swLm);
     // first unswapped left stopper (rank M) and the last swapped right stopper (rank M-1)
     const unsigned long long lM = __ballot_sync(kFull, L0 && lb0 == M) |
                                   (static_cast<unsigned long long>(__ballot_sync(kFull, L1 && lb1 == M)) << 32);
@@ -244,31 +245,28 @@ __device__ __forceinline__ int qs_partition(WarpScratch &s, int low, int high, i
     int i = lM ? (__ffsll(static_cast<long long>(lM)) - 1) : 64;
     if (bound < i) i = bound;
     __syncwarp();
-    if (swL0) { r0 = s.YI[lb0]; v0 = s.YV[lb0]; }
-    if (swL1) { r1 = s.YI[lb1]; v1 = s.YV[lb1]; }
-    if (swQ0) { r0 = s.XI[qa0]; v0 = s.XV[qa0]; }
-    if (swQ1) { r1 = s.XI[qa1]; v1 = s.XV[qa1]; }
+    if (swL0) q0 = s.Y[lb0];
+    if (swL1) q1 = s.Y[lb1];
+    if (swQ0) q0 = s.X[qa0];
+    if (swQ1) q1 = s.X[qa1];
     // the pivot lands on i, the element that was there moves to `high`
     if (in0) {
-        if (p0 == i) { s.R[high] = r0; s.W[high] = v0; s.R[p0] = rm; s.W[p0] = pivot; }
-        else { s.R[p0] = r0; s.W[p0] = v0; }
-    } else if (p0 == high && i == high) { s.R[p0] = rm; s.W[p0] = pivot; }
+        if (p0 == i) { s.Q[high] = static_cast<unsigned short>(q0); s.Q[p0] = static_cast<unsigned short>(im); }
+        else s.Q[p0] = static_cast<unsigned short>(q0);
+    } else if (p0 == high && i == high) s.Q[p0] = static_cast<unsigned short>(im);
     if (in1) {
-        if (p1 == i) { s.R[high] = r1; s.W[high] = v1; s.R[p1] = rm; s.W[p1] = pivot; }
-        else { s.R[p1] = r1; s.W[p1] = v1; }
-    } else if (p1 == high && i == high) { s.R[p1] = rm; s.W[p1] = pivot; }
+        if (p1 == i) { s.Q[high] = static_cast<unsigned short>(q1); s.Q[p1] = static_cast<unsigned short>(im); }
+        else s.Q[p1] = static_cast<unsigned short>(q1);
+    } else if (p1 == high && i == high) s.Q[p1] = static_cast<unsigned short>(im);
     __syncwarp();
     return i;
 }
 
-// Runs the partition phase of numba's argsort on the n candidates in V; afterwards a stable sort of
-// the permuted sequence (R, W) equals numba's final order (its insertion sort on segments < 16 is
-// stable).  Leaves P[candidate] = position.
+// Runs the partition phase of numba's argsort on the n items in Q; afterwards a stable sort of the
+// permuted sequence equals numba's final order (its insertion sort on segments < 16 is stable).
+// Leaves P[candidate] = position.
 __device__ __forceinline__ void qs_partition_phase(WarpScratch &s, int n, int lane)
 {
-    s.R[lane] = lane; s.R[lane + 32] = lane + 32;
-    s.W[lane] = s.V[lane]; s.W[lane + 32] = s.V[lane + 32];
-    __syncwarp();
     // pending (low, high) ranges, packed low<<8|high; numba pushes the larger side, so with n <= 63
     // and ranges shorter than 16 never pushed-and-split again more than twice, four slots suffice
     int sp = 0, k0 = 0, k1 = 0, k2 = 0, k3 = 0;
@@ -291,8 +289,8 @@ __device__ __forceinline__ void qs_partition_phase(WarpScratch &s, int n, int la
         low = k0 >> 8; high = k0 & 0xff;
         k0 = k1; k1 = k2; k2 = k3;
     }
-    if (lane < n) s.P[s.R[lane]] = lane;
-    if (lane + 32 < n) s.P[s.R[lane + 32]] = lane + 32;
+    if (lane < n) s.P[s.Q[lane] & 0xff] = lane;
+    if (lane + 32 < n) s.P[s.Q[lane + 32] & 0xff] = lane + 32;
     __syncwarp();
 }
 
@@ -401,12 +399,45 @@ __device__ __forceinline__ bool update_endpoint(const SpanParams &p, WarpScratch
         // rank = number of candidates strictly below; equal scores share a rank, which shows up as
         // a hole in the set of occupied ranks
         int r0 = 0, r1 = 0;
-        const ulonglong2 *V2 = reinterpret_cast<const ulonglong2 *>(s.V);
+        // Stored vectors are in ascending score order whenever their last update pruned (always, for
+        // a full vector), and scaling keeps that order.  If neither list was disturbed (no duplicate
+        // key added into A, new key not replacing an entry) and both are still sorted, ranks come from
+        // a merge: the run start inside the own list plus a binary search in the other one.
+        bool fast = dupmask == 0 && !replaced && !(ZEBRA_ABLATE & 8);
+        unsigned long long pa = 0, pb = 0;
+        if (fast) {
+            pa = __shfl_up_sync(kFull, b0, 1); pb = __shfl_up_sync(kFull, b1, 1);
+            const bool bad = lane > 0 && ((valid0 && b0 < pa) || (ndB && b1 < pb));
+            fast = !__any_sync(kFull, bad);
+        }
+        if (fast) {
+            const unsigned upto = 0xffffffffu >> (31 - lane);
+            const unsigned SA = ~__ballot_sync(kFull, valid0 && lane > 0 && b0 == pa);
+            const unsigned SB = ~__ballot_sync(kFull, ndB && lane > 0 && b1 == pb);
+            const int firstA = 31 - __clz(SA & upto), firstB = 31 - __clz(SB & upto);
+            const unsigned long long bw = order_bits(w_new);
+            const unsigned long long x1 = lane == 31 ? bw : b0;     // looked up in the peer's part [c1, c1+c2)
+            const unsigned long long x2 = b1;                       // looked up in the own part [0, c1)
+            int lb = 0, la = 0;
+#pragma unroll
+            for (int st = 16; st > 0; st >>= 1) {
+                const int ib = lb + st, ia = la + st;
+                const unsigned long long vb = s.V[c1 + (ib <= c2 ? ib : 1) - 1];
+                const unsigned long long va = s.V[(ia <= c1 ? ia : 1) - 1];
+                if (ib <= c2 && vb < x1) lb = ib;
+                if (ia <= c1 && va < x2) la = ia;
+            }
+            r0 = firstA + lb + (bw < b0 ? 1 : 0);
+            r1 = lane == 31 ? la + lb : firstB + la + (bw < b1 ? 1 : 0);
+            if (lane == 0) atomicAdd(p.status + 2, 1);
+        } else {
+            const ulonglong2 *V2 = reinterpret_cast<const ulonglong2 *>(s.V);
 #pragma unroll 4
-        for (int q = 0; q < (((ZEBRA_ABLATE & 2) ? 0 : n + 1) >> 1); ++q) {
-            const ulonglong2 vv = V2[q];
-            r0 += vv.x < b0; r1 += vv.x < b1;
-            r0 += vv.y < b0; r1 += vv.y < b1;
+            for (int q = 0; q < (((ZEBRA_ABLATE & 2) ? 0 : n + 1) >> 1); ++q) {
+                const ulonglong2 vv = V2[q];
+                r0 += vv.x < b0; r1 += vv.x < b1;
+                r0 += vv.y < b0; r1 += vv.y < b1;
+            }
         }
         const int cut = n - k;
         if (ZEBRA_ABLATE & 2) { r0 = lane; r1 = pos1; }
@@ -418,15 +449,24 @@ __device__ __forceinline__ bool update_endpoint(const SpanParams &p, WarpScratch
         // survivor set or its slot order depends on numba's (unstable) argsort
         const unsigned long long surv = ((1ull << k) - 1) << cut;
         if ((occ & surv) != surv && !(ZEBRA_ABLATE & 4)) {
+            // numba's (unstable) argsort decides the order inside a group of equal scores: replay its
+            // partition phase on the ranks, then order equals by their position in the permuted array
+            s.Mlo[lane] = 0; s.Mlo[lane + 32] = 0; s.Mhi[lane] = 0; s.Mhi[lane + 32] = 0;
+            if (valid0) s.Q[lane] = static_cast<unsigned short>((r0 << 8) | lane);
+            if (valid1) s.Q[pos1] = static_cast<unsigned short>((r1 << 8) | pos1);
+            __syncwarp();
             qs_partition_phase(s, n, lane);
-            // rank among equals = order of their positions after the partition phase
             const int P0 = valid0 ? s.P[lane] : 0, P1 = valid1 ? s.P[pos1] : 0;
-            const ulonglong2 *W2 = reinterpret_cast<const ulonglong2 *>(s.W);
-#pragma unroll 4
-            for (int q = 0; q < (n + 1) >> 1; ++q) {
-                const ulonglong2 ww = W2[q];
-                r0 += (ww.x == b0) && (2 * q < P0); r1 += (ww.x == b1) && (2 * q < P1);
-                r0 += (ww.y == b0) && (2 * q + 1 < P0); r1 += (ww.y == b1) && (2 * q + 1 < P1);
+            if (valid0) atomicOr(P0 < 32 ? &s.Mlo[r0] : &s.Mhi[r0], 1u << (P0 & 31));
+            if (valid1) atomicOr(P1 < 32 ? &s.Mlo[r1] : &s.Mhi[r1], 1u << (P1 & 31));
+            __syncwarp();
+            if (valid0) {
+                const unsigned lo = s.Mlo[r0], hi = s.Mhi[r0];
+                r0 += P0 < 32 ? __popc(lo & ((1u << P0) - 1)) : __popc(lo) + __popc(hi & ((1u << (P0 - 32)) - 1));
+            }
+            if (valid1) {
+                const unsigned lo = s.Mlo[r1], hi = s.Mhi[r1];
+                r1 += P1 < 32 ? __popc(lo & ((1u << P1) - 1)) : __popc(lo) + __popc(hi & ((1u << (P1 - 32)) - 1));
             }
             if (lane == 0) atomicAdd(p.status + 1, 1);
         }
@@ -448,11 +488,11 @@ __device__ __forceinline__ bool update_endpoint(const SpanParams &p, WarpScratch
         }
         if (lane == 0) atomicSub(rcnt, static_cast<int32_t>(rwait));
     }
-    if (keep0) st_entry(rec, k, pos0, A.e, A.n, A.ts, vA, tag);
-    if (keep1) st_entry(rec, k, pos1, e1, n1, ts1, v1, tag);
-    __syncwarp();
+    // every chunk validates itself by its tag, so the order of these stores does not matter
     const int upd = A.upd < kMaxUpdates ? A.upd + 1 : kMaxUpdates;
     if (lane == 0) st_chunk(rec, new_norm, n | (upd << kCountBits), tag);
+    if (keep0) st_entry(rec, k, pos0, A.e, A.n, A.ts, vA, tag);
+    if (keep1) st_entry(rec, k, pos1, e1, n1, ts1, v1, tag);
     ZP_MARK(12);
     return ok;
 }
@@ -498,6 +538,10 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
         char *recD = table + static_cast<size_t>(dN) * p.stride;
         const char *recG = table + static_cast<size_t>(gN) * p.stride;
         const uint32_t my_tag = tag_base + static_cast<uint32_t>(i);
+        // the rest of the edge record now: a load issued after the wait would sit on the chain
+        const double t = p.ts[i];
+        const int e = p.eidx[i];
+        const uint32_t rwS = p.rthr_s[i], rwD = loop ? 0u : p.rthr_d[i];
 
         // ---- read the three vectors; wait for the producers of src and dst (the chain) ----
         VecR S, D, G;
@@ -549,10 +593,6 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
         if (!neg_own) G = vsel(gN == sN, S, D);    // a negative equal to an endpoint: its OLD vector
         if (okG && neg_own && (flags & kFlagSignal) && lane == 0) atomicAdd(rcnt + gN, 1);
         bool sigG = okG;
-
-        const double t = p.ts[i];
-        const int e = p.eidx[i];
-        const uint32_t rwS = p.rthr_s[i], rwD = loop ? 0u : p.rthr_d[i];
 
         // ---- the hotter endpoint first: its next writer is the one most likely to be waiting ----
         // (one copy of the update code, run twice: the kernel is bound by instruction fetch otherwise)

@@ -252,9 +252,10 @@ class tppr_finder:  # noqa: N801  (name kept from the reference)
         check(self._L.zebra_tppr_sync_check(self._h, self._stream_ptr()))
 
     def counters(self):
-        o = np.zeros(4, np.int64)
+        o = np.zeros(8, np.int64)
         check(self._L.zebra_tppr_counters(self._h, _ptr(o)))
-        return {"items": int(o[0]), "tie_prunes": int(o[1]), "launches": int(o[2]), "timeouts": int(o[3])}
+        return {"items": int(o[0]), "tie_prunes": int(o[1]), "launches": int(o[2]), "timeouts": int(o[3]),
+                "merge_ranked": int(o[4])}
 
     def profile(self):
         o = np.zeros(16, np.uint64)
