@@ -143,6 +143,35 @@ int zebra_tppr_epoch_next(zebra_epoch_t *epoch, void **host_rows, int64_t *first
 int zebra_tppr_epoch_end(zebra_epoch_t *epoch);
 int64_t zebra_tppr_epoch_slot_bytes(const zebra_epoch_t *epoch);
 
+/* ---- node-sharded mode: one process (or handle) per GPU, T-PPR state partitioned by node id,
+ *      cross-shard endpoint vectors exchanged inside the span kernel through peer-mapped mailboxes
+ *      over NVLink (BASELINE.json north_star "partitioned by node id") --------
+ * Node v lives on rank v & (world-1), local row v >> log2(world); world is 2, 4 or 8.  Every rank
+ * creates its handle with the GLOBAL num_nodes, calls shard_init (which allocates the local table
+ * slices and the arena = mailboxes + output region, and returns a 64-byte cudaIpcMemHandle_t),
+ * exchanges the handles by any means (torch.distributed.all_gather) and calls shard_connect with
+ * the world*64 bytes.  Within one process (several GPUs, or tests on one GPU) shard_connect_local
+ * takes the handles of all ranks instead.
+ *
+ * Sharded handles stream through plans only (dependencies must be global to the span): every rank
+ * builds the same plan from the same replicated edge arrays and calls zebra_tppr_plan_run with
+ * dev_out = NULL and the same arguments.  A launch may cover at most max_window_edges edges.  Rows
+ * are written by the owner of the node they describe into the output region of EVERY rank at the
+ * plan-run slot offsets; after all ranks have synchronised their streams and met at a barrier, each
+ * rank's zebra_tppr_shard_out() holds the complete result, byte-identical to the single-GPU one.
+ * The caller places a barrier between shard_reset and the first launch and before reusing slots.
+ * backup/restore aliasing is a single-GPU feature; zebra_tppr_read_state reads owned nodes only.
+ */
+int zebra_tppr_shard_init(zebra_tppr_t *h, int32_t rank, int32_t world, int64_t max_window_edges,
+                          size_t out_bytes, void *ipc_handle_out);
+int zebra_tppr_shard_connect(zebra_tppr_t *h, const void *ipc_handles);
+int zebra_tppr_shard_connect_local(zebra_tppr_t *h, zebra_tppr_t *const *ranks);
+void *zebra_tppr_shard_out(zebra_tppr_t *h);
+size_t zebra_tppr_shard_out_bytes(const zebra_tppr_t *h);
+int zebra_tppr_shard_reset(zebra_tppr_t *h, void *stream);
+/* Caps the persistent grid (blocks of 8 warps); lets two ranks share one GPU in tests. */
+int zebra_tppr_set_max_blocks(zebra_tppr_t *h, int32_t blocks);
+
 /* Debug / test access: copy the vectors of `n_ids` nodes of instance `inst` to host arrays
  * (counts int32[n_ids], eidx int32[n_ids*k], node int32[n_ids*k], ts f64[n_ids*k],
  * score f64[n_ids*k], norm f64[n_ids]).  Synchronous. */

@@ -1,0 +1,105 @@
+"""GPU parity of the node-sharded span kernel (zebra_b200/sharded.py, tppr_shard_device.cuh).
+
+The sharded protocol (ownership, mailbox pushes, rows written into every rank's output region) is
+exercised here on ONE GPU: `world` handles in one process, each capped to 1/world of the persistent
+grid so that all ranks' kernels are co-resident, each on its own stream.  Every rank's output must be
+byte-identical to the C oracle's per-batch results (and so to the single-GPU path), and the owned
+vectors must equal the oracle's final state bit for bit.  tests/test_gpu_sharded_mp.py runs the same
+check with one process per GPU over CUDA IPC when the box has more than one GPU."""
+import numpy as np
+import pytest
+
+import oracle
+from zebra_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+AL, BE = [0.1, 0.1], [0.5, 0.95]
+
+
+def _run_sharded(world, st, neg, bs, k, window, rows_per_edge=3):
+    import torch
+    from zebra_b200.sharded import ShardedFinder
+    N = st.shape.table_nodes
+    n_batches = (st.n_edges + bs - 1) // bs
+    out_bytes = n_batches * 2 * 16 * rows_per_edge * bs * k
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    fs = [ShardedFinder(N, k, 2, AL, BE, r, world, window * bs, out_bytes) for r in range(world)]
+    for f in fs:
+        f.set_max_blocks(max(1, (2 * sms) // world))
+    ShardedFinder.connect_local(fs)
+    plans = [f.make_plan(st.src, st.dst, neg if rows_per_edge == 3 else None, st.ts, st.eidx, bs, rows_per_edge) for f in fs]
+    streams = [torch.cuda.Stream() for _ in fs]
+    torch.cuda.synchronize()
+    for f, p, s in zip(fs, plans, streams):
+        with torch.cuda.stream(s):
+            p.run(0, n_batches, window, out_slots=n_batches)
+    for f, s in zip(fs, streams):
+        with torch.cuda.stream(s):
+            f.sync_check()
+    torch.cuda.synchronize()
+    return fs, plans, n_batches
+
+
+@pytest.mark.parametrize("world,name,n_edges,bs,window", [(2, "wikipedia", 6000, 200, 8), (4, "superuser", 5000, 200, 4),
+                                                         (2, "reddit", 3100, 100, 64), (8, "superuser", 3000, 200, 2)])
+def test_sharded_matches_oracle(world, name, n_edges, bs, window):
+    st = synth.make_stream(name, n_edges=n_edges, seed=77)
+    neg = synth.make_negatives(st, bs)
+    N, k = st.shape.table_nodes, 20
+    fs, plans, n_batches = _run_sharded(world, st, neg, bs, k, window)
+    cpu = oracle.OracleFinder(N, k, 2, AL, BE)
+    for b in range(n_batches):
+        lo, hi = b * bs, min(n_edges, (b + 1) * bs)
+        nodes = np.concatenate([st.src[lo:hi], st.dst[lo:hi], neg[lo:hi]]).astype(np.int32)
+        ref = cpu.streaming_topk(nodes, np.concatenate([st.ts[lo:hi]] * 3), st.eidx[lo:hi])
+        for f, p in zip(fs, plans):
+            got = p.views(f.out, b, 0, n_batches)
+            for la, lb in zip(got, ref):
+                for x, y in zip(la, lb):
+                    assert np.array_equal(x.cpu().numpy(), y), f"rank {f.rank} batch {b}"
+    ids = np.unique(np.concatenate([st.src, st.dst]))
+    for f in fs:
+        mine = ids[(ids & (world - 1)) == f.rank][:400]
+        for j in range(2):
+            for a, (e, n, t, s, nm) in zip(mine, f.state(j, mine)):
+                oe, on, ot, os_, onm = cpu.state(j, int(a))
+                assert np.array_equal(e, oe) and np.array_equal(n, on) and np.array_equal(t, ot)
+                assert np.array_equal(s, os_), "fp64 scores must be bit-identical"
+                assert nm == onm
+        assert f.counters()["timeouts"] == 0
+    with pytest.raises(RuntimeError):
+        fs[0].state(0, np.array([1]))      # node 1 lives on rank 1
+
+
+def test_sharded_adversarial_self_loops_and_ties():
+    """Self-loops, negatives equal to an endpoint, exact score ties (alpha=beta=0.5), repeated pairs."""
+    rng = np.random.default_rng(3)
+    E, N, bs, k = 2400, 64, 100, 8
+    src = rng.integers(1, N, E).astype(np.int32)
+    dst = rng.integers(1, N, E).astype(np.int32)
+    dst[::17] = src[::17]
+    neg = rng.integers(1, N, E).astype(np.int32)
+    neg[::11] = src[::11]
+    neg[5::13] = dst[5::13]
+    ts = np.floor(np.cumsum(rng.exponential(3.0, E)))
+    eidx = np.arange(1, E + 1, dtype=np.int64)
+    shape = synth.StreamShape("adv", N - 1, 0, E, 0, 1.0, 0.1, 0.0)
+    st = synth.Stream(shape, src, dst, ts, eidx, np.unique(dst))
+    global AL, BE
+    old = (AL, BE)
+    AL, BE = [0.5, 0.1], [0.5, 0.5]
+    try:
+        fs, plans, n_batches = _run_sharded(2, st, neg, bs, k, 3)
+        cpu = oracle.OracleFinder(N, k, 2, AL, BE)
+        for b in range(n_batches):
+            lo, hi = b * bs, min(E, (b + 1) * bs)
+            nodes = np.concatenate([src[lo:hi], dst[lo:hi], neg[lo:hi]]).astype(np.int32)
+            ref = cpu.streaming_topk(nodes, np.concatenate([ts[lo:hi]] * 3), eidx[lo:hi])
+            for f, p in zip(fs, plans):
+                got = p.views(f.out, b, 0, n_batches)
+                for la, lb in zip(got, ref):
+                    for x, y in zip(la, lb):
+                        assert np.array_equal(x.cpu().numpy(), y), f"rank {f.rank} batch {b}"
+    finally:
+        AL, BE = old

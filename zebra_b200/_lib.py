@@ -29,6 +29,13 @@ SIGNATURES = {
     "zebra_tppr_epoch_next": (C.c_int, [_VP, C.POINTER(_VP), C.POINTER(_I64), C.POINTER(_I64)]),
     "zebra_tppr_epoch_end": (C.c_int, [_VP]),
     "zebra_tppr_epoch_slot_bytes": (_I64, [_VP]),
+    "zebra_tppr_shard_init": (C.c_int, [_VP, _I32, _I32, _I64, C.c_size_t, _VP]),
+    "zebra_tppr_shard_connect": (C.c_int, [_VP, _VP]),
+    "zebra_tppr_shard_connect_local": (C.c_int, [_VP, _VP]),
+    "zebra_tppr_shard_out": (_VP, [_VP]),
+    "zebra_tppr_shard_out_bytes": (C.c_size_t, [_VP]),
+    "zebra_tppr_shard_reset": (C.c_int, [_VP, _VP]),
+    "zebra_tppr_set_max_blocks": (C.c_int, [_VP, _I32]),
     "zebra_tppr_read_state": (C.c_int, [_VP, _I32, _VP, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "zebra_tppr_sync_check": (C.c_int, [_VP, _VP]),
     "zebra_tppr_counters": (C.c_int, [_VP, _VP]),

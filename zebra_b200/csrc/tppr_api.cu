@@ -6,6 +6,7 @@
 // CPU fallback: without a CUDA device every entry point fails with an error.
 #include "common.cuh"
 #include "tppr_device.cuh"
+#include "tppr_shard_device.cuh"
 #include "../../include/zebra_tppr.h"
 
 #include <algorithm>
@@ -87,6 +88,19 @@ struct zebra_tppr {
         bool copy_pending = false;
     } eslot[3];
     cudaStream_t copy_stream = nullptr;
+    // node-sharded mode (zebra_tppr_shard_*): tables are library-owned local slices, the arena
+    // (mailboxes + output region) is peer-mapped on every rank
+    int32_t world = 1, rank = 0, world_log2 = 0;
+    int64_t table_rows = 0;                    // records per table: num_nodes, or the local slice when sharded
+    bool own_tables = false;
+    char *arena = nullptr;
+    size_t mbox_half = 0, out_region = 0;
+    int64_t max_window_edges = 0;
+    char *peer_arena[zebra::kMaxRanks] = {};
+    bool peer_opened[zebra::kMaxRanks] = {};   // mapped with cudaIpcOpenMemHandle (to be closed)
+    int32_t launch_parity = 0;
+    uint32_t shard_seq = 1;                    // handle-local tag sequence: identical on every rank
+    int shard_max_blocks = 0;
 };
 
 // A span prepared once and kept resident in HBM (edge records + dependency thresholds).
@@ -220,6 +234,22 @@ struct BatchOut {
 // handle zeroes the tags of its bound tables before its next launch.
 int alloc_seq(zebra_tppr *h, int64_t n, cudaStream_t st, uint32_t *base)
 {
+    if (h->world > 1) {
+        // every rank must draw the same tags for the same span: a per-handle sequence, advanced by the
+        // same calls on every rank (SPMD), instead of the process-wide one
+        if (static_cast<uint64_t>(h->shard_seq) + static_cast<uint64_t>(n) >= 0xF0000000ull) {
+            const int per = 2 * h->k + 1;
+            const int64_t total = h->table_rows * per;
+            for (int j = 0; j < h->n_tppr; ++j)
+                zebra::tppr_retag_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(h->tables[j], h->stride, h->k,
+                                                                                                    h->table_rows);
+            CU(cudaGetLastError());
+            h->shard_seq = 1;
+        }
+        *base = h->shard_seq;
+        h->shard_seq += static_cast<uint32_t>(n);
+        return 0;
+    }
     uint32_t epoch;
     {
         std::lock_guard<std::mutex> lk(g_seq_mu);
@@ -230,10 +260,10 @@ int alloc_seq(zebra_tppr *h, int64_t n, cudaStream_t st, uint32_t *base)
     }
     if (h->epoch != epoch) {
         const int per = 2 * h->k + 1;
-        const int64_t total = h->num_nodes * per;
+        const int64_t total = h->table_rows * per;
         for (int j = 0; j < h->n_tppr; ++j)
             zebra::tppr_retag_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(h->tables[j], h->stride, h->k,
-                                                                                                h->num_nodes);
+                                                                                                h->table_rows);
         CU(cudaGetLastError());
         h->epoch = epoch;
     }
@@ -274,9 +304,31 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
     p.out = out; p.ticket = h->ticket; p.status = h->status; p.prof = h->prof;
     p.batch_size = bo.batch_size; p.first_batch = bo.first_batch; p.out_slots = bo.out_slots; p.slot_bytes = bo.slot_bytes;
     const int64_t items = m * h->n_tppr;
-    int blocks = static_cast<int>(std::min<int64_t>((items + zebra::kWarpsPerBlock - 1) / zebra::kWarpsPerBlock, h->max_blocks));
+    const bool sharded = h->world > 1;
+    int blocks = static_cast<int>(std::min<int64_t>((items + zebra::kWarpsPerBlock - 1) / zebra::kWarpsPerBlock,
+                                                    sharded ? h->shard_max_blocks : h->max_blocks));
     if (blocks < 1) blocks = 1;
-    zebra::tppr_span_kernel<<<blocks, zebra::kWarpsPerBlock * 32, 0, st>>>(p);
+    if (sharded) {
+        if (m > h->max_window_edges) return fail("sharded launch of %lld edges exceeds the mailbox window (%lld)", (long long)m, (long long)h->max_window_edges);
+        if (out) return fail("node-sharded mode writes rows to the shared output region: dev_out must be NULL");
+        for (int r = 0; r < h->world; ++r)
+            if (!h->peer_arena[r]) return fail("zebra_tppr_shard_connect has not been called");
+        if (rows_per_edge) {
+            const size_t need = bo.batch_size > 0 ? static_cast<size_t>(bo.out_slots) * bo.slot_bytes
+                                                  : zebra_tppr_out_bytes(h, n_total, rows_per_edge);
+            if (need > h->out_region) return fail("output of %zu bytes exceeds the shared output region (%zu)", need, h->out_region);
+        }
+        p.world_log2 = h->world_log2; p.rank = h->rank; p.mbox_parity = h->launch_parity;
+        p.mbox_half_bytes = static_cast<int64_t>(h->mbox_half);
+        for (int r = 0; r < h->world; ++r) {
+            p.mbox_peer[r] = h->peer_arena[r];
+            p.out_peer[r] = h->peer_arena[r] + 2 * h->mbox_half;
+        }
+        h->launch_parity ^= 1;
+        zebra::tppr_span_shard_kernel<<<blocks, zebra::kWarpsPerBlock * 32, 0, st>>>(p);
+    } else {
+        zebra::tppr_span_kernel<<<blocks, zebra::kWarpsPerBlock * 32, 0, st>>>(p);
+    }
     CU(cudaGetLastError());
     // every warp of the grid draws exactly one ticket past the end
     h->ticket_base += static_cast<uint32_t>(items) + static_cast<uint32_t>(blocks) * zebra::kWarpsPerBlock;
@@ -319,6 +371,7 @@ int run_span(zebra_tppr *h, const NodeT *src, const NodeT *dst, const NodeT *neg
     for (int j = 0; j < h->n_tppr; ++j)
         if (!h->tables[j]) return fail("zebra_tppr_bind_tables has not been called");
     if (h->plan_active || h->epoch_active) return fail("a plan or epoch is part-way through its batches; finish it before streaming other spans");
+    if (h->world > 1) return fail("node-sharded handles stream through plans (zebra_tppr_plan_run): dependencies must be span-global across ranks");
     CU(cudaSetDevice(h->device));
     CU(cudaMemsetAsync(h->status + 1, 0, 3 * sizeof(int32_t), st));   // [0] (time-out) is sticky
     h->last_items = 0;
@@ -361,6 +414,7 @@ int zebra_tppr_create(zebra_tppr_t **out, int64_t num_nodes, int32_t k, int32_t 
     zebra_tppr *h = new zebra_tppr();
     h->num_nodes = num_nodes; h->k = k; h->n_tppr = n_tppr; h->device = device;
     h->stride = static_cast<int32_t>(record_bytes(k));
+    h->table_rows = num_nodes;
     for (int j = 0; j < n_tppr; ++j) { h->alpha[j] = alpha_list[j]; h->beta[j] = beta_list[j]; }
     h->lastw.assign(static_cast<size_t>(num_nodes), -1);
     h->rhead.assign(static_cast<size_t>(num_nodes), -1);
@@ -423,6 +477,11 @@ int zebra_tppr_destroy(zebra_tppr_t *h)
         if (sl.ev_copy) cudaEventDestroy(sl.ev_copy);
     }
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+    for (int r = 0; r < zebra::kMaxRanks; ++r)
+        if (h->peer_opened[r] && h->peer_arena[r]) cudaIpcCloseMemHandle(h->peer_arena[r]);
+    if (h->arena) cudaFree(h->arena);
+    if (h->own_tables)
+        for (auto &t : h->tables) if (t) cudaFree(t);
     if (h->rcnt) cudaFree(h->rcnt);
     for (auto d : h->decay) if (d) cudaFree(d);
     if (h->ticket) cudaFree(h->ticket);
@@ -438,11 +497,12 @@ int zebra_tppr_destroy(zebra_tppr_t *h)
 }
 
 size_t zebra_tppr_record_bytes(const zebra_tppr_t *h) { return h ? static_cast<size_t>(h->stride) : 0; }
-size_t zebra_tppr_table_bytes(const zebra_tppr_t *h) { return h ? static_cast<size_t>(h->stride) * h->num_nodes : 0; }
+size_t zebra_tppr_table_bytes(const zebra_tppr_t *h) { return h ? static_cast<size_t>(h->stride) * h->table_rows : 0; }
 
 int zebra_tppr_bind_tables(zebra_tppr_t *h, void *const *dev_tables)
 {
     if (!h || !dev_tables) return fail("null argument");
+    if (h->own_tables) return fail("node-sharded handles own their tables (zebra_tppr_shard_reset zero-fills them)");
     for (int j = 0; j < h->n_tppr; ++j) {
         if (!dev_tables[j]) return fail("table %d is null", j);
         if (reinterpret_cast<uintptr_t>(dev_tables[j]) % 16) return fail("table %d is not 16-byte aligned", j);
@@ -523,6 +583,15 @@ int zebra_tppr_read_state(zebra_tppr_t *h, int32_t inst, const int64_t *host_ids
     if (n_ids <= 0) return 0;
     for (int64_t a = 0; a < n_ids; ++a)
         if (host_ids[a] < 0 || host_ids[a] >= h->num_nodes) return fail("node id out of range");
+    std::vector<int64_t> local;
+    if (h->world > 1) {          // node-sharded: only this rank's nodes, addressed by local row
+        local.resize(static_cast<size_t>(n_ids));
+        for (int64_t a = 0; a < n_ids; ++a) {
+            if ((host_ids[a] & (h->world - 1)) != h->rank) return fail("node %lld lives on rank %lld", (long long)host_ids[a], (long long)(host_ids[a] & (h->world - 1)));
+            local[static_cast<size_t>(a)] = host_ids[a] >> h->world_log2;
+        }
+        host_ids = local.data();
+    }
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     CU(cudaSetDevice(h->device));
     const int k = h->k;
@@ -615,7 +684,9 @@ int zebra_tppr_plan_run(zebra_tppr_t *h, zebra_plan_t *pl, int64_t first_batch, 
     if (h->plan_active != pl || h->plan_next != first_batch)
         return fail("plan batches must run in order starting from 0 (next expected %lld)", (long long)h->plan_next);
     if (pl->rows_per_edge) {
-        if (!dev_out || out_slots <= 0) return fail("plan with output rows needs dev_out and out_slots");
+        if (h->world > 1 ? (dev_out != nullptr || out_slots <= 0) : (!dev_out || out_slots <= 0))
+            return fail(h->world > 1 ? "node-sharded plans write to the shared output region: dev_out must be NULL, out_slots > 0"
+                                     : "plan with output rows needs dev_out and out_slots");
         if (out_slots < std::min(batches_per_launch, n_batches))
             return fail("out_slots must cover one launch window");
     }
@@ -709,6 +780,7 @@ int zebra_tppr_epoch_begin(zebra_tppr_t *h, const int32_t *host_src, const int32
     for (int j = 0; j < h->n_tppr; ++j)
         if (!h->tables[j]) return fail("zebra_tppr_bind_tables has not been called");
     if (h->plan_active || h->epoch_active) return fail("another plan or epoch is in progress on this handle");
+    if (h->world > 1) return fail("node-sharded handles stream through plans (zebra_tppr_plan_run)");
     CU(cudaSetDevice(h->device));
     if (!h->copy_stream) CU(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
     zebra_epoch *ep = new zebra_epoch();
@@ -774,6 +846,110 @@ int zebra_tppr_epoch_end(zebra_epoch_t *ep)
 }
 
 int64_t zebra_tppr_epoch_slot_bytes(const zebra_epoch_t *ep) { return ep ? static_cast<int64_t>(ep->slot_bytes) : 0; }
+
+/* ---- node-sharded mode ---- */
+
+int zebra_tppr_shard_init(zebra_tppr_t *h, int32_t rank, int32_t world, int64_t max_window_edges, size_t out_bytes,
+                          void *ipc_handle_out)
+{
+    if (!h) return fail("null handle");
+    if (h->own_tables || h->arena) return fail("handle is already sharded");
+    if (world != 2 && world != 4 && world != 8) return fail("world must be 2, 4 or 8 (node v lives on rank v & (world-1))");
+    if (rank < 0 || rank >= world) return fail("rank out of range");
+    if (max_window_edges <= 0) return fail("max_window_edges must be positive");
+    CU(cudaSetDevice(h->device));
+    int lg = 0;
+    while ((1 << lg) < world) ++lg;
+    h->world = world; h->rank = rank; h->world_log2 = lg;
+    h->table_rows = (h->num_nodes + world - 1) >> lg;
+    for (int j = 0; j < h->n_tppr; ++j) {
+        h->tables[j] = nullptr;
+        CU(cudaMalloc(&h->tables[j], static_cast<size_t>(h->table_rows) * h->stride));
+        CU(cudaMemset(h->tables[j], 0, static_cast<size_t>(h->table_rows) * h->stride));
+    }
+    h->own_tables = true;
+    h->max_window_edges = max_window_edges;
+    h->mbox_half = static_cast<size_t>(max_window_edges) * h->n_tppr * h->stride;
+    h->out_region = (out_bytes + 255) & ~static_cast<size_t>(255);
+    CU(cudaMalloc(&h->arena, 2 * h->mbox_half + h->out_region));
+    CU(cudaMemset(h->arena, 0, 2 * h->mbox_half + h->out_region));
+    CU(cudaDeviceSynchronize());
+    h->peer_arena[rank] = h->arena;
+    int per_sm = 0, sms = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, zebra::tppr_span_shard_kernel, zebra::kWarpsPerBlock * 32, 0));
+    CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
+    h->shard_max_blocks = std::max(1, per_sm * sms);
+    if (ipc_handle_out) {
+        cudaIpcMemHandle_t mh;
+        CU(cudaIpcGetMemHandle(&mh, h->arena));
+        static_assert(sizeof(mh) == 64, "cudaIpcMemHandle_t is 64 bytes");
+        memcpy(ipc_handle_out, &mh, sizeof mh);
+    }
+    return 0;
+}
+
+int zebra_tppr_shard_connect(zebra_tppr_t *h, const void *ipc_handles)
+{
+    if (!h || !ipc_handles) return fail("null argument");
+    if (!h->arena) return fail("zebra_tppr_shard_init has not been called");
+    CU(cudaSetDevice(h->device));
+    for (int r = 0; r < h->world; ++r) {
+        if (r == h->rank || h->peer_arena[r]) continue;
+        cudaIpcMemHandle_t mh;
+        memcpy(&mh, static_cast<const char *>(ipc_handles) + 64 * r, sizeof mh);
+        void *ptr = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&ptr, mh, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) return fail("cudaIpcOpenMemHandle(rank %d): %s", r, cudaGetErrorString(e));
+        h->peer_arena[r] = static_cast<char *>(ptr);
+        h->peer_opened[r] = true;
+    }
+    return 0;
+}
+
+int zebra_tppr_shard_connect_local(zebra_tppr_t *h, zebra_tppr_t *const *ranks)
+{
+    if (!h || !ranks) return fail("null argument");
+    if (!h->arena) return fail("zebra_tppr_shard_init has not been called");
+    CU(cudaSetDevice(h->device));
+    for (int r = 0; r < h->world; ++r) {
+        const zebra_tppr *o = ranks[r];
+        if (!o || !o->arena || o->world != h->world || o->rank != r) return fail("rank %d: not a sharded handle of this world", r);
+        if (o->mbox_half != h->mbox_half || o->out_region != h->out_region) return fail("rank %d: arena geometry differs", r);
+        if (o->device != h->device) {
+            int can = 0;
+            CU(cudaDeviceCanAccessPeer(&can, h->device, o->device));
+            if (!can) return fail("device %d cannot access device %d", h->device, o->device);
+            cudaError_t e = cudaDeviceEnablePeerAccess(o->device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return fail("enable peer access: %s", cudaGetErrorString(e));
+            cudaGetLastError();
+        }
+        h->peer_arena[r] = o->arena;
+    }
+    return 0;
+}
+
+void *zebra_tppr_shard_out(zebra_tppr_t *h) { return (h && h->arena) ? h->arena + 2 * h->mbox_half : nullptr; }
+size_t zebra_tppr_shard_out_bytes(const zebra_tppr_t *h) { return h ? h->out_region : 0; }
+
+int zebra_tppr_shard_reset(zebra_tppr_t *h, void *stream)
+{
+    if (!h || !h->own_tables) return fail("not a sharded handle");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    CU(cudaSetDevice(h->device));
+    for (int j = 0; j < h->n_tppr; ++j)
+        CU(cudaMemsetAsync(h->tables[j], 0, static_cast<size_t>(h->table_rows) * h->stride, st));
+    CU(cudaMemsetAsync(h->rcnt, 0, sizeof(int32_t) * h->num_nodes * h->n_tppr, st));
+    h->plan_active = nullptr;
+    return 0;
+}
+
+int zebra_tppr_set_max_blocks(zebra_tppr_t *h, int32_t blocks)
+{
+    if (!h || blocks < 1) return fail("bad argument");
+    h->max_blocks = std::min(h->max_blocks, static_cast<int>(blocks));
+    if (h->shard_max_blocks) h->shard_max_blocks = std::min(h->shard_max_blocks, static_cast<int>(blocks));
+    return 0;
+}
 
 int zebra_tppr_sync_check(zebra_tppr_t *h, void *stream)
 {

@@ -33,6 +33,7 @@ namespace zebra {
 #endif
 
 constexpr int kMaxInst = 8;
+constexpr int kMaxRanks = 8;
 constexpr int kWarpsPerBlock = 8;
 constexpr unsigned kFull = 0xffffffffu;
 constexpr uint32_t kNear = 192;          // edges: closer than this to our turn -> poll the whole record
@@ -95,6 +96,11 @@ struct SpanParams {
     uint32_t *ticket;
     int32_t *status;        // [0] spin time-out flag, [1] exact-tie prunes, [2] merge-ranked prunes (statistics)
     unsigned long long *prof;   // [8] cycle sums per phase (ZEBRA_PROFILE builds)
+    // node-sharded mode (tppr_shard_device.cuh): node v lives on rank v & (world-1), local row v >> world_log2
+    int32_t world_log2, rank, mbox_parity, pad_;
+    int64_t mbox_half_bytes;                        // bytes of one parity half of a mailbox
+    char *mbox_peer[kMaxRanks];                     // every rank's mailbox (peer-mapped), own included
+    char *out_peer[kMaxRanks];                      // every rank's output region (peer-mapped), own included
 };
 
 struct alignas(16) WarpScratch {
@@ -125,10 +131,14 @@ __device__ __forceinline__ VecR vsel(bool c, const VecR &a, const VecR &b)
     return r;
 }
 
+template <bool kSys = false>
 __device__ __forceinline__ uint4 ld_chunk(const char *p)
 {
     uint4 v;
-    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    if (kSys)   // memory another GPU writes into (mailboxes of the node-sharded mode)
+        asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    else
+        asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
     return v;
 }
 
@@ -154,12 +164,13 @@ __device__ __forceinline__ int32_t ld_relaxed_s32(const int32_t *p)
 // One attempt to read a whole record.  `any`: the record has no writer earlier in this span, so it
 // is stable and any self-consistent content is the wanted version; otherwise every chunk must carry
 // `expect`.  `cur` returns the header tag seen (progress estimate for the back-off).
+template <bool kSys = false>
 __device__ __forceinline__ bool try_load(const char *rec, int k, int lane, bool any, uint32_t expect, VecR &v, uint32_t &cur)
 {
     const int l = lane < k ? lane : k - 1;
-    const uint4 h = ld_chunk(rec);
-    const uint4 a = ld_chunk(rec + 16 + 16 * l);
-    const uint4 b = ld_chunk(rec + 16 + 16 * (k + l));
+    const uint4 h = ld_chunk<kSys>(rec);
+    const uint4 a = ld_chunk<kSys>(rec + 16 + 16 * l);
+    const uint4 b = ld_chunk<kSys>(rec + 16 + 16 * (k + l));
     cur = h.w;
     const uint32_t want = any ? h.w : expect;
     const int cnt = static_cast<int>(h.z & ((1u << kCountBits) - 1));

@@ -1,0 +1,192 @@
+// tppr_shard_device.cuh — node-sharded variant of the span kernel: one process per GPU, T-PPR state
+// partitioned by node id, cross-shard endpoint vectors exchanged INSIDE the kernel through
+// peer-mapped mailboxes over NVLink (no collective call between waves, no host round trip).
+//
+// Ownership.  Node v lives on rank v & (world-1) at local row v >> log2(world).  A record is read
+// and written only by its owner's warps, so the single-GPU hand-off protocol (tagged records,
+// tppr_device.cuh) is unchanged and never crosses NVLink.
+//
+// Exchange.  Every rank walks the same replicated edge stream.  For edge i = (s, d, neg) an
+// endpoint's update needs the OLD vector of the other endpoint (utils/util.py:533-538).  If the
+// two endpoints have different owners, each owner, as soon as it holds the right version of its
+// endpoint, PUSHES that old vector from registers into the partner's mailbox slot of item (i, j)
+// (16-byte chunks tagged with the edge's sequence number, the same self-validating format as a
+// record) and then polls its OWN mailbox slot — local memory — for the partner's vector.  Nothing
+// is ever pulled over NVLink, and no version can be overwritten under a remote reader.
+//
+// Mailboxes are indexed by launch-local item and double-buffered by launch parity: a rank can run
+// at most one launch ahead of a peer that still has to read a slot (a rank finishing launch n needs
+// every peer's pushes of launch n, hence every peer has at least started launch n and finished n-1).
+//
+// Output rows (utils/util.py:447-469) are written by the owner of the node they describe, straight
+// into the output region of EVERY rank (peer stores), so after the launch each rank holds the
+// complete batch result, as data-parallel training needs it.
+#pragma once
+#include "tppr_device.cuh"
+
+namespace zebra {
+
+template <bool kSys>
+__device__ __forceinline__ void st_chunk_t(char *p, double d, int i, uint32_t tag)
+{
+    const unsigned long long b = static_cast<unsigned long long>(__double_as_longlong(d));
+    if (kSys)
+        asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(static_cast<uint32_t>(b)),
+                     "r"(static_cast<uint32_t>(b >> 32)), "r"(i), "r"(tag) : "memory");
+    else
+        st_chunk(p, d, i, tag);
+}
+
+// Copy of a vector held in registers into a mailbox slot of a peer (or of this rank, world = 1 tests).
+__device__ __forceinline__ void push_vector(char *slot, int k, const VecR &v, uint32_t tag, int lane)
+{
+    if (lane == 0) st_chunk_t<true>(slot, v.norm, v.cnt | (v.upd << kCountBits), tag);
+    if (lane < v.cnt) {
+        st_chunk_t<true>(slot + 16 + 16 * lane, v.sc, v.e, tag);
+        st_chunk_t<true>(slot + 16 + 16 * (k + lane), v.ts, v.n, tag);
+    }
+}
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
+{
+    __shared__ WarpScratch scratch[kWarpsPerBlock];
+    const int lane = threadIdx.x & 31;
+    WarpScratch &s = scratch[threadIdx.x >> 5];
+    const unsigned long long total = static_cast<unsigned long long>(p.n_chunk) * p.n_tppr;
+    const int k = p.k;
+    const uint32_t tag_base = p.seq0 + static_cast<uint32_t>(p.tag_offset);
+    const int lg = p.world_log2, me = p.rank, pmask = (1 << lg) - 1, world = 1 << lg;
+    char *const my_mbox = p.mbox_peer[me] + static_cast<size_t>(p.mbox_parity) * p.mbox_half_bytes;
+
+    for (;;) {
+        uint32_t tk = 0;
+        if (lane == 0) tk = atomicAdd(p.ticket, 1u) - p.ticket_base;
+        tk = __shfl_sync(kFull, tk, 0);
+        if (tk >= total) break;
+        const int64_t i = tk / p.n_tppr;
+        const int j = tk - i * p.n_tppr;
+        if (!((p.inst_mask >> j) & 1)) continue;
+        const int sN = p.src[i], dN = p.dst[i];
+        const bool has_neg = p.rows_per_edge == 3;
+        const int gN = has_neg ? p.neg[i] : sN;
+        const bool loop = sN == dN;
+        const bool neg_own = has_neg && gN != sN && gN != dN;
+        const bool oS = (sN & pmask) == me, oD = loop ? oS : (dN & pmask) == me;
+        const bool oG = neg_own && (gN & pmask) == me;
+        if (!(oS || oD || oG)) continue;          // nothing of this edge lives here
+        const uint32_t flags = p.flags[i];
+        int32_t *rcnt = p.rcnt[j];
+        const int32_t pS = p.prev_s[i], pD = loop ? -1 : p.prev_d[i], pG = neg_own ? p.prev_n[i] : -1;
+        char *table = p.tables[j];
+        char *recS = table + static_cast<size_t>(sN >> lg) * p.stride;
+        char *recD = table + static_cast<size_t>(dN >> lg) * p.stride;
+        const char *recG = table + static_cast<size_t>(gN >> lg) * p.stride;
+        const uint32_t my_tag = tag_base + static_cast<uint32_t>(i);
+        const double t = p.ts[i];
+        const int e = p.eidx[i];
+        const uint32_t rwS = p.rthr_s[i], rwD = loop ? 0u : p.rthr_d[i];
+
+        const bool needSD = oS || oD;
+        const bool cross = needSD && !(oS && oD);              // the other endpoint lives on another rank
+        const size_t slot_off = (static_cast<size_t>(i) * p.n_tppr + j) * p.stride;
+        const char *mslot = my_mbox + slot_off;                 // partner's push for this item lands here
+        char *pslot = nullptr;
+        if (cross) {
+            const int partner = (oS ? dN : sN) & pmask;
+            pslot = p.mbox_peer[partner] + static_cast<size_t>(p.mbox_parity) * p.mbox_half_bytes + slot_off;
+        }
+
+        VecR S, D, G;
+        S.e = S.n = S.cnt = S.upd = 0; S.ts = S.sc = S.norm = 0.0;
+        D = S; G = S;
+        uint32_t curS = 0, curD = 0, curG = 0;
+        bool okS = !needSD, okD = !needSD || loop, okG = !oG;
+        bool pushed = !cross, alive = true;
+        unsigned spins = 0;
+        for (;;) {
+            if (!okS) okS = oS ? try_load<false>(recS, k, lane, pS < 0, p.seq0 + static_cast<uint32_t>(pS), S, curS)
+                               : try_load<true>(mslot, k, lane, false, my_tag, S, curS);
+            if (!okD) okD = oD ? try_load<false>(recD, k, lane, pD < 0, p.seq0 + static_cast<uint32_t>(pD), D, curD)
+                               : try_load<true>(mslot, k, lane, false, my_tag, D, curD);
+            if (!okG) okG = try_load<false>(recG, k, lane, pG < 0, p.seq0 + static_cast<uint32_t>(pG), G, curG);
+            if (!pushed && (oS ? okS : okD)) {      // our endpoint's OLD vector is here: send it before computing
+                push_vector(pslot, k, oS ? S : D, my_tag, lane);
+                pushed = true;
+            }
+            if (okS && okD) break;
+            // back off while the local producer is far away (same estimate as the single-GPU kernel)
+            uint32_t dist = 0;
+            if (!okS && oS) {
+                const uint32_t d = curS - tag_base, pe = static_cast<uint32_t>(pS - p.tag_offset);
+                dist = (d < static_cast<uint32_t>(p.n_chunk) && d <= pe) ? pe - d : pe + 1;
+            }
+            if (!okD && oD) {
+                const uint32_t d = curD - tag_base, pe = static_cast<uint32_t>(pD - p.tag_offset);
+                const uint32_t dd = (d < static_cast<uint32_t>(p.n_chunk) && d <= pe) ? pe - d : pe + 1;
+                dist = dd > dist ? dd : dist;
+            }
+            if (dist > kNear) __nanosleep(backoff_ns(dist));
+            else if ((!okS && !oS) || (!okD && !oD)) __nanosleep(100);   // waiting for a peer's push
+            if ((++spins & 0xff) == 0) {
+                if (*reinterpret_cast<volatile int32_t *>(p.status) != 0) { alive = false; break; }
+                if (spins > (1u << 22)) { atomicExch(p.status, 1); alive = false; break; }
+            }
+        }
+        if (!alive) continue;
+        if (loop) D = vsel(true, S, S);
+        if (!neg_own) G = vsel(gN == sN, S, D);
+        bool sigG = okG;
+        if (okG && oG && (flags & kFlagSignal) && lane == 0) atomicAdd(rcnt + gN, 1);
+
+        bool ok = true;
+        if (needSD) {
+            const bool df = (flags & kFlagDstFirst) && !loop;
+#pragma unroll 1
+            for (int h = 0; h < (loop ? 1 : 2); ++h) {
+                const bool isD = (h == 0) ? df : !df;
+                if (!(isD ? oD : oS)) continue;
+                const VecR A = vsel(isD, D, S), B = vsel(isD, S, D);
+                ok &= update_endpoint(p, s, A, B, isD ? sN : dN, e, t, j, isD ? recD : recS, my_tag,
+                                      rcnt + (isD ? dN : sN), isD ? rwD : rwS, lane);
+            }
+        }
+        if (!ok) { atomicExch(p.status, 1); continue; }
+
+        while (!okG) {
+            __nanosleep(64);
+            okG = try_load<false>(recG, k, lane, pG < 0, p.seq0 + static_cast<uint32_t>(pG), G, curG);
+            if ((++spins & 0xff) == 0) {
+                if (*reinterpret_cast<volatile int32_t *>(p.status) != 0) break;
+                if (spins > (1u << 22)) { atomicExch(p.status, 1); break; }
+            }
+        }
+        if (!okG) continue;
+        if (!sigG && oG && (flags & kFlagSignal) && lane == 0) atomicAdd(rcnt + gN, 1);
+
+        if (p.rows_per_edge >= 2) {
+            int64_t row = p.i_offset + i, nrow = p.n_total;
+            size_t off = 0;
+            if (p.batch_size > 0) {
+                const int64_t b = row / p.batch_size;
+                row -= b * p.batch_size;
+                nrow = p.n_total - b * p.batch_size;
+                if (nrow > p.batch_size) nrow = p.batch_size;
+                off = static_cast<size_t>((b - p.first_batch) % p.out_slots) * p.slot_bytes;
+            }
+            const size_t plane = static_cast<size_t>(nrow) * p.rows_per_edge * k;
+            off += static_cast<size_t>(j) * plane * 16;
+            // a row is written by the owner of the node it describes, into every rank's output region
+            const bool eS = oS, eD = oD;
+            const bool eG = has_neg && (neg_own ? oG : (gN == sN ? oS : oD));
+            for (int q = 0; q < world; ++q) {
+                char *obase = p.out_peer[q] + off;
+                if (eS) emit_row(p, obase, plane, row, S, t, lane);
+                if (eD) emit_row(p, obase, plane, row + nrow, D, t, lane);
+                if (eG) emit_row(p, obase, plane, row + 2 * nrow, G, t, lane);
+            }
+        }
+    }
+}
+
+}  // namespace zebra
