@@ -161,6 +161,156 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def run_sharded(args, torch, dist, world, rank, local, dev):
+    """N > 1: T-PPR state partitioned by node id over the N GPUs (zebra_b200/sharded.py).  Every rank
+    walks the same replicated edge stream; the span kernel pushes cross-shard old vectors through
+    peer-mapped mailboxes over NVLink and stores every output row into every rank's output region.
+
+    Weak scaling (the `value`): the graph grows with N — N wikitalk-shaped communities (N x nodes,
+    N x edges, hub degrees of one community), each spread over all ranks, so (N-1)/N of the edges
+    cross shards.  Strong scaling (extra key `strong`): the N=1 stream itself sharded over N GPUs;
+    its hottest node's dependency chain is as long as on one GPU, so it cannot speed up."""
+    from zebra_b200 import synth
+    from zebra_b200.sharded import create_sharded, exchange_stats
+    window = args.batches_per_launch
+    slot = len(ALPHAS) * 16 * 3 * BS * K
+    main = torch.cuda.current_stream()
+    copy_stream = torch.cuda.Stream()
+
+    def barrier():
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    def measure(st, neg, sampler=None, e2e=True):
+        E, N = st.n_edges, st.shape.table_nodes
+        f = create_sharded(N, K, len(ALPHAS), ALPHAS, BETAS, window * BS, 2 * window * slot)
+        plan = f.make_plan(st.src, st.dst, neg, st.ts, st.eidx, BS)
+        n_win = -(-plan.n_batches // window)
+
+        def step():
+            f.reset_tppr()                       # no barrier needed: records are touched by their owner only
+            plan.run(0, plan.n_batches, window, out_slots=window)
+
+        for _ in range(args.warmup):
+            step()
+        f.sync_check()
+        if sampler is not None:
+            sampler.start()
+        barrier()
+        l0 = f.counters()["launches"]
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        ev[0].record()
+        for _ in range(args.steps):
+            step()
+        ev[1].record()
+        barrier()
+        f.sync_check()
+        ms = ev[0].elapsed_time(ev[1])
+        launches = f.counters()["launches"] - l0
+        res = {"E": E, "N": N, "ms": ms, "launches": launches, "n_launch": n_win, "n_batches": plan.n_batches,
+               "record_bytes": f._record_bytes}
+        if e2e:
+            # end to end: host arrays in (dependency pass + H2D of the replicated span on every rank), the
+            # complete rows of every batch back in pinned host memory on EVERY rank.  Per window: kernel,
+            # a one-element all-reduce as cross-rank completion (plumbing, not data), D2H on a second stream.
+            pinned = [torch.empty(window * slot, dtype=torch.uint8).pin_memory() for _ in range(2)]
+            flag = torch.zeros(1, device=dev)
+            ev_ready = [torch.cuda.Event() for _ in range(2)]
+            ev_copy = [torch.cuda.Event() for _ in range(2)]
+
+            def e2e_pass():
+                pl = f.make_plan(st.src, st.dst, neg, st.ts, st.eidx, BS)
+                f.reset_tppr()
+                acc = 0.0
+                for w in range(n_win):
+                    h, b0 = w & 1, w * window
+                    nb = min(window, pl.n_batches - b0)
+                    pl.run(b0, nb, window, out_slots=window, out_offset=h * window * slot)
+                    if w >= 1:
+                        main.wait_event(ev_copy[(w - 1) & 1])   # this rank has drained the other half ...
+                    dist.all_reduce(flag)                       # ... and so has everybody once this completes
+                    ev_ready[h].record(main)
+                    if w >= 2:
+                        acc += float(pinned[h][0])              # host consumes window w-2 before its buffer is reused
+                    with torch.cuda.stream(copy_stream):
+                        copy_stream.wait_event(ev_ready[h])
+                        pinned[h][: nb * slot].copy_(f.out[h * window * slot: h * window * slot + nb * slot], non_blocking=True)
+                        ev_copy[h].record(copy_stream)
+                    if w >= 1:
+                        ev_copy[(w - 1) & 1].synchronize()
+                ev_copy[(n_win - 1) & 1].synchronize()
+                f.sync_check()
+                pl.close()
+                return acc
+
+            e2e_pass()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                e2e_pass()
+            barrier()
+            res["e2e_s"] = time.perf_counter() - t0
+        t = torch.tensor([res["ms"], res.get("e2e_s", 0.0)], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        res["ms"], res["e2e_s"] = float(t[0]), float(t[1])
+        res["tie_prunes"] = f.counters()["tie_prunes"]
+        plan.close()
+        f.disconnect()
+        barrier()
+        f.close()
+        return res
+
+    sampler = ClockSampler(local)
+    st, neg = synth.make_communities(WORKLOAD, world, BS, n_edges=args.edges)
+    xs = exchange_stats(st.src, st.dst, neg, world, K, len(ALPHAS))
+    weak = measure(st, neg, sampler if rank == 0 else None)
+    clocks = sampler.stop() if rank == 0 else None
+    del st, neg
+    strong = None
+    if not args.no_strong:
+        st1, neg1 = load_workload(n_edges=args.edges)
+        strong = measure(st1, neg1, e2e=False)
+        strong["exchange"] = exchange_stats(st1.src, st1.dst, neg1, world, K, len(ALPHAS))
+    if rank != 0:
+        return
+    peak, peak_src = peaks()
+    E, ms = weak["E"], weak["ms"]
+    value = E * args.steps / (ms * 1e-3)
+    per_launch_ms = ms / max(weak["launches"], 1)
+    achieved = E * bytes_per_edge() / weak["n_launch"] / (per_launch_ms * 1e-3) / 1e9
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"{world} {WORKLOAD}-shaped communities merged into one stream ({weak['N'] - 1} nodes, {E} edges; per GPU "
+                               f"{(weak['N'] - 1) // world} nodes of state), streaming T-PPR topk={K}, alpha {ALPHAS}, beta {BETAS}, bs={BS}, "
+                               f"negatives included",
+                   "step": "reset tables + stream the whole span once",
+                   "batches_per_launch": window,
+                   "parallelism": f"node-sharded x{world}: owner = id & {world - 1}; cross-shard old vectors pushed through peer-mapped "
+                                  f"mailboxes inside the span kernel (NVLink stores), rows stored into every rank's output region; "
+                                  f"no collective on the data path",
+                   "exchange": xs,
+                   "l2": f"per-GPU tables {len(ALPHAS) * ((weak['N'] + world - 1) // world) * weak['record_bytes'] / 1e6:.0f} MB + "
+                         f"outputs exceed the 126 MB L2 (inputs larger than L2)",
+                   "tie_path_prunes_last_step_rank0": weak["tie_prunes"]},
+        "e2e": {"value": E * args.steps / weak["e2e_s"], "unit": UNIT,
+                "h2d_bytes_per_step": world * ((E + 7) // 8 * 8) * 48, "d2h_bytes_per_step": world * len(ALPHAS) * 16 * 3 * E * K,
+                "step": f"per rank: plan built from host arrays (dependency pass + H2D of the replicated span), sharded run in windows of "
+                        f"{window} batches, complete rows of every batch copied to pinned host memory on every rank"},
+        "gpu_launches": weak["launches"] * world,
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak * world, "unit": "GB/s", "frac": achieved / (peak * world),
+                     "traffic": None, "peak_source": peak_src + f" x {world} GPUs", "kernel": "tppr_span_shard_kernel",
+                     "bytes_per_edge": bytes_per_edge(), "launch_ms": per_launch_ms},
+    }
+    if strong is not None:
+        line["strong"] = {"what": f"the N=1 workload ({strong['E']} edges, one community) node-sharded over {world} GPUs",
+                          "value": strong["E"] * args.steps / (strong["ms"] * 1e-3), "unit": UNIT,
+                          "ms_per_step": strong["ms"] / args.steps, "exchange": strong["exchange"]}
+    print(json.dumps(line), flush=True)
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -173,6 +323,10 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+        if args.mode == "sharded":
+            run_sharded(args, torch, dist, world, rank, local, dev)
+            dist.destroy_process_group()
+            return
 
     # every rank streams its own replica of the workload (different seed): weak scaling, no exchange
     st, neg = load_workload(n_edges=args.edges, seed=None if rank == 0 else 1005 + 100 * rank)
@@ -311,6 +465,9 @@ def main():
     ap.add_argument("--ref-sample-edges", type=int, default=1_000_000)
     ap.add_argument("--traffic", type=float, default=None, help="ncu dram bytes per launch, if captured")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--mode", default="sharded", choices=["sharded", "replicas"],
+                    help="N>1: node-sharded state with in-kernel NVLink exchange (default), or independent replicas")
+    ap.add_argument("--no-strong", action="store_true", help="N>1: skip the strong-scaling leg (same stream as N=1, sharded)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -155,7 +155,8 @@ int64_t zebra_tppr_epoch_slot_bytes(const zebra_epoch_t *epoch);
  *
  * Sharded handles stream through plans only (dependencies must be global to the span): every rank
  * builds the same plan from the same replicated edge arrays and calls zebra_tppr_plan_run with
- * dev_out = NULL and the same arguments.  A launch may cover at most max_window_edges edges.  Rows
+ * the same arguments; dev_out is then a byte OFFSET into the shared output region (NULL = 0), not
+ * a pointer.  A launch may cover at most max_window_edges edges.  Rows
  * are written by the owner of the node they describe into the output region of EVERY rank at the
  * plan-run slot offsets; after all ranks have synchronised their streams and met at a barrier, each
  * rank's zebra_tppr_shard_out() holds the complete result, byte-identical to the single-GPU one.
@@ -166,6 +167,9 @@ int zebra_tppr_shard_init(zebra_tppr_t *h, int32_t rank, int32_t world, int64_t 
                           size_t out_bytes, void *ipc_handle_out);
 int zebra_tppr_shard_connect(zebra_tppr_t *h, const void *ipc_handles);
 int zebra_tppr_shard_connect_local(zebra_tppr_t *h, zebra_tppr_t *const *ranks);
+/* Unmaps the peers' arenas; every rank calls it (then meets at a barrier) BEFORE any rank destroys
+ * its handle, so that no arena is freed while a peer still has it mapped. */
+int zebra_tppr_shard_disconnect(zebra_tppr_t *h);
 void *zebra_tppr_shard_out(zebra_tppr_t *h);
 size_t zebra_tppr_shard_out_bytes(const zebra_tppr_t *h);
 int zebra_tppr_shard_reset(zebra_tppr_t *h, void *stream);

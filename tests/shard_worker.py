@@ -55,6 +55,8 @@ def main():
     if rank == 0:
         print("exchange:", exchange_stats(st.src, st.dst, neg, world, k, 2), flush=True)
     print(f"SHARD_OK rank {rank}/{world} kernel_ms {f.last_kernel_ms():.2f} {f.counters()}", flush=True)
+    f.disconnect()
+    dist.barrier()
     f.close()
     dist.destroy_process_group()
 

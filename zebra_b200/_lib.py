@@ -32,6 +32,7 @@ SIGNATURES = {
     "zebra_tppr_shard_init": (C.c_int, [_VP, _I32, _I32, _I64, C.c_size_t, _VP]),
     "zebra_tppr_shard_connect": (C.c_int, [_VP, _VP]),
     "zebra_tppr_shard_connect_local": (C.c_int, [_VP, _VP]),
+    "zebra_tppr_shard_disconnect": (C.c_int, [_VP]),
     "zebra_tppr_shard_out": (_VP, [_VP]),
     "zebra_tppr_shard_out_bytes": (C.c_size_t, [_VP]),
     "zebra_tppr_shard_reset": (C.c_int, [_VP, _VP]),

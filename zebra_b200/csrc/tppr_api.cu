@@ -310,20 +310,22 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
     if (blocks < 1) blocks = 1;
     if (sharded) {
         if (m > h->max_window_edges) return fail("sharded launch of %lld edges exceeds the mailbox window (%lld)", (long long)m, (long long)h->max_window_edges);
-        if (out) return fail("node-sharded mode writes rows to the shared output region: dev_out must be NULL");
+        const size_t out_off = reinterpret_cast<size_t>(out);   // sharded: dev_out carries a byte OFFSET into the region
+        if (out_off % 16) return fail("output offset must be a multiple of 16");
         for (int r = 0; r < h->world; ++r)
             if (!h->peer_arena[r]) return fail("zebra_tppr_shard_connect has not been called");
         if (rows_per_edge) {
             const size_t need = bo.batch_size > 0 ? static_cast<size_t>(bo.out_slots) * bo.slot_bytes
                                                   : zebra_tppr_out_bytes(h, n_total, rows_per_edge);
-            if (need > h->out_region) return fail("output of %zu bytes exceeds the shared output region (%zu)", need, h->out_region);
+            if (need + out_off > h->out_region) return fail("output of %zu bytes at offset %zu exceeds the shared output region (%zu)", need, out_off, h->out_region);
         }
         p.world_log2 = h->world_log2; p.rank = h->rank; p.mbox_parity = h->launch_parity;
         p.mbox_half_bytes = static_cast<int64_t>(h->mbox_half);
         for (int r = 0; r < h->world; ++r) {
             p.mbox_peer[r] = h->peer_arena[r];
-            p.out_peer[r] = h->peer_arena[r] + 2 * h->mbox_half;
+            p.out_peer[r] = h->peer_arena[r] + 2 * h->mbox_half + out_off;
         }
+        p.out = nullptr;
         h->launch_parity ^= 1;
         zebra::tppr_span_shard_kernel<<<blocks, zebra::kWarpsPerBlock * 32, 0, st>>>(p);
     } else {
@@ -684,9 +686,7 @@ int zebra_tppr_plan_run(zebra_tppr_t *h, zebra_plan_t *pl, int64_t first_batch, 
     if (h->plan_active != pl || h->plan_next != first_batch)
         return fail("plan batches must run in order starting from 0 (next expected %lld)", (long long)h->plan_next);
     if (pl->rows_per_edge) {
-        if (h->world > 1 ? (dev_out != nullptr || out_slots <= 0) : (!dev_out || out_slots <= 0))
-            return fail(h->world > 1 ? "node-sharded plans write to the shared output region: dev_out must be NULL, out_slots > 0"
-                                     : "plan with output rows needs dev_out and out_slots");
+        if (out_slots <= 0 || (h->world == 1 && !dev_out)) return fail("plan with output rows needs dev_out and out_slots");
         if (out_slots < std::min(batches_per_launch, n_batches))
             return fail("out_slots must cover one launch window");
     }
@@ -924,6 +924,20 @@ int zebra_tppr_shard_connect_local(zebra_tppr_t *h, zebra_tppr_t *const *ranks)
             cudaGetLastError();
         }
         h->peer_arena[r] = o->arena;
+    }
+    return 0;
+}
+
+int zebra_tppr_shard_disconnect(zebra_tppr_t *h)
+{
+    if (!h) return 0;
+    cudaSetDevice(h->device);
+    cudaDeviceSynchronize();
+    for (int r = 0; r < zebra::kMaxRanks; ++r) {
+        if (r == h->rank) continue;
+        if (h->peer_opened[r] && h->peer_arena[r]) cudaIpcCloseMemHandle(h->peer_arena[r]);
+        h->peer_arena[r] = nullptr;
+        h->peer_opened[r] = false;
     }
     return 0;
 }

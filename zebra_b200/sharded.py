@@ -162,6 +162,11 @@ class ShardedFinder:
     def last_kernel_ms(self):
         return float(self._L.zebra_tppr_last_kernel_ms(self._h))
 
+    def disconnect(self):
+        """Unmap the peers' arenas.  Multi-process teardown: every rank disconnects, barrier, close."""
+        if getattr(self, "_h", None):
+            self._check(self._L.zebra_tppr_shard_disconnect(self._h))
+
     def close(self):
         if getattr(self, "_h", None):
             self.out = None
@@ -181,7 +186,8 @@ def _make_sharded_plan_class():
     class ShardedPlan(StreamPlan):
         """StreamPlan whose rows land in the shared output region of every rank (finder.out)."""
 
-        def run(self, first=0, n_batches=None, batches_per_launch=1, out=None, out_slots=None):
+        def run(self, first=0, n_batches=None, batches_per_launch=1, out=None, out_slots=None, out_offset=0):
+            """Rows go to slot (b - first) % out_slots of finder.out[out_offset:] on EVERY rank."""
             import torch
             if out is not None:
                 raise ValueError("sharded plans write to finder.out")
@@ -192,9 +198,9 @@ def _make_sharded_plan_class():
                 out_slots = min(batches_per_launch, n_batches)
             f = self.f
             with torch.cuda.device(f.device):
-                f._check(f._L.zebra_tppr_plan_run(f._h, self._p, first, n_batches, batches_per_launch, None, out_slots,
-                                                  f._stream_ptr()))
-            return f.out
+                f._check(f._L.zebra_tppr_plan_run(f._h, self._p, first, n_batches, batches_per_launch,
+                                                  C.c_void_p(int(out_offset)) if out_offset else None, out_slots, f._stream_ptr()))
+            return f.out[int(out_offset):] if out_offset else f.out
 
     return ShardedPlan
 

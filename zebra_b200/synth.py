@@ -215,3 +215,34 @@ def wave_stats(src: np.ndarray, dst: np.ndarray, neg: np.ndarray | None = None) 
         last_w[d] = lvl
         depth = max(depth, lvl + 1)
     return {"edges": len(src), "depth": depth, "mean_width": len(src) / max(depth, 1)}
+
+
+def make_communities(name: str, n_comm: int, batch_size: int, n_edges: int | None = None):
+    """Weak-scaling workload: `n_comm` independent streams of shape `name` (different seeds) merged
+    into one chronological stream over n_comm x the nodes.  Community c's node v becomes
+    1 + c*n_nodes + (v-1), so every community is spread over all ranks of a node-sharded run
+    (owner = id & (world-1)) and a fraction (world-1)/world of its edges crosses shards.  The hub
+    degrees stay those of one community while nodes and edges grow n_comm-fold.
+    Returns (Stream, negatives); negatives are drawn per community like make_negatives."""
+    shape = SHAPES[name]
+    parts, negs = [], []
+    for c in range(n_comm):
+        st = make_stream(name, seed=SEEDS.get(name, 1000) + 100 * c, n_edges=n_edges)
+        ng = make_negatives(st, batch_size, seed=7 + c)
+        off = c * shape.n_nodes
+        parts.append((st.src + off, st.dst + off, st.ts))
+        negs.append(ng + off)
+    if n_comm == 1:
+        st = make_stream(name, n_edges=n_edges)
+        return st, negs[0]
+    src = np.concatenate([p[0] for p in parts])
+    dst = np.concatenate([p[1] for p in parts])
+    ts = np.concatenate([p[2] for p in parts])
+    neg = np.concatenate(negs)
+    order = np.argsort(ts, kind="stable")
+    src, dst, ts, neg = src[order].astype(np.int32), dst[order].astype(np.int32), ts[order], neg[order].astype(np.int32)
+    E = len(src)
+    big = dataclasses.replace(shape, name=f"{name}x{n_comm}", n_users=shape.n_users * n_comm, n_items=shape.n_items * n_comm,
+                              n_edges=E)
+    return Stream(shape=big, src=src, dst=dst, ts=ts, eidx=np.arange(1, E + 1, dtype=np.int64),
+                  dst_pool=np.unique(dst).astype(np.int32)), neg
