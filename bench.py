@@ -172,7 +172,9 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
     its hottest node's dependency chain is as long as on one GPU, so it cannot speed up."""
     from zebra_b200 import synth
     from zebra_b200.sharded import create_sharded, exchange_stats
-    window = args.batches_per_launch
+    # batches per launch grow with N so that one launch holds as much work per community as at N=1
+    # (every launch boundary drains all dependency chains on all ranks)
+    window = args.batches_per_launch * world
     slot = len(ALPHAS) * 16 * 3 * BS * K
     main = torch.cuda.current_stream()
     copy_stream = torch.cuda.Stream()

@@ -111,6 +111,10 @@ struct zebra_plan {
     char *dev = nullptr;
     size_t cap = 0;
     uint32_t seq0 = 0;                          // tag base of the run in progress
+    // node-sharded handles: span indices of the edges this rank takes part in, and for every batch the
+    // position in that list of its first edge
+    int32_t *dev_list = nullptr;
+    std::vector<int64_t> batch_ofs;
 };
 
 // A pipelined pass over a host-resident span: windows of whole batches are staged, computed and
@@ -281,7 +285,7 @@ int prepare_chunk(zebra_tppr *h, Staging &s, const NodeT *src, const NodeT *dst,
 // Launches the span kernel over m edges whose SoA arrays (stride `cap`) start at `dev`+`lo`.
 int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_t m, int64_t n_total, int64_t i_offset,
                   int32_t rows_per_edge, int32_t inst_mask, char *out, const BatchOut &bo, uint32_t seq0, int64_t tag_offset,
-                  cudaStream_t st)
+                  cudaStream_t st, const int32_t *list = nullptr, int64_t n_list = 0)
 {
     zebra::SpanParams p;
     memset(&p, 0, sizeof p);
@@ -303,8 +307,10 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
     }
     p.out = out; p.ticket = h->ticket; p.status = h->status; p.prof = h->prof;
     p.batch_size = bo.batch_size; p.first_batch = bo.first_batch; p.out_slots = bo.out_slots; p.slot_bytes = bo.slot_bytes;
-    const int64_t items = m * h->n_tppr;
     const bool sharded = h->world > 1;
+    if (sharded && !list) return fail("node-sharded launch without a work list");
+    p.list = list; p.n_list = n_list;
+    const int64_t items = (sharded ? n_list : m) * h->n_tppr;
     int blocks = static_cast<int>(std::min<int64_t>((items + zebra::kWarpsPerBlock - 1) / zebra::kWarpsPerBlock,
                                                     sharded ? h->shard_max_blocks : h->max_blocks));
     if (blocks < 1) blocks = 1;
@@ -643,10 +649,32 @@ int zebra_tppr_plan_create(zebra_tppr_t *h, const int32_t *host_src, const int32
         delete pl;
         return 1;
     }
+    std::vector<int32_t> list;
+    if (h->world > 1) {
+        const int32_t pm = h->world - 1, me = h->rank;
+        pl->batch_ofs.assign(static_cast<size_t>(pl->n_batches) + 1, 0);
+        list.reserve(static_cast<size_t>(n / h->world) * 2 + 16);
+        for (int64_t i = 0; i < n; ++i) {
+            if (i % batch_size == 0) pl->batch_ofs[static_cast<size_t>(i / batch_size)] = static_cast<int64_t>(list.size());
+            const int32_t a = host_src[i], b = host_dst[i];
+            bool mine = (a & pm) == me || (b & pm) == me;
+            if (!mine && rows_per_edge == 3) {
+                const int32_t g = host_neg[i];
+                mine = g != a && g != b && (g & pm) == me;
+            }
+            if (mine) list.push_back(static_cast<int32_t>(i));
+        }
+        pl->batch_ofs[static_cast<size_t>(pl->n_batches)] = static_cast<int64_t>(list.size());
+    }
     cudaError_t e = cudaMalloc(&pl->dev, pl->cap * kEdgeBytes);
     if (e == cudaSuccess) e = cudaMemcpy(pl->dev, host.data(), pl->cap * kEdgeBytes, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && h->world > 1) {
+        e = cudaMalloc(&pl->dev_list, std::max<size_t>(list.size(), 1) * sizeof(int32_t));
+        if (e == cudaSuccess) e = cudaMemcpy(pl->dev_list, list.data(), list.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
+    }
     if (e != cudaSuccess) {
         if (pl->dev) cudaFree(pl->dev);
+        if (pl->dev_list) cudaFree(pl->dev_list);
         delete pl;
         return fail("plan upload failed: %s", cudaGetErrorString(e));
     }
@@ -659,6 +687,7 @@ int zebra_tppr_plan_destroy(zebra_plan_t *pl)
     if (!pl) return 0;
     if (pl->h && pl->h->plan_active == pl) pl->h->plan_active = nullptr;
     if (pl->dev) { cudaSetDevice(pl->h->device); cudaDeviceSynchronize(); cudaFree(pl->dev); }
+    if (pl->dev_list) cudaFree(pl->dev_list);
     delete pl;
     return 0;
 }
@@ -700,8 +729,14 @@ int zebra_tppr_plan_run(zebra_tppr_t *h, zebra_plan_t *pl, int64_t first_batch, 
     for (int64_t b = first_batch; b < last; b += batches_per_launch) {
         const int64_t be = std::min(last, b + batches_per_launch);
         const int64_t lo = b * pl->batch_size, hi = std::min(pl->n, be * pl->batch_size);
+        const int32_t *list = nullptr;
+        int64_t n_list = 0;
+        if (h->world > 1) {
+            list = pl->dev_list + pl->batch_ofs[static_cast<size_t>(b)];
+            n_list = pl->batch_ofs[static_cast<size_t>(be)] - pl->batch_ofs[static_cast<size_t>(b)];
+        }
         if (launch_kernel(h, pl->dev, pl->cap, lo, hi - lo, pl->n, lo, pl->rows_per_edge, (1 << h->n_tppr) - 1,
-                          static_cast<char *>(dev_out), bo, pl->seq0, lo, st)) return 1;
+                          static_cast<char *>(dev_out), bo, pl->seq0, lo, st, list, n_list)) return 1;
     }
     CU(cudaEventRecord(h->ev1, st));
     h->timed = true;

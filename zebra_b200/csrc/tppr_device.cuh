@@ -98,6 +98,8 @@ struct SpanParams {
     unsigned long long *prof;   // [8] cycle sums per phase (ZEBRA_PROFILE builds)
     // node-sharded mode (tppr_shard_device.cuh): node v lives on rank v & (world-1), local row v >> world_log2
     int32_t world_log2, rank, mbox_parity, pad_;
+    const int32_t *list;                            // sharded: span indices of the edges this rank takes part in (this launch's range)
+    int64_t n_list;
     int64_t mbox_half_bytes;                        // bytes of one parity half of a mailbox
     char *mbox_peer[kMaxRanks];                     // every rank's mailbox (peer-mapped), own included
     char *out_peer[kMaxRanks];                      // every rank's output region (peer-mapped), own included

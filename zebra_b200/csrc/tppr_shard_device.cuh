@@ -14,6 +14,9 @@
 // record) and then polls its OWN mailbox slot — local memory — for the partner's vector.  Nothing
 // is ever pulled over NVLink, and no version can be overwritten under a remote reader.
 //
+// Work list.  The host gives every rank the (sorted) list of edges it takes part in — it owns src,
+// dst or a distinct negative — and the tickets run over that list only.
+//
 // Mailboxes are indexed by launch-local item and double-buffered by launch parity: a rank can run
 // at most one launch ahead of a peer that still has to read a slot (a rank finishing launch n needs
 // every peer's pushes of launch n, hence every peer has at least started launch n and finished n-1).
@@ -53,7 +56,9 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
     __shared__ WarpScratch scratch[kWarpsPerBlock];
     const int lane = threadIdx.x & 31;
     WarpScratch &s = scratch[threadIdx.x >> 5];
-    const unsigned long long total = static_cast<unsigned long long>(p.n_chunk) * p.n_tppr;
+    // tickets run over this rank's own list of edges (built by the host from the ownership rule), so
+    // edges that do not touch this shard cost nothing here
+    const unsigned long long total = static_cast<unsigned long long>(p.n_list) * p.n_tppr;
     const int k = p.k;
     const uint32_t tag_base = p.seq0 + static_cast<uint32_t>(p.tag_offset);
     const int lg = p.world_log2, me = p.rank, pmask = (1 << lg) - 1, world = 1 << lg;
@@ -64,9 +69,10 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
         if (lane == 0) tk = atomicAdd(p.ticket, 1u) - p.ticket_base;
         tk = __shfl_sync(kFull, tk, 0);
         if (tk >= total) break;
-        const int64_t i = tk / p.n_tppr;
-        const int j = tk - i * p.n_tppr;
+        const int64_t li = tk / p.n_tppr;
+        const int j = tk - li * p.n_tppr;
         if (!((p.inst_mask >> j) & 1)) continue;
+        const int64_t i = static_cast<int64_t>(p.list[li]) - p.i_offset;     // launch-local edge index
         const int sN = p.src[i], dN = p.dst[i];
         const bool has_neg = p.rows_per_edge == 3;
         const int gN = has_neg ? p.neg[i] : sN;
