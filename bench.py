@@ -444,6 +444,26 @@ def run_ours(args):
                          "traffic": args.traffic, "peak_source": peak_src, "kernel": "tppr_span_kernel",
                          "bytes_per_edge": bytes_per_edge(), "launch_ms": per_launch_ms},
         }
+        if world == 1 and not args.no_flat:
+            # the same kernel on a hub-free stream of the same size class (uniform endpoints): no long
+            # dependency chain, i.e. the kernel's throughput regime, where HBM is the relevant roofline
+            from zebra_b200 import synth
+            nf = min(E, 4_000_000)
+            shp = synth.StreamShape("flat", st.shape.n_nodes, 0, nf, 0, 2320.0, 1.0 / st.shape.n_nodes, 0.0)
+            fs_ = synth.make_stream("flat", seed=11, shape=shp)
+            fneg = synth.make_negatives(fs_, BS)
+            fplan = f.make_plan(fs_.src, fs_.dst, fneg, fs_.ts, fs_.eidx, BS)
+            best = 1e30
+            for _ in range(3):
+                f.reset_tppr()
+                fplan.run(0, fplan.n_batches, window, out=out, out_slots=window)
+                f.sync_check()
+                best = min(best, f.last_kernel_ms())
+            fplan.close()
+            fa = nf * bytes_per_edge() / (best * 1e-3) / 1e9
+            line["roofline"]["hub_free_stream"] = {
+                "what": f"same kernel, {nf} edges with uniform endpoints over {st.shape.n_nodes} nodes (no hub chain), rows included",
+                "edges_per_sec": nf / (best * 1e-3), "achieved": fa, "frac": fa / peak}
         if not args.no_cpu and world == 1:
             v, n, dt = cpu_port_throughput(st, neg, args.cpu_sample_edges, 1)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
@@ -467,6 +487,7 @@ def main():
     ap.add_argument("--ref-sample-edges", type=int, default=1_000_000)
     ap.add_argument("--traffic", type=float, default=None, help="ncu dram bytes per launch, if captured")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-flat", action="store_true", help="skip the hub-free throughput leg")
     ap.add_argument("--mode", default="sharded", choices=["sharded", "replicas"],
                     help="N>1: node-sharded state with in-kernel NVLink exchange (default), or independent replicas")
     ap.add_argument("--no-strong", action="store_true", help="N>1: skip the strong-scaling leg (same stream as N=1, sharded)")

@@ -42,6 +42,24 @@ def bulk(name, n_edges=None):
         dt = time.perf_counter() - t
         print(f"{name} bulk update-only E={E}: {E/dt/1e6:.2f} M edges/s wall, kernel-span {f.last_kernel_ms():.1f} ms -> {E/f.last_kernel_ms()/1e3:.2f} M edges/s, GB/s alg={E*2*1976/f.last_kernel_ms()/1e6:.1f} {f.counters()}", flush=True)
 
+def flat(n_nodes=1_140_149, n_edges=4_000_000, bs=200, window=64):
+    """No hubs (uniform endpoints): no dependency chain longer than a few edges, so this is the span
+    kernel's THROUGHPUT, the regime where the HBM roofline is the relevant bound."""
+    shape = synth.StreamShape("flat", n_nodes, 0, n_edges, 0, 2320.0, 1.0 / n_nodes, 0.0)
+    st = synth.make_stream("flat", seed=11, shape=shape)
+    neg = synth.make_negatives(st, bs)
+    f = tppr_finder(st.shape.table_nodes, 20, 2, [0.1, 0.1], [0.5, 0.95])
+    plan = f.make_plan(st.src, st.dst, neg, st.ts, st.eidx, bs)
+    out = plan.alloc_out(window)
+    for rep in range(3):
+        f.reset_tppr()
+        plan.run(0, plan.n_batches, window, out=out, out_slots=window)
+        f.sync_check()
+        ms = f.last_kernel_ms()
+        print(f"flat stream E={n_edges} N={n_nodes} with rows: {n_edges/ms/1e3:.1f} M edges/s, alg {n_edges*6856/ms/1e6:.0f} GB/s "
+              f"({n_edges*6856/ms/1e6/6534.1*100:.1f}% of measured HBM peak) {f.counters()}", flush=True)
+
+
 def star(n_edges=100000, n_nodes=200000, pool=None, insts=((1, [0.1], [0.5]), (1, [0.1], [0.95]), (2, [0.1, 0.1], [0.5, 0.95]))):
     """Every edge touches node 1: throughput = 1 / (latency of one step of a hub chain)."""
     rng = np.random.default_rng(0)
@@ -67,8 +85,12 @@ if __name__ == "__main__":
     star(pool=2000, insts=((1, [0.1], [0.5]), (1, [0.1], [0.95])))
     if os.environ.get("ZEBRA_TPPR_LIB") or "--star" in sys.argv:
         sys.exit(0)
+    if "--flat" in sys.argv:
+        flat()
+        sys.exit(0)
     per_batch("wikipedia", 157474)
     per_batch("reddit", 200000)
     per_batch("wikitalk", 400000)
     bulk("reddit")
     bulk("wikitalk")
+    flat()

@@ -105,6 +105,13 @@ struct SpanParams {
     char *out_peer[kMaxRanks];                      // every rank's output region (peer-mapped), own included
 };
 
+constexpr int kKeySlotBits = 11, kKeySlots = 1 << kKeySlotBits;
+
+__device__ __forceinline__ unsigned key_slot(int e, int n)
+{
+    return (static_cast<unsigned>(e) * 0x9E3779B1u ^ static_cast<unsigned>(n) * 0x85EBCA6Bu) >> (32 - kKeySlotBits);
+}
+
 struct alignas(16) WarpScratch {
     unsigned long long V[64];   // candidate scores by candidate index (fp64 bit patterns in integer order)
     unsigned long long K[32];   // peer keys of the duplicate scan
@@ -114,6 +121,7 @@ struct alignas(16) WarpScratch {
     unsigned short Q[64];       // sort position -> item (numba quicksort working array)
     unsigned short X[32], Y[32];   // swap exchange
     unsigned char P[64];        // candidate -> sort position
+    unsigned char T[kKeySlots]; // duplicate lookup: slot of a peer key -> lane holding it, 0xff = empty
 };
 
 struct VecR {
@@ -344,34 +352,61 @@ __device__ __forceinline__ bool update_endpoint(const SpanParams &p, WarpScratch
     double vB = __dmul_rn(B.sc, s2c);
     const unsigned long long keyA = pack_key(A.e, A.n), keyB = pack_key(B.e, B.n);
 
-    // ---- duplicate keys between A and B: every A lane scans the peer's keys in shared memory ----
+    // ---- duplicate keys between A and B ----
+    // The peer's keys are dropped into a 2048-slot byte table (slot = hash of (eidx, node), value =
+    // lane); each own key looks its slot up and confirms the full key (eidx, node, ts) of the lane it
+    // finds.  Exact as long as the peer's keys fall into distinct slots (checked by reading the slots
+    // back); otherwise every own lane scans all peer keys in shared memory.  The table is kept clean
+    // (0xff) between uses by erasing the slots just written.
     unsigned dupmask = 0;          // peer entries whose key A already holds
     if (c1 > 0 && c2 > 0 && !(ZEBRA_ABLATE & 1)) {
+        const unsigned hA = key_slot(A.e, A.n), hB = key_slot(B.e, B.n);
+        const bool isB = lane < c2;
         __syncwarp();
-        s.K[lane] = lane < c2 ? keyB : 0xffffffffffffffffull;   // (eidx -1, node -1) never occurs
+        if (isB) s.T[hB] = static_cast<unsigned char>(lane);
         __syncwarp();
-        unsigned cand = 0;
-        const ulonglong2 *K2 = reinterpret_cast<const ulonglong2 *>(s.K);
-#pragma unroll 4
-        for (int q = 0; q < (c2 + 1) >> 1; ++q) {
-            const ulonglong2 kk = K2[q];
-            cand |= (kk.x == keyA ? 1u : 0u) << (2 * q);
-            cand |= (kk.y == keyA ? 1u : 0u) << (2 * q + 1);
-        }
-        if (lane >= c1) cand = 0;
-        // keys are (eidx, node, ts): confirm the timestamp of the (rare) candidates
+        const int back = isB ? s.T[hB] : lane;
+        int probe = lane < c1 ? s.T[hA] : 0xff;
+        const bool clash = __any_sync(kFull, back != lane) || (ZEBRA_ABLATE & 16);
+        const bool found = __any_sync(kFull, probe != 0xff);      // no own key maps to an occupied slot: no duplicate
+        __syncwarp();                  // every lane has read its slots
+        if (isB) s.T[hB] = 0xff;
         int hit = -1;
-        while (__any_sync(kFull, cand != 0)) {
-            const int t = cand ? (__ffs(cand) - 1) : 0;
-            const double ots = __shfl_sync(kFull, B.ts, t);
-            if (cand) {
-                if (ots == A.ts) { hit = t; cand = 0; }
-                else cand &= cand - 1;
+        if (!clash && !found) {
+            // nothing to add, dupmask stays 0
+        } else if (!clash) {
+            const int c = probe < 32 ? probe : 0;
+            const unsigned long long kb = __shfl_sync(kFull, keyB, c);
+            const double tb = __shfl_sync(kFull, B.ts, c);
+            if (probe < c2 && kb == keyA && tb == A.ts) hit = probe;
+        } else {
+            __syncwarp();
+            s.K[lane] = isB ? keyB : 0xffffffffffffffffull;   // (eidx -1, node -1) never occurs
+            __syncwarp();
+            unsigned cand = 0;
+            const ulonglong2 *K2 = reinterpret_cast<const ulonglong2 *>(s.K);
+#pragma unroll 4
+            for (int q = 0; q < (c2 + 1) >> 1; ++q) {
+                const ulonglong2 kk = K2[q];
+                cand |= (kk.x == keyA ? 1u : 0u) << (2 * q);
+                cand |= (kk.y == keyA ? 1u : 0u) << (2 * q + 1);
+            }
+            if (lane >= c1) cand = 0;
+            // keys are (eidx, node, ts): confirm the timestamp of the (rare) candidates
+            while (__any_sync(kFull, cand != 0)) {
+                const int t = cand ? (__ffs(cand) - 1) : 0;
+                const double ots = __shfl_sync(kFull, B.ts, t);
+                if (cand) {
+                    if (ots == A.ts) { hit = t; cand = 0; }
+                    else cand &= cand - 1;
+                }
             }
         }
-        const double got = __shfl_sync(kFull, vB, hit >= 0 ? hit : 0);
-        if (hit >= 0) vA = __dadd_rn(vA, got);
-        dupmask = __reduce_or_sync(kFull, hit >= 0 ? (1u << hit) : 0u);
+        if (clash || found) {
+            const double got = __shfl_sync(kFull, vB, hit >= 0 ? hit : 0);
+            if (hit >= 0) vA = __dadd_rn(vA, got);
+            dupmask = __reduce_or_sync(kFull, hit >= 0 ? (1u << hit) : 0u);
+        }
     }
     ZP_MARK(8);
 
@@ -510,6 +545,13 @@ __device__ __forceinline__ bool update_endpoint(const SpanParams &p, WarpScratch
     return ok;
 }
 
+__device__ __forceinline__ void scratch_init(WarpScratch &s, int lane)
+{
+    uint4 *t = reinterpret_cast<uint4 *>(s.T);
+    for (int q = lane; q < kKeySlots / 16; q += 32) t[q] = make_uint4(~0u, ~0u, ~0u, ~0u);
+    __syncwarp();
+}
+
 // how long to sleep before looking again at a record whose wanted version is `dist` edges away
 __device__ __forceinline__ unsigned backoff_ns(uint32_t dist)
 {
@@ -523,6 +565,7 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
     __shared__ WarpScratch scratch[kWarpsPerBlock];
     const int lane = threadIdx.x & 31;
     WarpScratch &s = scratch[threadIdx.x >> 5];
+    scratch_init(s, lane);
     const unsigned long long total = static_cast<unsigned long long>(p.n_chunk) * p.n_tppr;
     const int k = p.k;
     const uint32_t tag_base = p.seq0 + static_cast<uint32_t>(p.tag_offset);   // tag of launch-local edge 0

@@ -56,6 +56,7 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
     __shared__ WarpScratch scratch[kWarpsPerBlock];
     const int lane = threadIdx.x & 31;
     WarpScratch &s = scratch[threadIdx.x >> 5];
+    scratch_init(s, lane);
     // tickets run over this rank's own list of edges (built by the host from the ownership rule), so
     // edges that do not touch this shard cost nothing here
     const unsigned long long total = static_cast<unsigned long long>(p.n_list) * p.n_tppr;

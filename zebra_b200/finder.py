@@ -52,6 +52,8 @@ class tppr_finder:  # noqa: N801  (name kept from the reference)
         b = (C.c_double * self.n_tppr)(*self.beta_list)
         check(self._L.zebra_tppr_create(C.byref(h), self.num_nodes, self.k, self.n_tppr, a, b, self.device.index or 0))
         self._h = h
+        if os.environ.get("ZEBRA_MAX_BLOCKS"):            # developer knob: cap the persistent grid (blocks of 8 warps)
+            check(self._L.zebra_tppr_set_max_blocks(h, int(os.environ["ZEBRA_MAX_BLOCKS"])))
         self._table_bytes = self._L.zebra_tppr_table_bytes(h)
         self._record_bytes = self._L.zebra_tppr_record_bytes(h)
         self._host_out = None
