@@ -3,7 +3,7 @@
 # Usage (from the repo root on the GPU box): bash tools/gpu_check.sh [tests|bench|ncu ...]
 set -u
 mkdir -p gpurun_out
-WHAT="${*:-tests probe bench ncu}"
+WHAT="${*:-tests probe bench ncu kernels}"
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/gpu.txt 2>&1
 lscpu | head -20 > gpurun_out/lscpu.txt 2>&1
 for w in $WHAT; do
@@ -23,5 +23,9 @@ ncu)
   echo "ncu launches rc=$?"
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:tppr_span -s 40 -c 2 -f -o gpurun_out/prof $CMD > gpurun_out/ncu_full.log 2>&1
   echo "ncu full rc=$?"; tail -3 gpurun_out/ncu_full.log ;;
+kernels)
+  timeout 600 python tools/perf_kernels.py > gpurun_out/kernels.log 2>&1; echo "kernels rc=$?"; cat gpurun_out/kernels.log
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:"gather_fwd|prune_topk" -c 6 -f -o gpurun_out/prof_kernels python tools/perf_kernels.py > gpurun_out/ncu_kernels.log 2>&1
+  echo "ncu kernels rc=$?" ;;
 esac
 done
