@@ -215,7 +215,10 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
             # end to end: host arrays in (dependency pass + H2D of the replicated span on every rank), the
             # complete rows of every batch back in pinned host memory on EVERY rank.  Per window: kernel,
             # a one-element all-reduce as cross-rank completion (plumbing, not data), D2H on a second stream.
-            pinned = [torch.empty(window * slot, dtype=torch.uint8).pin_memory() for _ in range(2)]
+            # data-parallel consumers: rank r reads back the rows of its 1/N of every window's batches
+            # (together the ranks read every batch exactly once); the full rows are on every GPU anyway
+            per = -(-window // world)
+            pinned = [torch.empty(per * slot, dtype=torch.uint8).pin_memory() for _ in range(2)]
             flag = torch.zeros(1, device=dev)
             ev_ready = [torch.cuda.Event() for _ in range(2)]
             ev_copy = [torch.cuda.Event() for _ in range(2)]
@@ -236,7 +239,10 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
                         acc += float(pinned[h][0])              # host consumes window w-2 before its buffer is reused
                     with torch.cuda.stream(copy_stream):
                         copy_stream.wait_event(ev_ready[h])
-                        pinned[h][: nb * slot].copy_(f.out[h * window * slot: h * window * slot + nb * slot], non_blocking=True)
+                        q0, q1 = min(nb, rank * per), min(nb, (rank + 1) * per)
+                        if q1 > q0:
+                            base = h * window * slot
+                            pinned[h][: (q1 - q0) * slot].copy_(f.out[base + q0 * slot: base + q1 * slot], non_blocking=True)
                         ev_copy[h].record(copy_stream)
                     if w >= 1:
                         ev_copy[(w - 1) & 1].synchronize()
@@ -297,9 +303,10 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
                          f"outputs exceed the 126 MB L2 (inputs larger than L2)",
                    "tie_path_prunes_last_step_rank0": weak["tie_prunes"]},
         "e2e": {"value": E * args.steps / weak["e2e_s"], "unit": UNIT,
-                "h2d_bytes_per_step": world * ((E + 7) // 8 * 8) * 48, "d2h_bytes_per_step": world * len(ALPHAS) * 16 * 3 * E * K,
-                "step": f"per rank: plan built from host arrays (dependency pass + H2D of the replicated span), sharded run in windows of "
-                        f"{window} batches, complete rows of every batch copied to pinned host memory on every rank"},
+                "h2d_bytes_per_step": world * ((E + 7) // 8 * 8) * 48, "d2h_bytes_per_step": len(ALPHAS) * 16 * 3 * E * K,
+                "step": f"per rank: plan built from host arrays (ownership-aware dependency pass + H2D of the replicated span), sharded "
+                        f"run in windows of {window} batches, a one-element all-reduce per window as cross-rank completion, rank r copies "
+                        f"the rows of its 1/{world} of every window's batches to pinned host memory (every batch read back once)"},
         "gpu_launches": weak["launches"] * world,
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak * world, "unit": "GB/s", "frac": achieved / (peak * world),

@@ -14,6 +14,7 @@
 #include <cstdio>
 #include <climits>
 #include <cstring>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -226,6 +227,92 @@ int fill_soa(zebra_tppr *h, char *host, size_t cap, const NodeT *src, const Node
     for (int64_t i = 0; i < m; ++i) {
         lastw[o_src[i]] = -1; lastw[o_dst[i]] = -1;
         rhead[o_neg[i]] = -1; rcount[o_neg[i]] = 0;
+    }
+    return 0;
+}
+
+// Node-sharded variant of fill_soa: a rank only ever reads and writes the records of the nodes it
+// owns, so only edges it takes part in get a staging record, and dependencies are tracked for owned
+// endpoints only (scratch indexed by local row: 1/world of the nodes, cache resident).  A non-owned
+// endpoint arrives through the mailbox, tagged with the edge itself: no prev, no reader threshold.
+// Also builds the rank's work list and, per batch, the list position of its first edge.
+int fill_soa_sharded(zebra_tppr *h, char *host, size_t cap, const int32_t *src, const int32_t *dst, const int32_t *neg,
+                     const double *ts, const int64_t *eidx, int64_t m, int64_t batch_size, std::vector<int32_t> &list,
+                     std::vector<int64_t> &batch_ofs)
+{
+    const int64_t N = h->num_nodes;
+    const int32_t pm = h->world - 1, me = h->rank, lg = h->world_log2;
+    int32_t *o_src = reinterpret_cast<int32_t *>(host);
+    int32_t *o_dst = o_src + cap, *o_neg = o_dst + cap, *o_e = o_neg + cap;
+    int32_t *p_s = o_e + cap, *p_d = p_s + cap, *p_n = p_d + cap;
+    uint32_t *r_s = reinterpret_cast<uint32_t *>(p_n + cap), *r_d = r_s + cap, *flg = r_d + cap;
+    double *o_ts = reinterpret_cast<double *>(flg + cap);
+    int32_t *lastw = h->lastw.data(), *rhead = h->rhead.data();      // sized num_nodes >= local rows
+    uint32_t *rcount = h->rcount.data();
+    const int64_t n_batches = (m + batch_size - 1) / batch_size;
+    batch_ofs.assign(static_cast<size_t>(n_batches) + 1, 0);
+    list.clear();
+    list.reserve(static_cast<size_t>(m / h->world) * 3 + 16);
+    // rnext is indexed by list position here (readers are list members)
+    std::vector<int32_t> &rnext_v = h->rnext;
+    for (int64_t i = 0; i < m; ++i) {
+        if (i % batch_size == 0) batch_ofs[static_cast<size_t>(i / batch_size)] = static_cast<int64_t>(list.size());
+        const int64_t a64 = src[i], b64 = dst[i], g64 = neg ? static_cast<int64_t>(neg[i]) : a64;
+        if (a64 < 0 || a64 >= N || b64 < 0 || b64 >= N || g64 < 0 || g64 >= N)
+            return fail("node id out of range at edge %lld (num_nodes=%lld)", (long long)i, (long long)N);
+        const int32_t a = static_cast<int32_t>(a64), b = static_cast<int32_t>(b64), g = static_cast<int32_t>(g64);
+        const bool oa = (a & pm) == me, ob = (b & pm) == me;
+        const bool og = neg && g != a && g != b && (g & pm) == me;
+        if (!(oa || ob || og)) continue;
+        const int64_t e = eidx[i];
+        if (e < 0 || e > 0x7fffffffLL) return fail("edge id %lld does not fit int32", (long long)e);
+        const int32_t li = static_cast<int32_t>(list.size());
+        list.push_back(static_cast<int32_t>(i));
+        if (rnext_v.size() <= static_cast<size_t>(li)) rnext_v.resize(static_cast<size_t>(li) * 2 + 1024);
+        int32_t *rnext = rnext_v.data();
+        o_src[i] = a; o_dst[i] = b; o_neg[i] = g; o_e[i] = static_cast<int32_t>(e); o_ts[i] = ts[i];
+        flg[i] = 0; p_s[i] = -1; p_d[i] = -1; p_n[i] = -1; r_s[i] = 0; r_d[i] = 0;
+        if (og) {
+            const int32_t gl = g >> lg;
+            p_n[i] = lastw[gl];
+            rnext[li] = rhead[gl]; rhead[gl] = li; rcount[gl]++;
+        }
+        if (oa) {
+            const int32_t al = a >> lg;
+            p_s[i] = lastw[al]; r_s[i] = rcount[al];
+            if (rcount[al]) {
+                for (int32_t r = rhead[al]; r >= 0; r = rnext[r]) flg[list[static_cast<size_t>(r)]] |= zebra::kFlagSignal;
+                rhead[al] = -1; rcount[al] = 0;
+            }
+            lastw[al] = static_cast<int32_t>(i);
+        }
+        if (ob && b != a) {
+            const int32_t bl = b >> lg;
+            p_d[i] = lastw[bl]; r_d[i] = rcount[bl];
+            if (rcount[bl]) {
+                for (int32_t r = rhead[bl]; r >= 0; r = rnext[r]) flg[list[static_cast<size_t>(r)]] |= zebra::kFlagSignal;
+                rhead[bl] = -1; rcount[bl] = 0;
+            }
+            lastw[bl] = static_cast<int32_t>(i);
+        }
+    }
+    batch_ofs[static_cast<size_t>(n_batches)] = static_cast<int64_t>(list.size());
+    // backward: which owned endpoint is written again first (only matters when both are owned)
+    for (int32_t i : list) {
+        if ((o_src[i] & pm) == me) lastw[o_src[i] >> lg] = INT_MAX;
+        if ((o_dst[i] & pm) == me) lastw[o_dst[i] >> lg] = INT_MAX;
+    }
+    for (size_t q = list.size(); q-- > 0;) {
+        const int32_t i = list[q], a = o_src[i], b = o_dst[i];
+        const bool oa = (a & pm) == me, ob = (b & pm) == me;
+        if (oa && ob && a != b && lastw[b >> lg] < lastw[a >> lg]) flg[i] |= zebra::kFlagDstFirst;
+        if (oa) lastw[a >> lg] = i;
+        if (ob) lastw[b >> lg] = i;
+    }
+    for (int32_t i : list) {
+        if ((o_src[i] & pm) == me) lastw[o_src[i] >> lg] = -1;
+        if ((o_dst[i] & pm) == me) lastw[o_dst[i] >> lg] = -1;
+        if ((o_neg[i] & pm) == me) { rhead[o_neg[i] >> lg] = -1; rcount[o_neg[i] >> lg] = 0; }
     }
     return 0;
 }
@@ -643,31 +730,20 @@ int zebra_tppr_plan_create(zebra_tppr_t *h, const int32_t *host_src, const int32
     pl->n_batches = (n + batch_size - 1) / batch_size;
     pl->cap = (static_cast<size_t>(n) + 7) & ~static_cast<size_t>(7);
     if (n >= 0x70000000LL) { delete pl; return fail("plan too long"); }
-    std::vector<char> host(pl->cap * kEdgeBytes);
-    if (fill_soa<int32_t>(h, host.data(), pl->cap, host_src, host_dst, rows_per_edge == 3 ? host_neg : nullptr, host_ts,
-                          host_eidx, n)) {
+    // staging image of the span (uninitialised: a sharded rank fills only the records it takes part in)
+    std::unique_ptr<char[]> host(new char[pl->cap * kEdgeBytes]);
+    std::vector<int32_t> list;
+    const int rc = h->world > 1
+        ? fill_soa_sharded(h, host.get(), pl->cap, host_src, host_dst, rows_per_edge == 3 ? host_neg : nullptr, host_ts, host_eidx,
+                           n, batch_size, list, pl->batch_ofs)
+        : fill_soa<int32_t>(h, host.get(), pl->cap, host_src, host_dst, rows_per_edge == 3 ? host_neg : nullptr, host_ts,
+                            host_eidx, n);
+    if (rc) {
         delete pl;
         return 1;
     }
-    std::vector<int32_t> list;
-    if (h->world > 1) {
-        const int32_t pm = h->world - 1, me = h->rank;
-        pl->batch_ofs.assign(static_cast<size_t>(pl->n_batches) + 1, 0);
-        list.reserve(static_cast<size_t>(n / h->world) * 2 + 16);
-        for (int64_t i = 0; i < n; ++i) {
-            if (i % batch_size == 0) pl->batch_ofs[static_cast<size_t>(i / batch_size)] = static_cast<int64_t>(list.size());
-            const int32_t a = host_src[i], b = host_dst[i];
-            bool mine = (a & pm) == me || (b & pm) == me;
-            if (!mine && rows_per_edge == 3) {
-                const int32_t g = host_neg[i];
-                mine = g != a && g != b && (g & pm) == me;
-            }
-            if (mine) list.push_back(static_cast<int32_t>(i));
-        }
-        pl->batch_ofs[static_cast<size_t>(pl->n_batches)] = static_cast<int64_t>(list.size());
-    }
     cudaError_t e = cudaMalloc(&pl->dev, pl->cap * kEdgeBytes);
-    if (e == cudaSuccess) e = cudaMemcpy(pl->dev, host.data(), pl->cap * kEdgeBytes, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(pl->dev, host.get(), pl->cap * kEdgeBytes, cudaMemcpyHostToDevice);
     if (e == cudaSuccess && h->world > 1) {
         e = cudaMalloc(&pl->dev_list, std::max<size_t>(list.size(), 1) * sizeof(int32_t));
         if (e == cudaSuccess) e = cudaMemcpy(pl->dev_list, list.data(), list.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
