@@ -185,7 +185,8 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
 
     def measure(st, neg, sampler=None, e2e=True):
         E, N = st.n_edges, st.shape.table_nodes
-        f = create_sharded(N, K, len(ALPHAS), ALPHAS, BETAS, window * BS, 2 * window * slot)
+        # rows of batch b are delivered to rank b % N only: each data-parallel rank consumes its own batches
+        f = create_sharded(N, K, len(ALPHAS), ALPHAS, BETAS, window * BS, 2 * window * slot, row_mode=1)
         plan = f.make_plan(st.src, st.dst, neg, st.ts, st.eidx, BS)
         n_win = -(-plan.n_batches // window)
 
@@ -217,8 +218,8 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
             # a one-element all-reduce as cross-rank completion (plumbing, not data), D2H on a second stream.
             # data-parallel consumers: rank r reads back the rows of its 1/N of every window's batches
             # (together the ranks read every batch exactly once); the full rows are on every GPU anyway
-            per = -(-window // world)
-            pinned = [torch.empty(per * slot, dtype=torch.uint8).pin_memory() for _ in range(2)]
+            per = window // world                    # window is a multiple of world, windows start at multiples of it
+            pinned = [torch.empty((per, slot), dtype=torch.uint8).pin_memory() for _ in range(2)]
             flag = torch.zeros(1, device=dev)
             ev_ready = [torch.cuda.Event() for _ in range(2)]
             ev_copy = [torch.cuda.Event() for _ in range(2)]
@@ -236,13 +237,13 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
                     dist.all_reduce(flag)                       # ... and so has everybody once this completes
                     ev_ready[h].record(main)
                     if w >= 2:
-                        acc += float(pinned[h][0])              # host consumes window w-2 before its buffer is reused
+                        acc += float(pinned[h][0, 0])           # host consumes window w-2 before its buffer is reused
                     with torch.cuda.stream(copy_stream):
                         copy_stream.wait_event(ev_ready[h])
-                        q0, q1 = min(nb, rank * per), min(nb, (rank + 1) * per)
-                        if q1 > q0:
-                            base = h * window * slot
-                            pinned[h][: (q1 - q0) * slot].copy_(f.out[base + q0 * slot: base + q1 * slot], non_blocking=True)
+                        base = h * window * slot
+                        mine = f.out[base: base + nb * slot].view(nb, slot)[rank::world]      # batches b with b % N == rank
+                        if mine.shape[0]:
+                            pinned[h][: mine.shape[0]].copy_(mine, non_blocking=True)
                         ev_copy[h].record(copy_stream)
                     if w >= 1:
                         ev_copy[(w - 1) & 1].synchronize()
@@ -270,7 +271,7 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
 
     sampler = ClockSampler(local)
     st, neg = synth.make_communities(WORKLOAD, world, BS, n_edges=args.edges)
-    xs = exchange_stats(st.src, st.dst, neg, world, K, len(ALPHAS))
+    xs = exchange_stats(st.src, st.dst, neg, world, K, len(ALPHAS), row_mode=1)
     weak = measure(st, neg, sampler if rank == 0 else None)
     clocks = sampler.stop() if rank == 0 else None
     del st, neg
@@ -278,7 +279,7 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
     if not args.no_strong:
         st1, neg1 = load_workload(n_edges=args.edges)
         strong = measure(st1, neg1, e2e=False)
-        strong["exchange"] = exchange_stats(st1.src, st1.dst, neg1, world, K, len(ALPHAS))
+        strong["exchange"] = exchange_stats(st1.src, st1.dst, neg1, world, K, len(ALPHAS), row_mode=1)
     if rank != 0:
         return
     peak, peak_src = peaks()
@@ -296,7 +297,7 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
                    "step": "reset tables + stream the whole span once",
                    "batches_per_launch": window,
                    "parallelism": f"node-sharded x{world}: owner = id & {world - 1}; cross-shard old vectors pushed through peer-mapped "
-                                  f"mailboxes inside the span kernel (NVLink stores), rows stored into every rank's output region; "
+                                  f"mailboxes inside the span kernel (NVLink stores), rows of batch b stored by their owners into rank b % N's output region; "
                                   f"no collective on the data path",
                    "exchange": xs,
                    "l2": f"per-GPU tables {len(ALPHAS) * ((weak['N'] + world - 1) // world) * weak['record_bytes'] / 1e6:.0f} MB + "
@@ -306,7 +307,7 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
                 "h2d_bytes_per_step": world * ((E + 7) // 8 * 8) * 48, "d2h_bytes_per_step": len(ALPHAS) * 16 * 3 * E * K,
                 "step": f"per rank: plan built from host arrays (ownership-aware dependency pass + H2D of the replicated span), sharded "
                         f"run in windows of {window} batches, a one-element all-reduce per window as cross-rank completion, rank r copies "
-                        f"the rows of its 1/{world} of every window's batches to pinned host memory (every batch read back once)"},
+                        f"the rows of its batches (b % {world} == r) to pinned host memory (every batch read back once)"},
         "gpu_launches": weak["launches"] * world,
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak * world, "unit": "GB/s", "frac": achieved / (peak * world),

@@ -173,6 +173,10 @@ int zebra_tppr_shard_disconnect(zebra_tppr_t *h);
 void *zebra_tppr_shard_out(zebra_tppr_t *h);
 size_t zebra_tppr_shard_out_bytes(const zebra_tppr_t *h);
 int zebra_tppr_shard_reset(zebra_tppr_t *h, void *stream);
+/* Row delivery of plans with batch structure: 0 (default) every rank receives every row; 1 the rows
+ * of batch b go to rank b & (world-1) only (same slot offset), the other ranks' slots of that batch
+ * stay untouched.  Same setting on every rank. */
+int zebra_tppr_shard_row_mode(zebra_tppr_t *h, int32_t mode);
 /* Caps the persistent grid (blocks of 8 warps); lets two ranks share one GPU in tests. */
 int zebra_tppr_set_max_blocks(zebra_tppr_t *h, int32_t blocks);
 

@@ -17,7 +17,7 @@ pytestmark = pytest.mark.gpu
 AL, BE = [0.1, 0.1], [0.5, 0.95]
 
 
-def _run_sharded(world, st, neg, bs, k, window, rows_per_edge=3):
+def _run_sharded(world, st, neg, bs, k, window, rows_per_edge=3, row_mode=0):
     import torch
     from zebra_b200.sharded import ShardedFinder
     N = st.shape.table_nodes
@@ -27,6 +27,7 @@ def _run_sharded(world, st, neg, bs, k, window, rows_per_edge=3):
     fs = [ShardedFinder(N, k, 2, AL, BE, r, world, window * bs, out_bytes) for r in range(world)]
     for f in fs:
         f.set_max_blocks(max(1, (2 * sms) // world))
+        f.set_row_mode(row_mode)
     ShardedFinder.connect_local(fs)
     plans = [f.make_plan(st.src, st.dst, neg if rows_per_edge == 3 else None, st.ts, st.eidx, bs, rows_per_edge) for f in fs]
     streams = [torch.cuda.Stream() for _ in fs]
@@ -103,3 +104,27 @@ def test_sharded_adversarial_self_loops_and_ties():
                         assert np.array_equal(x.cpu().numpy(), y), f"rank {f.rank} batch {b}"
     finally:
         AL, BE = old
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_sharded_row_mode_delivers_each_batch_to_one_rank(world):
+    """row_mode 1: the rows of batch b land on rank b & (world-1) only; the union is the full result."""
+    import torch
+    n_edges, bs = 4200, 200
+    st = synth.make_stream("superuser", n_edges=n_edges, seed=78)
+    neg = synth.make_negatives(st, bs)
+    N, k = st.shape.table_nodes, 20
+    fs, plans, n_batches = _run_sharded(world, st, neg, bs, k, 4, row_mode=1)
+    cpu = oracle.OracleFinder(N, k, 2, AL, BE)
+    for b in range(n_batches):
+        lo, hi = b * bs, min(n_edges, (b + 1) * bs)
+        nodes = np.concatenate([st.src[lo:hi], st.dst[lo:hi], neg[lo:hi]]).astype(np.int32)
+        ref = cpu.streaming_topk(nodes, np.concatenate([st.ts[lo:hi]] * 3), st.eidx[lo:hi])
+        for f, p in zip(fs, plans):
+            got = p.views(f.out, b, 0, n_batches)
+            if f.rank == (b & (world - 1)):
+                for la, lb in zip(got, ref):
+                    for x, y in zip(la, lb):
+                        assert np.array_equal(x.cpu().numpy(), y), f"rank {f.rank} batch {b}"
+            else:                                  # never written: still the zero fill of the arena
+                assert all(int(torch.count_nonzero(x)) == 0 for la in got for x in la), f"rank {f.rank} batch {b}"

@@ -34,6 +34,21 @@ struct GatherParams {
     int32_t *status;           // [0] set to 1 on an out-of-range id (row skipped)
 };
 
+// cos of an fp32 argument that can reach 1e6 and more (dt * w, model/time_encoding.py:23-28).  Below
+// libdevice's fast-path limit this IS cosf.  Above it, cosf would run its Payne-Hanek reduction on
+// the few lanes that hold the high frequencies while the rest of the warp waits; instead the argument
+// is reduced in fp64 (two-constant 2*pi: the error after reduction is ~1e-10 for |x| < 2^31) and the
+// fp64 cosine of the reduced argument is rounded to fp32 — at least as accurate as cosf itself.
+__device__ __forceinline__ float cos_arg(float x)
+{
+    if (fabsf(x) <= 100000.f) return cosf(x);
+    const double xd = static_cast<double>(x);
+    const double n = rint(xd * 0.15915494309189535);
+    double r = fma(-n, 6.283185307179586, xd);
+    r = fma(-n, 2.4492935982947064e-16, r);
+    return static_cast<float>(cos(r));
+}
+
 template <bool VEC>
 __device__ __forceinline__ void copy_row(float *dst, const float *src, int n, int lane)
 {
@@ -73,13 +88,13 @@ gather_fwd_kernel(const GatherParams p)
                     const float4 w = __ldg(reinterpret_cast<const float4 *>(p.time_w) + c);
                     const float4 b = __ldg(reinterpret_cast<const float4 *>(p.time_b) + c);
                     float4 r;
-                    r.x = cosf(__fadd_rn(__fmul_rn(dt, w.x), b.x)); r.y = cosf(__fadd_rn(__fmul_rn(dt, w.y), b.y));
-                    r.z = cosf(__fadd_rn(__fmul_rn(dt, w.z), b.z)); r.w = cosf(__fadd_rn(__fmul_rn(dt, w.w), b.w));
+                    r.x = cos_arg(__fadd_rn(__fmul_rn(dt, w.x), b.x)); r.y = cos_arg(__fadd_rn(__fmul_rn(dt, w.y), b.y));
+                    r.z = cos_arg(__fadd_rn(__fmul_rn(dt, w.z), b.z)); r.w = cos_arg(__fadd_rn(__fmul_rn(dt, w.w), b.w));
                     reinterpret_cast<float4 *>(xt)[c] = r;
                 }
             } else {
                 for (int c = lane; c < p.Dt; c += 32)
-                    xt[c] = cosf(__fadd_rn(__fmul_rn(dt, __ldg(p.time_w + c)), __ldg(p.time_b + c)));
+                    xt[c] = cos_arg(__fadd_rn(__fmul_rn(dt, __ldg(p.time_w + c)), __ldg(p.time_b + c)));
             }
         }
         // normalised weights: the warp of slot 0 of each row handles the row's k weights

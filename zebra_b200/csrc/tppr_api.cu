@@ -50,14 +50,18 @@ struct Staging {
 
 }  // namespace
 
+// per-node scratch of the host dependency pass: last writer, head of the list of negative readers of
+// the current version and their count (all -1 / 0 between passes)
+struct NodeDep { int32_t lastw, rhead; uint32_t rcount, pad; };
+
 struct zebra_tppr {
     int64_t num_nodes = 0;
     int32_t k = 0, n_tppr = 0, stride = 0, device = 0;
     double alpha[zebra::kMaxInst], beta[zebra::kMaxInst];
     char *tables[zebra::kMaxInst] = {};
     int32_t *rcnt = nullptr;                  // [n_tppr][num_nodes] negative reads finished, not yet consumed by a writer
-    std::vector<int32_t> lastw, rhead, rnext; // host scratch of the dependency pass (all -1 between passes)
-    std::vector<uint32_t> rcount;             // host scratch: negative reads of a node since its last write
+    std::vector<NodeDep> dep;                 // host scratch of the dependency pass, one cache line touch per node
+    std::vector<int32_t> rnext;
     uint32_t epoch = 0;                       // tag epoch the bound tables were last written in
     zebra::DecayStep *decay[zebra::kMaxInst] = {};   // device: update factors by update count
     int32_t decay_len[zebra::kMaxInst] = {}, decay_fixed[zebra::kMaxInst] = {};
@@ -102,6 +106,7 @@ struct zebra_tppr {
     int32_t launch_parity = 0;
     uint32_t shard_seq = 1;                    // handle-local tag sequence: identical on every rank
     int shard_max_blocks = 0;
+    int32_t row_mode = 0;
 };
 
 // A span prepared once and kept resident in HBM (edge records + dependency thresholds).
@@ -183,8 +188,7 @@ int fill_soa(zebra_tppr *h, char *host, size_t cap, const NodeT *src, const Node
             return fail("node id out of range at edge %lld (num_nodes=%lld)", (long long)i, (long long)N);
         if (e < 0 || e > 0x7fffffffLL) return fail("edge id %lld does not fit int32", (long long)e);
     }
-    int32_t *lastw = h->lastw.data(), *rhead = h->rhead.data();
-    uint32_t *rcount = h->rcount.data();
+    NodeDep *dep = h->dep.data();
     if (h->rnext.size() < static_cast<size_t>(m)) h->rnext.resize(static_cast<size_t>(m));
     int32_t *rnext = h->rnext.data();
     for (int64_t i = 0; i < m; ++i) {
@@ -195,38 +199,38 @@ int fill_soa(zebra_tppr *h, char *host, size_t cap, const NodeT *src, const Node
         o_ts[i] = ts[i];
         flg[i] = 0;
         if (neg && g != a && g != b) {
-            p_n[i] = lastw[g];
-            rnext[i] = rhead[g]; rhead[g] = static_cast<int32_t>(i); rcount[g]++;
+            p_n[i] = dep[g].lastw;
+            rnext[i] = dep[g].rhead; dep[g].rhead = static_cast<int32_t>(i); dep[g].rcount++;
         } else {
             p_n[i] = -1;
         }
-        p_s[i] = lastw[a]; r_s[i] = rcount[a];
-        if (rcount[a]) {
-            for (int32_t r = rhead[a]; r >= 0; r = rnext[r]) flg[r] |= zebra::kFlagSignal;
-            rhead[a] = -1; rcount[a] = 0;
+        p_s[i] = dep[a].lastw; r_s[i] = dep[a].rcount;
+        if (dep[a].rcount) {
+            for (int32_t r = dep[a].rhead; r >= 0; r = rnext[r]) flg[r] |= zebra::kFlagSignal;
+            dep[a].rhead = -1; dep[a].rcount = 0;
         }
-        lastw[a] = static_cast<int32_t>(i);
+        dep[a].lastw = static_cast<int32_t>(i);
         if (b != a) {
-            p_d[i] = lastw[b]; r_d[i] = rcount[b];
-            if (rcount[b]) {
-                for (int32_t r = rhead[b]; r >= 0; r = rnext[r]) flg[r] |= zebra::kFlagSignal;
-                rhead[b] = -1; rcount[b] = 0;
+            p_d[i] = dep[b].lastw; r_d[i] = dep[b].rcount;
+            if (dep[b].rcount) {
+                for (int32_t r = dep[b].rhead; r >= 0; r = rnext[r]) flg[r] |= zebra::kFlagSignal;
+                dep[b].rhead = -1; dep[b].rcount = 0;
             }
-            lastw[b] = static_cast<int32_t>(i);
+            dep[b].lastw = static_cast<int32_t>(i);
         } else {
             p_d[i] = -1; r_d[i] = 0;
         }
     }
     // backward: which endpoint is written again first (lastw doubles as "next write", INT_MAX = never)
-    for (int64_t i = 0; i < m; ++i) { lastw[o_src[i]] = INT_MAX; lastw[o_dst[i]] = INT_MAX; }
+    for (int64_t i = 0; i < m; ++i) { dep[o_src[i]].lastw = INT_MAX; dep[o_dst[i]].lastw = INT_MAX; }
     for (int64_t i = m - 1; i >= 0; --i) {
         const int32_t a = o_src[i], b = o_dst[i];
-        if (a != b && lastw[b] < lastw[a]) flg[i] |= zebra::kFlagDstFirst;
-        lastw[a] = static_cast<int32_t>(i); lastw[b] = static_cast<int32_t>(i);
+        if (a != b && dep[b].lastw < dep[a].lastw) flg[i] |= zebra::kFlagDstFirst;
+        dep[a].lastw = static_cast<int32_t>(i); dep[b].lastw = static_cast<int32_t>(i);
     }
     for (int64_t i = 0; i < m; ++i) {
-        lastw[o_src[i]] = -1; lastw[o_dst[i]] = -1;
-        rhead[o_neg[i]] = -1; rcount[o_neg[i]] = 0;
+        dep[o_src[i]].lastw = -1; dep[o_dst[i]].lastw = -1;
+        dep[o_neg[i]].rhead = -1; dep[o_neg[i]].rcount = 0;
     }
     return 0;
 }
@@ -247,8 +251,7 @@ int fill_soa_sharded(zebra_tppr *h, char *host, size_t cap, const int32_t *src, 
     int32_t *p_s = o_e + cap, *p_d = p_s + cap, *p_n = p_d + cap;
     uint32_t *r_s = reinterpret_cast<uint32_t *>(p_n + cap), *r_d = r_s + cap, *flg = r_d + cap;
     double *o_ts = reinterpret_cast<double *>(flg + cap);
-    int32_t *lastw = h->lastw.data(), *rhead = h->rhead.data();      // sized num_nodes >= local rows
-    uint32_t *rcount = h->rcount.data();
+    NodeDep *dep = h->dep.data();                                     // sized num_nodes >= local rows
     const int64_t n_batches = (m + batch_size - 1) / batch_size;
     batch_ofs.assign(static_cast<size_t>(n_batches) + 1, 0);
     list.clear();
@@ -274,45 +277,45 @@ int fill_soa_sharded(zebra_tppr *h, char *host, size_t cap, const int32_t *src, 
         flg[i] = 0; p_s[i] = -1; p_d[i] = -1; p_n[i] = -1; r_s[i] = 0; r_d[i] = 0;
         if (og) {
             const int32_t gl = g >> lg;
-            p_n[i] = lastw[gl];
-            rnext[li] = rhead[gl]; rhead[gl] = li; rcount[gl]++;
+            p_n[i] = dep[gl].lastw;
+            rnext[li] = dep[gl].rhead; dep[gl].rhead = li; dep[gl].rcount++;
         }
         if (oa) {
             const int32_t al = a >> lg;
-            p_s[i] = lastw[al]; r_s[i] = rcount[al];
-            if (rcount[al]) {
-                for (int32_t r = rhead[al]; r >= 0; r = rnext[r]) flg[list[static_cast<size_t>(r)]] |= zebra::kFlagSignal;
-                rhead[al] = -1; rcount[al] = 0;
+            p_s[i] = dep[al].lastw; r_s[i] = dep[al].rcount;
+            if (dep[al].rcount) {
+                for (int32_t r = dep[al].rhead; r >= 0; r = rnext[r]) flg[list[static_cast<size_t>(r)]] |= zebra::kFlagSignal;
+                dep[al].rhead = -1; dep[al].rcount = 0;
             }
-            lastw[al] = static_cast<int32_t>(i);
+            dep[al].lastw = static_cast<int32_t>(i);
         }
         if (ob && b != a) {
             const int32_t bl = b >> lg;
-            p_d[i] = lastw[bl]; r_d[i] = rcount[bl];
-            if (rcount[bl]) {
-                for (int32_t r = rhead[bl]; r >= 0; r = rnext[r]) flg[list[static_cast<size_t>(r)]] |= zebra::kFlagSignal;
-                rhead[bl] = -1; rcount[bl] = 0;
+            p_d[i] = dep[bl].lastw; r_d[i] = dep[bl].rcount;
+            if (dep[bl].rcount) {
+                for (int32_t r = dep[bl].rhead; r >= 0; r = rnext[r]) flg[list[static_cast<size_t>(r)]] |= zebra::kFlagSignal;
+                dep[bl].rhead = -1; dep[bl].rcount = 0;
             }
-            lastw[bl] = static_cast<int32_t>(i);
+            dep[bl].lastw = static_cast<int32_t>(i);
         }
     }
     batch_ofs[static_cast<size_t>(n_batches)] = static_cast<int64_t>(list.size());
     // backward: which owned endpoint is written again first (only matters when both are owned)
     for (int32_t i : list) {
-        if ((o_src[i] & pm) == me) lastw[o_src[i] >> lg] = INT_MAX;
-        if ((o_dst[i] & pm) == me) lastw[o_dst[i] >> lg] = INT_MAX;
+        if ((o_src[i] & pm) == me) dep[o_src[i] >> lg].lastw = INT_MAX;
+        if ((o_dst[i] & pm) == me) dep[o_dst[i] >> lg].lastw = INT_MAX;
     }
     for (size_t q = list.size(); q-- > 0;) {
         const int32_t i = list[q], a = o_src[i], b = o_dst[i];
         const bool oa = (a & pm) == me, ob = (b & pm) == me;
-        if (oa && ob && a != b && lastw[b >> lg] < lastw[a >> lg]) flg[i] |= zebra::kFlagDstFirst;
-        if (oa) lastw[a >> lg] = i;
-        if (ob) lastw[b >> lg] = i;
+        if (oa && ob && a != b && dep[b >> lg].lastw < dep[a >> lg].lastw) flg[i] |= zebra::kFlagDstFirst;
+        if (oa) dep[a >> lg].lastw = i;
+        if (ob) dep[b >> lg].lastw = i;
     }
     for (int32_t i : list) {
-        if ((o_src[i] & pm) == me) lastw[o_src[i] >> lg] = -1;
-        if ((o_dst[i] & pm) == me) lastw[o_dst[i] >> lg] = -1;
-        if ((o_neg[i] & pm) == me) { rhead[o_neg[i] >> lg] = -1; rcount[o_neg[i] >> lg] = 0; }
+        if ((o_src[i] & pm) == me) dep[o_src[i] >> lg].lastw = -1;
+        if ((o_dst[i] & pm) == me) dep[o_dst[i] >> lg].lastw = -1;
+        if ((o_neg[i] & pm) == me) { dep[o_neg[i] >> lg].rhead = -1; dep[o_neg[i] >> lg].rcount = 0; }
     }
     return 0;
 }
@@ -412,7 +415,7 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
                                                   : zebra_tppr_out_bytes(h, n_total, rows_per_edge);
             if (need + out_off > h->out_region) return fail("output of %zu bytes at offset %zu exceeds the shared output region (%zu)", need, out_off, h->out_region);
         }
-        p.world_log2 = h->world_log2; p.rank = h->rank; p.mbox_parity = h->launch_parity;
+        p.world_log2 = h->world_log2; p.rank = h->rank; p.mbox_parity = h->launch_parity; p.row_mode = h->row_mode;
         p.mbox_half_bytes = static_cast<int64_t>(h->mbox_half);
         for (int r = 0; r < h->world; ++r) {
             p.mbox_peer[r] = h->peer_arena[r];
@@ -511,9 +514,7 @@ int zebra_tppr_create(zebra_tppr_t **out, int64_t num_nodes, int32_t k, int32_t 
     h->stride = static_cast<int32_t>(record_bytes(k));
     h->table_rows = num_nodes;
     for (int j = 0; j < n_tppr; ++j) { h->alpha[j] = alpha_list[j]; h->beta[j] = beta_list[j]; }
-    h->lastw.assign(static_cast<size_t>(num_nodes), -1);
-    h->rhead.assign(static_cast<size_t>(num_nodes), -1);
-    h->rcount.assign(static_cast<size_t>(num_nodes), 0u);
+    h->dep.assign(static_cast<size_t>(num_nodes), NodeDep{-1, -1, 0u, 0u});
     CU(cudaMalloc(&h->rcnt, sizeof(int32_t) * num_nodes * n_tppr));
     CU(cudaMemset(h->rcnt, 0, sizeof(int32_t) * num_nodes * n_tppr));
     { std::lock_guard<std::mutex> lk(g_seq_mu); h->epoch = g_epoch; }
@@ -1065,6 +1066,14 @@ int zebra_tppr_shard_reset(zebra_tppr_t *h, void *stream)
         CU(cudaMemsetAsync(h->tables[j], 0, static_cast<size_t>(h->table_rows) * h->stride, st));
     CU(cudaMemsetAsync(h->rcnt, 0, sizeof(int32_t) * h->num_nodes * h->n_tppr, st));
     h->plan_active = nullptr;
+    return 0;
+}
+
+int zebra_tppr_shard_row_mode(zebra_tppr_t *h, int32_t mode)
+{
+    if (!h || !h->own_tables) return fail("not a sharded handle");
+    if (mode != 0 && mode != 1) return fail("row mode must be 0 (replicate) or 1 (batch b to rank b & (world-1))");
+    h->row_mode = mode;
     return 0;
 }
 

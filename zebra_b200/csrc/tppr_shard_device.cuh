@@ -22,8 +22,9 @@
 // every peer's pushes of launch n, hence every peer has at least started launch n and finished n-1).
 //
 // Output rows (utils/util.py:447-469) are written by the owner of the node they describe, straight
-// into the output region of EVERY rank (peer stores), so after the launch each rank holds the
-// complete batch result, as data-parallel training needs it.
+// into the output region of the consuming rank(s) (peer stores): row_mode 0 replicates every row on
+// every rank, row_mode 1 delivers the rows of batch b to rank b & (world-1) only — what data-parallel
+// training consumes (each rank works on its own batches), with 1/world of the NVLink store traffic.
 #pragma once
 #include "tppr_device.cuh"
 
@@ -174,8 +175,10 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
         if (p.rows_per_edge >= 2) {
             int64_t row = p.i_offset + i, nrow = p.n_total;
             size_t off = 0;
+            int q_lo = 0, q_hi = world;              // destination ranks of this edge's rows
             if (p.batch_size > 0) {
                 const int64_t b = row / p.batch_size;
+                if (p.row_mode == 1) { q_lo = static_cast<int>(b & pmask); q_hi = q_lo + 1; }
                 row -= b * p.batch_size;
                 nrow = p.n_total - b * p.batch_size;
                 if (nrow > p.batch_size) nrow = p.batch_size;
@@ -186,7 +189,7 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
             // a row is written by the owner of the node it describes, into every rank's output region
             const bool eS = oS, eD = oD;
             const bool eG = has_neg && (neg_own ? oG : (gN == sN ? oS : oD));
-            for (int q = 0; q < world; ++q) {
+            for (int q = q_lo; q < q_hi; ++q) {
                 char *obase = p.out_peer[q] + off;
                 if (eS) emit_row(p, obase, plane, row, S, t, lane);
                 if (eD) emit_row(p, obase, plane, row + nrow, D, t, lane);

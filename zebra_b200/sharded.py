@@ -31,10 +31,11 @@ def local_row(nodes, world: int):
     return np.asarray(nodes) >> (int(world).bit_length() - 1)
 
 
-def exchange_stats(src, dst, neg, world: int, k: int, n_tppr: int):
+def exchange_stats(src, dst, neg, world: int, k: int, n_tppr: int, row_mode: int = 0):
     """What the sharded kernel moves over NVLink for a span, computed from the edge list alone:
     cross-shard edges push two old vectors per instance (24k+8 algorithmic bytes each, SURVEY.md
-    §8d), and every output row (16k bytes per instance) is stored to the world-1 other ranks."""
+    §8d), and every output row (16k bytes per instance) is stored to the world-1 other ranks
+    (row_mode 0) or to its one consumer rank, remote with probability (world-1)/world (row_mode 1)."""
     src, dst = np.asarray(src), np.asarray(dst)
     os_, od = owner_of(src, world), owner_of(dst, world)
     cross = int(np.count_nonzero((os_ != od) & (src != dst)))
@@ -43,7 +44,7 @@ def exchange_stats(src, dst, neg, world: int, k: int, n_tppr: int):
     return {
         "edges": int(len(src)), "cross_edges": cross, "cross_fraction": cross / max(1, len(src)),
         "mailbox_bytes": cross * 2 * n_tppr * (24 * k + 8),
-        "row_bytes": rows * n_tppr * 16 * k * (world - 1),
+        "row_bytes": rows * n_tppr * 16 * k * (world - 1) if row_mode == 0 else rows * n_tppr * 16 * k * (world - 1) // world,
         "updates_per_rank": per_rank_updates.tolist(),
     }
 
@@ -115,6 +116,11 @@ class ShardedFinder:
         arr = (C.c_void_p * len(finders))(*[f._h for f in finders])
         for f in finders:
             f._check(f._L.zebra_tppr_shard_connect_local(f._h, arr))
+
+    def set_row_mode(self, mode):
+        """0: every rank receives every row (default); 1: the rows of batch b go to rank b & (world-1)."""
+        self._check(self._L.zebra_tppr_shard_row_mode(self._h, int(mode)))
+        self.row_mode = int(mode)
 
     def set_max_blocks(self, blocks):
         self._check(self._L.zebra_tppr_set_max_blocks(self._h, int(blocks)))
@@ -209,11 +215,13 @@ def _ShardedPlan(*a, **kw):
     return _make_sharded_plan_class()(*a, **kw)
 
 
-def create_sharded(num_nodes, k, n_tppr, alpha_list, beta_list, max_window_edges, out_bytes, group=None, device=None):
+def create_sharded(num_nodes, k, n_tppr, alpha_list, beta_list, max_window_edges, out_bytes, group=None, device=None,
+                   row_mode=0):
     """torchrun entry: build this rank's ShardedFinder, exchange IPC handles, connect, barrier."""
     import torch.distributed as dist
     rank, world = dist.get_rank(group), dist.get_world_size(group)
     f = ShardedFinder(num_nodes, k, n_tppr, alpha_list, beta_list, rank, world, max_window_edges, out_bytes, device=device)
+    f.set_row_mode(row_mode)
     f.connect(gather_handles(f.ipc_handle, group))
     dist.barrier(group)
     return f
