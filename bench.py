@@ -174,7 +174,7 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
     from zebra_b200.sharded import create_sharded, exchange_stats
     # batches per launch grow with N so that one launch holds as much work per community as at N=1
     # (every launch boundary drains all dependency chains on all ranks)
-    window = args.batches_per_launch * world
+    window = args.shard_batches_per_launch * world
     slot = len(ALPHAS) * 16 * 3 * BS * K
     main = torch.cuda.current_stream()
     copy_stream = torch.cuda.Stream()
@@ -489,6 +489,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--edges", type=int, default=None, help="truncate the stream (debug only)")
     ap.add_argument("--batches-per-launch", type=int, default=64)
+    ap.add_argument("--shard-batches-per-launch", type=int, default=256, help="N>1: batches per launch PER GPU")
     ap.add_argument("--e2e-batches", type=int, default=2000)
     ap.add_argument("--e2e-window", type=int, default=128)
     ap.add_argument("--cpu-sample-edges", type=int, default=1_000_000)
