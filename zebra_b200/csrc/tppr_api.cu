@@ -730,7 +730,7 @@ int zebra_tppr_plan_create(zebra_tppr_t *h, const int32_t *host_src, const int32
     pl->h = h; pl->n = n; pl->batch_size = batch_size; pl->rows_per_edge = rows_per_edge;
     pl->n_batches = (n + batch_size - 1) / batch_size;
     pl->cap = (static_cast<size_t>(n) + 7) & ~static_cast<size_t>(7);
-    if (n >= 0x70000000LL) { delete pl; return fail("plan too long"); }
+    if (n >= 0x70000000LL || batch_size >= 0x70000000LL) { delete pl; return fail("plan too long"); }
     // staging image of the span (uninitialised: a sharded rank fills only the records it takes part in)
     std::unique_ptr<char[]> host(new char[pl->cap * kEdgeBytes]);
     std::vector<int32_t> list;
@@ -889,6 +889,7 @@ int zebra_tppr_epoch_begin(zebra_tppr_t *h, const int32_t *host_src, const int32
     if (rows_per_edge != 0 && rows_per_edge != 2 && rows_per_edge != 3) return fail("rows_per_edge must be 0, 2 or 3");
     if (!host_src || !host_dst || !host_ts || !host_eidx || (rows_per_edge == 3 && !host_neg)) return fail("null input");
     if (batch_size * batches_per_window > (1 << 22)) return fail("window too long (max 2^22 edges)");
+    if (n >= 0x70000000LL) return fail("epoch too long");
     for (int j = 0; j < h->n_tppr; ++j)
         if (!h->tables[j]) return fail("zebra_tppr_bind_tables has not been called");
     if (h->plan_active || h->epoch_active) return fail("another plan or epoch is in progress on this handle");

@@ -284,6 +284,45 @@ __device__ __forceinline__ int qs_partition(WarpScratch &s, int low, int high, i
     return i;
 }
 
+// The same step for a range of at most 32 positions: one position per lane (position = low + lane),
+// 32-bit stopper bitmaps, half the votes and population counts of the two-position version.
+__device__ __forceinline__ int qs_partition32(WarpScratch &s, int low, int high, int lane)
+{
+    const int mid = (low + high) >> 1;
+    const int pos = low + lane;
+    unsigned il = s.Q[low], im = s.Q[mid], ih = s.Q[high];
+    unsigned q = s.Q[pos <= high ? pos : high];
+    if ((im >> 8) < (il >> 8)) { const unsigned t = il; il = im; im = t; }
+    if ((ih >> 8) < (im >> 8)) { const unsigned t = ih; ih = im; im = t; }
+    if ((im >> 8) < (il >> 8)) { const unsigned t = il; il = im; im = t; }
+    const unsigned pivot = im >> 8;
+    if (pos == low) q = il; else if (pos == mid) q = ih;
+    const bool in = pos < high;
+    const bool L = in && (q >> 8) >= pivot;          // i stops here
+    const bool R = in && (q >> 8) <= pivot;          // j stops here
+    const unsigned Lm = __ballot_sync(kFull, L), Rm = __ballot_sync(kFull, R);
+    const int lb = __popc(Lm & ((1u << lane) - 1));
+    const int ra = __popc((Rm >> lane) >> 1);
+    const bool swL = L && ra > lb, swR = R && lb > ra;
+    if (swL) s.X[lb] = static_cast<unsigned short>(q);
+    if (swR) s.Y[ra] = static_cast<unsigned short>(q);
+    const int M = __popc(__ballot_sync(kFull, swL));
+    const unsigned lM = __ballot_sync(kFull, L && lb == M);
+    const unsigned rM = __ballot_sync(kFull, R && ra == M - 1);
+    const int bound = (M > 0 && rM) ? low + __ffs(rM) - 1 : high;
+    int i = lM ? low + __ffs(lM) - 1 : 64;
+    if (bound < i) i = bound;
+    __syncwarp();
+    if (swL) q = s.Y[lb];
+    if (swR) q = s.X[ra];
+    if (in) {
+        if (pos == i) { s.Q[high] = static_cast<unsigned short>(q); s.Q[pos] = static_cast<unsigned short>(im); }
+        else s.Q[pos] = static_cast<unsigned short>(q);
+    } else if (pos == high && i == high) s.Q[pos] = static_cast<unsigned short>(im);
+    __syncwarp();
+    return i;
+}
+
 // Runs the partition phase of numba's argsort on the n items in Q; afterwards a stable sort of the
 // permuted sequence equals numba's final order (its insertion sort on segments < 16 is stable).
 // Leaves P[candidate] = position.
@@ -295,7 +334,7 @@ __device__ __forceinline__ void qs_partition_phase(WarpScratch &s, int n, int la
     int low = 0, high = n - 1;
     for (;;) {
         while (high - low >= 15) {
-            const int i = qs_partition(s, low, high, lane);
+            const int i = (high - low <= 31) ? qs_partition32(s, low, high, lane) : qs_partition(s, low, high, lane);
             int push = -1;
             if (high - i > i - low) {
                 if (high > i) push = ((i + 1) << 8) | high;
@@ -577,7 +616,7 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
         tk = __shfl_sync(kFull, tk, 0);
         if (tk >= total) break;
         ZP_DECL;
-        const int64_t i = tk / p.n_tppr;
+        const int64_t i = tk / static_cast<uint32_t>(p.n_tppr);     // 32-bit division: items < 2^32
         const int j = tk - i * p.n_tppr;
         const int sN = p.src[i], dN = p.dst[i];
         const bool has_neg = p.rows_per_edge == 3;
@@ -681,11 +720,12 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
             int64_t row = p.i_offset + i, nrow = p.n_total;
             char *obase = p.out;
             if (p.batch_size > 0) {
-                const int64_t b = row / p.batch_size;
+                // plans and epochs are shorter than 2^31 edges (checked on the host): 32-bit divisions
+                const int64_t b = static_cast<uint32_t>(row) / static_cast<uint32_t>(p.batch_size);
                 row -= b * p.batch_size;
                 nrow = p.n_total - b * p.batch_size;
                 if (nrow > p.batch_size) nrow = p.batch_size;
-                obase += static_cast<size_t>((b - p.first_batch) % p.out_slots) * p.slot_bytes;
+                obase += static_cast<size_t>(static_cast<uint32_t>(b - p.first_batch) % static_cast<uint32_t>(p.out_slots)) * p.slot_bytes;
             }
             const size_t plane = static_cast<size_t>(nrow) * p.rows_per_edge * k;
             obase += static_cast<size_t>(j) * plane * 16;

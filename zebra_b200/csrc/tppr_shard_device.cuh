@@ -71,7 +71,7 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
         if (lane == 0) tk = atomicAdd(p.ticket, 1u) - p.ticket_base;
         tk = __shfl_sync(kFull, tk, 0);
         if (tk >= total) break;
-        const int64_t li = tk / p.n_tppr;
+        const int64_t li = tk / static_cast<uint32_t>(p.n_tppr);    // 32-bit division: items < 2^32
         const int j = tk - li * p.n_tppr;
         if (!((p.inst_mask >> j) & 1)) continue;
         const int64_t i = static_cast<int64_t>(p.list[li]) - p.i_offset;     // launch-local edge index
@@ -177,12 +177,13 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
             size_t off = 0;
             int q_lo = 0, q_hi = world;              // destination ranks of this edge's rows
             if (p.batch_size > 0) {
-                const int64_t b = row / p.batch_size;
+                // plans and epochs are shorter than 2^31 edges (checked on the host): 32-bit divisions
+                const int64_t b = static_cast<uint32_t>(row) / static_cast<uint32_t>(p.batch_size);
                 if (p.row_mode == 1) { q_lo = static_cast<int>(b & pmask); q_hi = q_lo + 1; }
                 row -= b * p.batch_size;
                 nrow = p.n_total - b * p.batch_size;
                 if (nrow > p.batch_size) nrow = p.batch_size;
-                off = static_cast<size_t>((b - p.first_batch) % p.out_slots) * p.slot_bytes;
+                off = static_cast<size_t>(static_cast<uint32_t>(b - p.first_batch) % static_cast<uint32_t>(p.out_slots)) * p.slot_bytes;
             }
             const size_t plane = static_cast<size_t>(nrow) * p.rows_per_edge * k;
             off += static_cast<size_t>(j) * plane * 16;
