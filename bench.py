@@ -50,6 +50,30 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic():
+    """DRAM bytes per span-kernel launch (read + write) from the newest committed `ncu --set full` capture
+    of this command (profiles/*ncu_full_span*_raw.csv), or None."""
+    import csv
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*ncu_full_span*_raw.csv")))
+    if not files:
+        return None, None
+    try:
+        rows = list(csv.reader(open(files[-1])))
+        hdr, units, data = rows[0], rows[1], rows[2:]
+        tot = []
+        for r in data:
+            b = 0.0
+            for name in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                i = hdr.index(name)
+                scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[units[i]]
+                b += float(r[i]) * scale
+            tot.append(b)
+        return (sum(tot) / len(tot), os.path.relpath(files[-1], ROOT)) if tot else (None, None)
+    except Exception:
+        return None, None
+
+
 class ClockSampler:
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
@@ -429,6 +453,7 @@ def run_ours(args):
         per_launch_ms = ms / max(launches, 1)
         alg_per_launch = E * bytes_per_edge() / n_launch
         achieved = alg_per_launch / (per_launch_ms * 1e-3) / 1e9
+        traffic, traffic_src = (args.traffic, "--traffic") if args.traffic is not None else ncu_traffic()
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -449,8 +474,9 @@ def run_ours(args):
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": args.traffic, "peak_source": peak_src, "kernel": "tppr_span_kernel",
-                         "bytes_per_edge": bytes_per_edge(), "launch_ms": per_launch_ms},
+                         "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "kernel": "tppr_span_kernel",
+                         "bytes_per_edge": bytes_per_edge(), "algorithmic_bytes_per_launch": alg_per_launch,
+                         "launch_ms": per_launch_ms},
         }
         if world == 1 and not args.no_flat:
             # the same kernel on a hub-free stream of the same size class (uniform endpoints): no long
