@@ -162,7 +162,13 @@ def run_reference(args):
         return
     threads = len(ALPHAS)          # the only parallelism the algorithm admits: independent instances
     sample = args.ref_sample_edges
-    st, neg = load_workload(n_edges=min(sample, 7_833_140))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world > 1:
+        # same workload as our arm at this N: `world` communities merged into one stream
+        from zebra_b200 import synth
+        st, neg = synth.make_communities(WORKLOAD, world, BS, n_edges=-(-sample // world))
+    else:
+        st, neg = load_workload(n_edges=min(sample, 7_833_140))
     vals = []
     for _ in range(max(1, min(args.warmup, 1))):
         cpu_port_throughput(st, neg, min(sample, 100_000), threads)
@@ -175,7 +181,8 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * t_all / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"{WORKLOAD}-shaped synthetic stream, streaming T-PPR topk={K}, alpha {ALPHAS}, beta {BETAS}, bs={BS}",
+        "config": {"workload": (f"{world} {WORKLOAD}-shaped communities merged into one stream" if world > 1 else
+                                f"{WORKLOAD}-shaped synthetic stream") + f", streaming T-PPR topk={K}, alpha {ALPHAS}, beta {BETAS}, bs={BS}",
                    "sample": f"first {sample} edges per step"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
                          "sample": f"first {sample} edges of the workload, bs={BS}, with negatives; one thread per (alpha,beta) instance"},

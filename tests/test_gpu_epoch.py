@@ -88,3 +88,38 @@ def test_epoch_window_mode_and_update_only():
     for j in range(2):
         for (e, n, t, s, nm), (e2, n2, t2, s2, nm2) in zip(f.state(j, ids), g.state(j, ids)):
             assert np.array_equal(e, e2) and np.array_equal(n, n2) and np.array_equal(s, s2) and nm == nm2
+
+
+def test_epoch_error_behaviour():
+    """Misuse fails loudly through zebra_last_error, and leaves the handle usable."""
+    st = synth.make_stream("wikipedia", n_edges=1000, seed=4)
+    neg = synth.make_negatives(st, 200)
+    N = st.shape.table_nodes
+    f = _finder(N, 20, 2, [0.1, 0.1], [0.5, 0.95])
+    with pytest.raises(ValueError):
+        list(f.stream_epoch(st.src, st.dst[:-1], neg, st.ts, st.eidx, 200))
+    with pytest.raises(RuntimeError, match="rows_per_edge"):
+        list(f.stream_epoch(st.src, st.dst, neg, st.ts, st.eidx, 200, rows_per_edge=1))
+    with pytest.raises(RuntimeError, match="null input"):
+        list(f.stream_epoch(st.src, st.dst, None, st.ts, st.eidx, 200, rows_per_edge=3))
+    bad = st.src.copy()
+    bad[700] = N + 5                                            # out-of-range node in the fourth batch
+    it = f.stream_epoch(bad, st.dst, neg, st.ts, st.eidx, 200, window=1)
+    with pytest.raises(RuntimeError, match="out of range"):
+        list(it)
+    # an epoch abandoned half-way releases the handle when the generator is closed
+    it = f.stream_epoch(st.src, st.dst, neg, st.ts, st.eidx, 200, window=1)
+    next(it)
+    with pytest.raises(RuntimeError, match="in progress|part-way"):
+        f.streaming_topk(np.concatenate([st.src[:200], st.dst[:200], neg[:200]]).astype(np.int32),
+                         np.concatenate([st.ts[:200]] * 3), st.eidx[:200])
+    it.close()
+    f.reset_tppr()
+    cpu = oracle.OracleFinder(N, 20, 2, [0.1, 0.1], [0.5, 0.95])
+    for b, out in enumerate(f.stream_epoch(st.src, st.dst, neg, st.ts, st.eidx, 200, window=2)):
+        lo, hi = b * 200, (b + 1) * 200
+        ref = cpu.streaming_topk(np.concatenate([st.src[lo:hi], st.dst[lo:hi], neg[lo:hi]]).astype(np.int32),
+                                 np.concatenate([st.ts[lo:hi]] * 3), st.eidx[lo:hi])
+        for la, lb in zip(out, ref):
+            for x, y in zip(la, lb):
+                assert np.array_equal(x, y)

@@ -128,3 +128,26 @@ def test_sharded_row_mode_delivers_each_batch_to_one_rank(world):
                         assert np.array_equal(x.cpu().numpy(), y), f"rank {f.rank} batch {b}"
             else:                                  # never written: still the zero fill of the arena
                 assert all(int(torch.count_nonzero(x)) == 0 for la in got for x in la), f"rank {f.rank} batch {b}"
+
+
+def test_sharded_error_behaviour():
+    from zebra_b200.sharded import ShardedFinder
+    st = synth.make_stream("wikipedia", n_edges=1000, seed=4)
+    neg = synth.make_negatives(st, 200)
+    N = st.shape.table_nodes
+    with pytest.raises(RuntimeError, match="world must be"):
+        ShardedFinder(N, 20, 2, AL, BE, 0, 3, 1000, 1 << 20)
+    f = ShardedFinder(N, 20, 2, AL, BE, 0, 2, 400, 1 << 20)
+    plan = f.make_plan(st.src, st.dst, neg, st.ts, st.eidx, 200)
+    with pytest.raises(RuntimeError, match="shard_connect"):
+        plan.run(0, 1, 1)                                       # peers not connected yet
+    with pytest.raises(ValueError, match="window"):
+        plan.run(0, 4, 4)                                       # 800 edges > the 400-edge mailbox window
+    g = ShardedFinder(N, 20, 2, AL, BE, 1, 2, 400, 1 << 20)
+    ShardedFinder.connect_local([f, g])
+    with pytest.raises(RuntimeError, match="exceeds the shared output region"):
+        plan.run(0, 5, 1, out_slots=5, out_offset=(1 << 20) - 4096)
+    with pytest.raises(RuntimeError, match="stream through plans"):
+        f._check(f._L.zebra_tppr_update_only(f._h, None, None, None, None, 0, None) or
+                 f._L.zebra_tppr_stream(f._h, st.src[:2].ctypes.data, st.ts[:2].ctypes.data, st.eidx[:1].ctypes.data, 1, 2, -1,
+                                        None, None, None))
