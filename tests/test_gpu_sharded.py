@@ -148,6 +148,6 @@ def test_sharded_error_behaviour():
     with pytest.raises(RuntimeError, match="exceeds the shared output region"):
         plan.run(0, 5, 1, out_slots=5, out_offset=(1 << 20) - 4096)
     with pytest.raises(RuntimeError, match="stream through plans"):
-        f._check(f._L.zebra_tppr_update_only(f._h, None, None, None, None, 0, None) or
-                 f._L.zebra_tppr_stream(f._h, st.src[:2].ctypes.data, st.ts[:2].ctypes.data, st.eidx[:1].ctypes.data, 1, 2, -1,
+        nodes = np.concatenate([st.src[:1], st.dst[:1]]).astype(np.int32)
+        f._check(f._L.zebra_tppr_stream(f._h, nodes.ctypes.data, st.ts[:1].ctypes.data, st.eidx[:1].ctypes.data, 1, 2, -1,
                                         None, None, None))

@@ -468,8 +468,8 @@ int run_span(zebra_tppr *h, const NodeT *src, const NodeT *dst, const NodeT *neg
 {
     for (int j = 0; j < h->n_tppr; ++j)
         if (!h->tables[j]) return fail("zebra_tppr_bind_tables has not been called");
-    if (h->plan_active || h->epoch_active) return fail("a plan or epoch is part-way through its batches; finish it before streaming other spans");
     if (h->world > 1) return fail("node-sharded handles stream through plans (zebra_tppr_plan_run): dependencies must be span-global across ranks");
+    if (h->plan_active || h->epoch_active) return fail("a plan or epoch is part-way through its batches; finish it before streaming other spans");
     CU(cudaSetDevice(h->device));
     CU(cudaMemsetAsync(h->status + 1, 0, 3 * sizeof(int32_t), st));   // [0] (time-out) is sticky
     h->last_items = 0;
@@ -813,7 +813,10 @@ int zebra_tppr_plan_run(zebra_tppr_t *h, zebra_plan_t *pl, int64_t first_batch, 
             n_list = pl->batch_ofs[static_cast<size_t>(be)] - pl->batch_ofs[static_cast<size_t>(b)];
         }
         if (launch_kernel(h, pl->dev, pl->cap, lo, hi - lo, pl->n, lo, pl->rows_per_edge, (1 << h->n_tppr) - 1,
-                          static_cast<char *>(dev_out), bo, pl->seq0, lo, st, list, n_list)) return 1;
+                          static_cast<char *>(dev_out), bo, pl->seq0, lo, st, list, n_list)) {
+            h->plan_active = nullptr;          // a failed launch abandons the run
+            return 1;
+        }
     }
     CU(cudaEventRecord(h->ev1, st));
     h->timed = true;
