@@ -37,6 +37,7 @@ int zebra_gather_fwd(const void *dev_topk, int32_t n_tppr, int64_t rows, int32_t
         return fail("null device pointer");
     if (n_tppr < 1 || rows < 0 || k < 1 || dim_mem < 1 || dim_edge < 1 || dim_time < 1) return fail("bad gather shape");
     if ((dev_src_rows != nullptr) != (dev_src_nodes != nullptr)) return fail("src_nodes and src_rows go together");
+    if (static_cast<double>(n_tppr) * static_cast<double>(rows) * k >= 2147483648.0) return fail("gather of 2^31 slots or more");
     if (rows == 0) return 0;
     if (ensure_status()) return 1;
     zebra::GatherParams p;
@@ -63,6 +64,7 @@ int zebra_gather_bwd(const void *dev_topk, int32_t n_tppr, int64_t rows, int32_t
 {
     if (!dev_topk || !dev_gx || !dev_wn || !dev_gmemory) return fail("null device pointer");
     if ((dev_gsrc != nullptr) != (dev_src_nodes != nullptr)) return fail("src_nodes and g_src go together");
+    if (static_cast<double>(n_tppr) * static_cast<double>(rows) * k >= 2147483648.0) return fail("gather of 2^31 slots or more");
     if (rows == 0) return 0;
     zebra::GatherBwdParams p;
     memset(&p, 0, sizeof p);

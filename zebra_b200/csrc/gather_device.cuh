@@ -71,7 +71,8 @@ gather_fwd_kernel(const GatherParams p)
     const int64_t plane = p.R * p.k;
     const int D = p.Dm + p.De + p.Dt;
     if (warp < slots) {
-        const int64_t j = warp / plane, o = warp - j * plane;
+        // slot counts stay below 2^31 (checked on the host): 32-bit divisions
+        const int64_t j = static_cast<uint32_t>(warp) / static_cast<uint32_t>(plane), o = warp - j * plane;
         const char *base = p.topk + static_cast<size_t>(j) * plane * 16;
         const int node = reinterpret_cast<const int32_t *>(base)[o];
         const int eidx = reinterpret_cast<const int32_t *>(base + plane * 4)[o];
@@ -98,7 +99,7 @@ gather_fwd_kernel(const GatherParams p)
             }
         }
         // normalised weights: the warp of slot 0 of each row handles the row's k weights
-        const int64_t row = o / p.k;
+        const int64_t row = static_cast<uint32_t>(o) / static_cast<uint32_t>(p.k);
         if (o - row * p.k == 0) {
             const float *w = reinterpret_cast<const float *>(base + plane * 12) + row * p.k;
             float *out = p.wn + static_cast<size_t>(j) * plane + row * p.k;
@@ -140,7 +141,8 @@ gather_bwd_kernel(const GatherBwdParams p)
     const float *g;
     int node;
     if (warp < slots) {
-        const int64_t j = warp / plane, o = warp - j * plane;
+        // slot counts stay below 2^31 (checked on the host): 32-bit divisions
+        const int64_t j = static_cast<uint32_t>(warp) / static_cast<uint32_t>(plane), o = warp - j * plane;
         if (p.wn[warp] == 0.f) return;
         node = reinterpret_cast<const int32_t *>(p.topk + static_cast<size_t>(j) * plane * 16)[o];
         g = p.gX + static_cast<size_t>(warp) * p.D;
