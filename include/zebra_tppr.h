@@ -257,6 +257,17 @@ int zebra_gather_bwd(const void *dev_topk, int32_t n_tppr, int64_t rows, int32_t
                      const float *dev_wn, const float *dev_gsrc, const int32_t *dev_src_nodes,
                      float *dev_gmemory, int64_t num_nodes, int32_t dim_mem, int32_t dim_total,
                      void *stream);
+/* Reproducible variant of the backward (no atomics): the caller passes the sources sorted by
+ * destination node — sources [0, n_tppr*rows*k) are the gather slots in buffer order, the next
+ * `rows` are the src rows (only if dev_gsrc != NULL); dev_order int64[total] is a STABLE sort
+ * permutation of the source indices by node id, dev_sorted_nodes int32[total] the node ids in that
+ * order.  Every node's sources are summed one after the other in that order and stored;
+ * dev_gmemory must be zero-filled.  This mirrors the reference's backward, whose index_put with
+ * accumulate sorts as well (torch IndexBackward), so a level-1 run is reproducible run to run. */
+int zebra_gather_bwd_sorted(int32_t n_tppr, int64_t rows, int32_t k, const float *dev_gx, const float *dev_wn,
+                            const float *dev_gsrc, const int32_t *dev_sorted_nodes, const int64_t *dev_order,
+                            float *dev_gmemory, int64_t num_nodes, int32_t dim_mem, int32_t dim_total,
+                            void *stream);
 int zebra_gather_check(void *stream);
 
 const char *zebra_last_error(void);

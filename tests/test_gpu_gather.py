@@ -113,3 +113,53 @@ def test_embedding_matches_reference_recording(strategy, name, n_edges, d_e):
                 ref = torch.from_numpy(g[f"emb_{b}"]).to(dev)
                 assert emb.shape == ref.shape == (600, 300)
                 torch.testing.assert_close(emb, ref, rtol=2e-5, atol=2e-5)
+
+
+def test_gather_backward_sorted_is_reproducible_and_matches_atomic():
+    """The default (sorted) backward gives bit-identical gradients run after run; the atomic variant agrees
+    with it to fp32 rounding.  Hub-like ids (many slots on few nodes) make the summation order matter."""
+    from zebra_b200 import embedding as E
+    dev = torch.device("cuda")
+    g = torch.Generator(device="cpu").manual_seed(5)
+    R, k, n_tppr, Dm, De, Dt, N, Ee = 600, 20, 2, 100, 4, 100, 300, 500
+    memory = torch.randn(N, Dm, generator=g).to(dev).requires_grad_(True)
+    ef = torch.randn(Ee, De, generator=g).to(dev)
+    tw = torch.from_numpy(1 / 10 ** np.linspace(0, 9, Dt, dtype=np.float32)).to(dev)
+    tb = torch.zeros(Dt, device=dev)
+    ids = torch.randint(0, 12, (n_tppr, R, k), generator=g, dtype=torch.int32)          # 12 hot nodes
+    ids[:, ::3] = torch.randint(0, N, (n_tppr, (R + 2) // 3, k), generator=g, dtype=torch.int32)
+    eidx = torch.randint(0, Ee, (n_tppr, R, k), generator=g, dtype=torch.int32)
+    dt = (torch.rand(n_tppr, R, k, generator=g) * 1e5).float()
+    w = torch.rand(n_tppr, R, k, generator=g).float()
+    w[:, 1::5, k // 2:] = 0
+    src = torch.randint(0, N, (R,), generator=g, dtype=torch.int32).to(dev)
+    topk = torch.cat([torch.cat([x[j].reshape(-1).view(torch.uint8) for x in (ids, eidx, dt, w)]) for j in range(n_tppr)]).to(dev)
+    gX = gS = None
+
+    def grad(reproducible):
+        nonlocal gX, gS
+        old = E.REPRODUCIBLE_BACKWARD
+        E.REPRODUCIBLE_BACKWARD = reproducible
+        try:
+            X, wn, srows = E.FusedGather.apply(memory, topk, src, ef, tw, tb, n_tppr, R, k)
+            if gX is None:
+                gX = torch.randn(X.shape, generator=g).to(dev) * (wn.reshape(n_tppr, R * k, 1) != 0)
+                gS = torch.randn(srows.shape, generator=g).to(dev)
+            memory.grad = None
+            (X * gX).sum().add((srows * gS).sum()).backward()
+            return memory.grad.clone()
+        finally:
+            E.REPRODUCIBLE_BACKWARD = old
+
+    a, b = grad(True), grad(True)
+    assert torch.equal(a, b), "sorted backward must be bit-reproducible"
+    c = grad(False)
+    torch.testing.assert_close(a, c, rtol=1e-4, atol=1e-3)
+    # against torch's own (sort-based) backward of the same gathers
+    memory.grad = None
+    ref = 0
+    for j in range(n_tppr):
+        Xr, _, _ = _torch_reference(memory, ef, tw, tb, ids[j].to(dev), eidx[j].to(dev), dt[j].to(dev), w[j].to(dev), src)
+        ref = ref + (Xr.reshape(R * k, -1) * gX[j]).sum()
+    (ref + (memory[src.long()] * gS).sum()).backward()
+    torch.testing.assert_close(a, memory.grad, rtol=1e-4, atol=1e-3)

@@ -50,6 +50,7 @@ SIGNATURES = {
     "zebra_prune_launches": (_I64, [_VP]),
     "zebra_gather_fwd": (C.c_int, [_VP, _I32, _I64, _I32, _VP, _I64, _I32, _VP, _I64, _I32, _VP, _VP, _I32, _VP, _VP, _VP, _VP, _VP]),
     "zebra_gather_bwd": (C.c_int, [_VP, _I32, _I64, _I32, _VP, _VP, _VP, _VP, _VP, _I64, _I32, _I32, _VP]),
+    "zebra_gather_bwd_sorted": (C.c_int, [_I32, _I64, _I32, _VP, _VP, _VP, _VP, _VP, _VP, _I64, _I32, _I32, _VP]),
     "zebra_gather_check": (C.c_int, [_VP]),
     "zebra_last_error": (C.c_char_p, []),
     "zebra_build_info": (C.c_char_p, []),

@@ -164,4 +164,45 @@ gather_bwd_kernel(const GatherBwdParams p)
     }
 }
 
+// Reproducible backward: the (slot, src-row) sources are visited in the order of a stable sort by
+// destination node (`order` = sorted permutation of the source indices, `keys` = their node ids in
+// that order; sources [0, slots) are gather slots, [slots, slots+R) the src rows).  The warp that
+// sits on the first source of a node sums that node's sources one after the other and STORES the
+// row: fixed summation order, no atomics.  g_memory must be zero-filled beforehand.
+__global__ void __launch_bounds__(256)
+gather_bwd_sorted_kernel(const GatherBwdParams p, const int32_t *keys, const int64_t *order, int64_t total)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t pos = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    if (pos >= total) return;
+    const int node = keys[pos];
+    if (pos > 0 && keys[pos - 1] == node) return;            // not the first source of its node
+    if (node < 0 || node >= p.num_nodes) return;
+    const int64_t slots = static_cast<int64_t>(p.n_tppr) * p.R * p.k;
+    float acc[8];                                             // Dm <= 256 columns: 8 per lane
+#pragma unroll
+    for (int c = 0; c < 8; ++c) acc[c] = 0.f;
+    for (int64_t q = pos; q < total && keys[q] == node; ++q) {
+        const int64_t src = order[q];
+        const float *g;
+        if (src < slots) {
+            if (p.wn[src] == 0.f) continue;                   // exactly-zero gradient (weight 0)
+            g = p.gX + static_cast<size_t>(src) * p.D;
+        } else {
+            g = p.g_src + static_cast<size_t>(src - slots) * p.Dm;
+        }
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            const int col = lane + 32 * c;
+            if (col < p.Dm) acc[c] = __fadd_rn(acc[c], __ldg(g + col));
+        }
+    }
+    float *dst = p.g_memory + static_cast<size_t>(node) * p.Dm;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        const int col = lane + 32 * c;
+        if (col < p.Dm) dst[col] = acc[c];
+    }
+}
+
 }  // namespace zebra

@@ -14,12 +14,19 @@ The function is written against the reference module's attributes (`fc1`, `fc2`,
 from __future__ import annotations
 
 import ctypes as C
+import os
 import time
 
 import numpy as np
 import torch
 
 from ._lib import check, lib
+
+
+# backward of the memory-row gathers: "sorted" (default) sums every node's gradient rows in a fixed order
+# (reproducible, like the reference's index_put backward); "atomic" scatter-adds with red.global (faster on
+# very large batches, not reproducible in the last bits)
+REPRODUCIBLE_BACKWARD = os.environ.get("ZEBRA_GATHER_BACKWARD", "sorted").lower() != "atomic"
 
 
 def _p(t):
@@ -62,8 +69,19 @@ class FusedGather(torch.autograd.Function):
         gsrc = gsrc.contiguous() if gsrc is not None else None
         with torch.cuda.device(dev):
             st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
-            check(lib().zebra_gather_bwd(_p(topk), n_tppr, rows, k, _p(gX), _p(wn), _p(gsrc),
-                                         _p(src_nodes) if gsrc is not None else None, _p(gmem), N, Dm, D, st))
+            if REPRODUCIBLE_BACKWARD and Dm <= 256:
+                # sources sorted (stably) by destination node, summed in that order: run-to-run reproducible,
+                # like the reference's sort-based index_put backward
+                plane = rows * k
+                keys = [topk[j * plane * 16: j * plane * 16 + plane * 4].view(torch.int32) for j in range(n_tppr)]
+                if gsrc is not None:
+                    keys.append(src_nodes.to(torch.int32))
+                skeys, order = torch.sort(torch.cat(keys), stable=True)
+                check(lib().zebra_gather_bwd_sorted(n_tppr, rows, k, _p(gX), _p(wn), _p(gsrc), _p(skeys), _p(order), _p(gmem),
+                                                    N, Dm, D, st))
+            else:
+                check(lib().zebra_gather_bwd(_p(topk), n_tppr, rows, k, _p(gX), _p(wn), _p(gsrc),
+                                             _p(src_nodes) if gsrc is not None else None, _p(gmem), N, Dm, D, st))
         return gmem, None, None, None, None, None, None, None, None
 
 
