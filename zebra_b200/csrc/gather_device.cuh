@@ -34,20 +34,11 @@ struct GatherParams {
     int32_t *status;           // [0] set to 1 on an out-of-range id (row skipped)
 };
 
-// cos of an fp32 argument that can reach 1e6 and more (dt * w, model/time_encoding.py:23-28).  Below
-// libdevice's fast-path limit this IS cosf.  Above it, cosf would run its Payne-Hanek reduction on
-// the few lanes that hold the high frequencies while the rest of the warp waits; instead the argument
-// is reduced in fp64 (two-constant 2*pi: the error after reduction is ~1e-10 for |x| < 2^31) and the
-// fp64 cosine of the reduced argument is rounded to fp32 — at least as accurate as cosf itself.
-__device__ __forceinline__ float cos_arg(float x)
-{
-    if (fabsf(x) <= 100000.f) return cosf(x);
-    const double xd = static_cast<double>(x);
-    const double n = rint(xd * 0.15915494309189535);
-    double r = fma(-n, 6.283185307179586, xd);
-    r = fma(-n, 2.4492935982947064e-16, r);
-    return static_cast<float>(cos(r));
-}
+// Time encoding (model/time_encoding.py:23-28).  The reference runs torch.cos on the GPU, i.e. libdevice's
+// accurate cosf; calling the same routine makes this part of X bit-identical to the reference's (an fp64
+// range reduction for the large arguments was tried: it is as fast and marginally more accurate, but it
+// differs from cosf in the last bit for 20 % of the arguments beyond 1e5 — parity wins).
+__device__ __forceinline__ float cos_arg(float x) { return cosf(x); }
 
 template <bool VEC>
 __device__ __forceinline__ void copy_row(float *dst, const float *src, int n, int lane)
@@ -164,11 +155,16 @@ gather_bwd_kernel(const GatherBwdParams p)
     }
 }
 
-// Reproducible backward: the (slot, src-row) sources are visited in the order of a stable sort by
-// destination node (`order` = sorted permutation of the source indices, `keys` = their node ids in
-// that order; sources [0, slots) are gather slots, [slots, slots+R) the src rows).  The warp that
-// sits on the first source of a node sums that node's sources one after the other and STORES the
-// row: fixed summation order, no atomics.  g_memory must be zero-filled beforehand.
+// Reproducible backward, bit-identical to the reference's autograd.  The reference gathers memory
+// rows with three (n_tppr + 1) separate index operations (embedding_module.py:243-245, 253); torch's
+// backward of each is index_put(accumulate) with a stable sort — duplicates of a node are added one
+// after the other in source order — and autograd then adds the pieces as
+// ((g[n_tppr-1] + g[n_tppr-2]) + ... + g[0]) + g[src]  (reverse order of creation; checked on B200).
+// Here the sources (slots [0, n_tppr*R*k) in buffer order, then the R src rows) arrive stably sorted
+// by destination node (`keys` = node ids in sorted order, `order` = source indices).  The warp that
+// sits on the first source of a node replays exactly that arithmetic: one accumulator per piece,
+// filled in source order, pieces combined in autograd's order, result STORED (g_memory zero-filled
+// beforehand).  No atomics; every run gives the same bits.
 __global__ void __launch_bounds__(256)
 gather_bwd_sorted_kernel(const GatherBwdParams p, const int32_t *keys, const int64_t *order, int64_t total)
 {
@@ -178,30 +174,40 @@ gather_bwd_sorted_kernel(const GatherBwdParams p, const int32_t *keys, const int
     const int node = keys[pos];
     if (pos > 0 && keys[pos - 1] == node) return;            // not the first source of its node
     if (node < 0 || node >= p.num_nodes) return;
-    const int64_t slots = static_cast<int64_t>(p.n_tppr) * p.R * p.k;
-    float acc[8];                                             // Dm <= 256 columns: 8 per lane
+    const int64_t plane = p.R * p.k, slots = static_cast<int64_t>(p.n_tppr) * plane;
+    int64_t end = pos + 1;
+    while (end < total && keys[end] == node) ++end;
+    float tot[8];                                             // Dm <= 256 columns: 8 per lane
 #pragma unroll
-    for (int c = 0; c < 8; ++c) acc[c] = 0.f;
-    for (int64_t q = pos; q < total && keys[q] == node; ++q) {
-        const int64_t src = order[q];
-        const float *g;
-        if (src < slots) {
-            if (p.wn[src] == 0.f) continue;                   // exactly-zero gradient (weight 0)
-            g = p.gX + static_cast<size_t>(src) * p.D;
-        } else {
-            g = p.g_src + static_cast<size_t>(src - slots) * p.Dm;
+    for (int c = 0; c < 8; ++c) tot[c] = 0.f;
+    bool first = true;
+    // sources of a node are in ascending source index, i.e. piece 0, 1, ..., n_tppr-1, src: walk the
+    // pieces in autograd's order and pick each piece's sources out of the run
+    for (int pc = p.n_tppr - 1; pc >= -1; --pc) {
+        if (pc < 0 && !p.g_src) break;
+        const int64_t lo = pc >= 0 ? pc * plane : slots, hi = pc >= 0 ? lo + plane : slots + p.R;
+        float acc[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) acc[c] = 0.f;
+        for (int64_t q = pos; q < end; ++q) {
+            const int64_t src = order[q];
+            if (src < lo || src >= hi) continue;
+            const float *g = pc >= 0 ? p.gX + static_cast<size_t>(src) * p.D : p.g_src + static_cast<size_t>(src - slots) * p.Dm;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const int col = lane + 32 * c;
+                if (col < p.Dm) acc[c] = __fadd_rn(acc[c], __ldg(g + col));
+            }
         }
 #pragma unroll
-        for (int c = 0; c < 8; ++c) {
-            const int col = lane + 32 * c;
-            if (col < p.Dm) acc[c] = __fadd_rn(acc[c], __ldg(g + col));
-        }
+        for (int c = 0; c < 8; ++c) tot[c] = first ? acc[c] : __fadd_rn(tot[c], acc[c]);
+        first = false;
     }
     float *dst = p.g_memory + static_cast<size_t>(node) * p.Dm;
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
         const int col = lane + 32 * c;
-        if (col < p.Dm) dst[col] = acc[c];
+        if (col < p.Dm) dst[col] = tot[c];
     }
 }
 

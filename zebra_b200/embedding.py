@@ -29,6 +29,11 @@ from ._lib import check, lib
 REPRODUCIBLE_BACKWARD = os.environ.get("ZEBRA_GATHER_BACKWARD", "sorted").lower() != "atomic"
 
 
+# weight normalisation of the neighbour sum: the reference's torch ops (default, bit-identical) or the fused
+# kernel's output (ZEBRA_WEIGHT_NORM=fused: saves four small launches per instance, last-bit differences)
+EXACT_WEIGHT_NORM = os.environ.get("ZEBRA_WEIGHT_NORM", "torch").lower() != "fused"
+
+
 def _p(t):
     return None if t is None else C.c_void_p(t.data_ptr())
 
@@ -130,7 +135,17 @@ def compute_embedding_tppr_ensemble(self, memory, source_nodes, timestamps, edge
     embeddings = self.transform_source(src_rows)
     for j in range(n_tppr):
         h = self.transform(X[j]).view(R, k, -1)
-        h = torch.sum(h * wn[j][:, :, None], dim=1)
+        if EXACT_WEIGHT_NORM:
+            # the reference's own three ops (embedding_module.py:268-271) on the device-resident weights:
+            # 12,000 floats per instance, and bit-identical to the reference whatever order torch.sum adds in
+            # (the kernel's wn sums left to right and differs in the last bit for about half of the rows)
+            wj = topk[j * plane * 16 + plane * 12: (j + 1) * plane * 16].view(torch.float32).view(R, k)
+            ws = torch.sum(wj, dim=1)
+            wnj = wj / ws.unsqueeze(1)
+            wnj[ws == 0] = 0
+        else:
+            wnj = wn[j]
+        h = torch.sum(h * wnj[:, :, None], dim=1)
         embeddings = torch.cat((embeddings, h), dim=1)
     return embeddings
 
