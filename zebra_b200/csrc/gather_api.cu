@@ -87,7 +87,7 @@ int zebra_gather_bwd_sorted(int32_t n_tppr, int64_t rows, int32_t k, const float
                             float *dev_gmemory, int64_t num_nodes, int32_t dim_mem, int32_t dim_total, void *stream)
 {
     if (!dev_gx || !dev_wn || !dev_gmemory || !dev_sorted_nodes || !dev_order) return fail("null device pointer");
-    if (dim_mem > 256) return fail("reproducible gather backward supports dim_mem <= 256");
+    if (dim_mem < 1 || dim_mem > 4096) return fail("bad dim_mem");
     if (static_cast<double>(n_tppr) * static_cast<double>(rows) * k >= 2147483648.0) return fail("gather of 2^31 slots or more");
     if (rows == 0) return 0;
     zebra::GatherBwdParams p;
@@ -96,8 +96,9 @@ int zebra_gather_bwd_sorted(int32_t n_tppr, int64_t rows, int32_t k, const float
     p.gX = dev_gx; p.wn = dev_wn; p.g_src = dev_gsrc; p.g_memory = dev_gmemory;
     p.num_nodes = num_nodes; p.Dm = dim_mem; p.D = dim_total;
     const int64_t total = static_cast<int64_t>(n_tppr) * rows * k + (dev_gsrc ? rows : 0);
-    const unsigned blocks = static_cast<unsigned>((total + 7) / 8);
-    zebra::gather_bwd_sorted_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(p, dev_sorted_nodes, dev_order, total);
+    const int chunks = (dim_mem + 31) / 32;
+    const unsigned blocks = static_cast<unsigned>((total * chunks + 7) / 8);
+    zebra::gather_bwd_sorted_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(p, dev_sorted_nodes, dev_order, total, chunks);
     CU(cudaGetLastError());
     return 0;
 }

@@ -166,10 +166,14 @@ gather_bwd_kernel(const GatherBwdParams p)
 // filled in source order, pieces combined in autograd's order, result STORED (g_memory zero-filled
 // beforehand).  No atomics; every run gives the same bits.
 __global__ void __launch_bounds__(256)
-gather_bwd_sorted_kernel(const GatherBwdParams p, const int32_t *keys, const int64_t *order, int64_t total)
+gather_bwd_sorted_kernel(const GatherBwdParams p, const int32_t *keys, const int64_t *order, int64_t total, int chunks)
 {
+    // one warp per (sorted position, chunk of 32 columns): a hub node's long run of sources is walked by
+    // `chunks` warps side by side, one column per lane, several row loads in flight
     const int lane = threadIdx.x & 31;
-    const int64_t pos = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t w = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t pos = w / chunks;
+    const int col = static_cast<int>(w - pos * chunks) * 32 + lane;
     if (pos >= total) return;
     const int node = keys[pos];
     if (pos > 0 && keys[pos - 1] == node) return;            // not the first source of its node
@@ -177,38 +181,38 @@ gather_bwd_sorted_kernel(const GatherBwdParams p, const int32_t *keys, const int
     const int64_t plane = p.R * p.k, slots = static_cast<int64_t>(p.n_tppr) * plane;
     int64_t end = pos + 1;
     while (end < total && keys[end] == node) ++end;
-    float tot[8];                                             // Dm <= 256 columns: 8 per lane
-#pragma unroll
-    for (int c = 0; c < 8; ++c) tot[c] = 0.f;
+    const bool live = col < p.Dm;
+    float tot = 0.f;
     bool first = true;
     // sources of a node are in ascending source index, i.e. piece 0, 1, ..., n_tppr-1, src: walk the
-    // pieces in autograd's order and pick each piece's sources out of the run
+    // pieces in autograd's order; each piece is a contiguous part [a, b) of the run
+    int64_t b = end;
+    if (p.g_src) { while (b > pos && order[b - 1] >= slots) --b; }
+    const int64_t src_begin = b;                               // [src_begin, end) are src rows
     for (int pc = p.n_tppr - 1; pc >= -1; --pc) {
-        if (pc < 0 && !p.g_src) break;
-        const int64_t lo = pc >= 0 ? pc * plane : slots, hi = pc >= 0 ? lo + plane : slots + p.R;
-        float acc[8];
-#pragma unroll
-        for (int c = 0; c < 8; ++c) acc[c] = 0.f;
-        for (int64_t q = pos; q < end; ++q) {
-            const int64_t src = order[q];
-            if (src < lo || src >= hi) continue;
-            const float *g = pc >= 0 ? p.gX + static_cast<size_t>(src) * p.D : p.g_src + static_cast<size_t>(src - slots) * p.Dm;
-#pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const int col = lane + 32 * c;
-                if (col < p.Dm) acc[c] = __fadd_rn(acc[c], __ldg(g + col));
+        int64_t lo_q, hi_q;
+        if (pc < 0) {
+            if (!p.g_src) break;
+            lo_q = src_begin; hi_q = end;
+        } else {
+            hi_q = b;
+            const int64_t lo = pc * plane;
+            while (b > pos && order[b - 1] >= lo) --b;
+            lo_q = b;
+        }
+        float acc = 0.f;
+        if (live) {
+#pragma unroll 4
+            for (int64_t q = lo_q; q < hi_q; ++q) {
+                const int64_t src = order[q];
+                const float *g = pc >= 0 ? p.gX + static_cast<size_t>(src) * p.D : p.g_src + static_cast<size_t>(src - slots) * p.Dm;
+                acc = __fadd_rn(acc, __ldg(g + col));
             }
         }
-#pragma unroll
-        for (int c = 0; c < 8; ++c) tot[c] = first ? acc[c] : __fadd_rn(tot[c], acc[c]);
+        tot = first ? acc : __fadd_rn(tot, acc);
         first = false;
     }
-    float *dst = p.g_memory + static_cast<size_t>(node) * p.Dm;
-#pragma unroll
-    for (int c = 0; c < 8; ++c) {
-        const int col = lane + 32 * c;
-        if (col < p.Dm) dst[col] = tot[c];
-    }
+    if (live) p.g_memory[static_cast<size_t>(node) * p.Dm + col] = tot;
 }
 
 }  // namespace zebra

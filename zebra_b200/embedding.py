@@ -74,7 +74,7 @@ class FusedGather(torch.autograd.Function):
         gsrc = gsrc.contiguous() if gsrc is not None else None
         with torch.cuda.device(dev):
             st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
-            if REPRODUCIBLE_BACKWARD and Dm <= 256:
+            if REPRODUCIBLE_BACKWARD:
                 # sources sorted (stably) by destination node, summed in that order: run-to-run reproducible,
                 # like the reference's sort-based index_put backward
                 plane = rows * k
