@@ -63,7 +63,7 @@ def gather(R, k=20, n_tppr=2, Dm=100, De=172, Dt=100, N=10985, E=672448, flush=N
         torch.autograd.backward([X, srows], [gX, gS], retain_graph=True)
     ms = timed(bwd, flush=flush)
     bwd_bytes = slots * (4 * (Dm + De + Dt) // 1 * 0 + 4 * Dm * 2 + 8) + N * Dm * 4
-    print(f"gather_bwd{tag} (zero-fill of grad[N,Dm] + scatter-add) R={R}: {ms*1e3:.1f} us, alg {bwd_bytes/1e6:.1f} MB -> "
+    print(f"gather_bwd{tag} (default: stable sort of the destination ids + autograd-order sums) R={R}: {ms*1e3:.1f} us, alg {bwd_bytes/1e6:.1f} MB -> "
           f"{bwd_bytes/ms/1e6:.0f} GB/s", flush=True)
 
 
