@@ -270,6 +270,40 @@ int zebra_gather_bwd_sorted(int32_t n_tppr, int64_t rows, int32_t k, const float
                             void *stream);
 int zebra_gather_check(void *stream);
 
+/* ---- lazy memory update feeding the gather: replaces, in the train branch of
+ *      compute_embedding_tppr_ensemble (modules/embedding_module.py:227-230) and
+ *      SequenceMemoryUpdater.get_updated_memory (modules/memory_updater.py:61-90), the D2H of the
+ *      neighbour ids, the host-side unique + flag lookup, the clone of the whole [num_nodes, dim_mem]
+ *      memory and the [num_nodes, dim_mem] gradient of that clone ------------------------------------
+ *
+ * zebra_pending_select: the PENDING SET = distinct node ids of dev_topk's id planes whose dev_flags byte
+ * (Memory.nodes, modules/memory.py:22,27) is non-zero.  Outputs, all caller-owned device memory:
+ *   dev_bitmap      u32 [(num_nodes+31)/32]  bit v set iff v is pending (zeroed by the call)
+ *   dev_wordprefix  i32 [(num_nodes+31)/32]  number of pending nodes below word w's first bit
+ *   dev_ids         i64 [>= min(num_nodes, n_tppr*rows*k)]  the pending ids in ascending order — exactly
+ *                   the `unique_node_ids` of memory_updater.py:68-70, ready to index torch tensors with
+ *   dev_count       i32 [1]  how many
+ * The caller reads the count (4 bytes), runs the reference's own memory updater on those rows
+ * (GRUCell(messages[ids], memory[ids]) -> upd_rows [count, dim_mem]) and hands the result to
+ * zebra_gather_fwd_lazy, which is zebra_gather_fwd except that a pending node's row comes from
+ * dev_upd_rows (row = its rank in dev_ids) instead of dev_memory.  zebra_gather_bwd_lazy is
+ * zebra_gather_bwd_sorted except that it produces dev_gupd [count, dim_mem] (zero-filled by the caller),
+ * the gradient of upd_rows: bit-identical to what autograd hands the updater in the reference
+ * (grad of the clone, indexed by unique_node_ids), without materialising [num_nodes, dim_mem]. */
+int zebra_pending_select(const void *dev_topk, int32_t n_tppr, int64_t rows, int32_t k, const uint8_t *dev_flags,
+                         int64_t num_nodes, uint32_t *dev_bitmap, int32_t *dev_wordprefix, int64_t *dev_ids,
+                         int32_t *dev_count, void *stream);
+int zebra_gather_fwd_lazy(const void *dev_topk, int32_t n_tppr, int64_t rows, int32_t k, const float *dev_memory,
+                          int64_t num_nodes, int32_t dim_mem, const float *dev_edge_feat, int64_t n_edge_rows,
+                          int32_t dim_edge, const float *dev_time_w, const float *dev_time_b, int32_t dim_time,
+                          const int32_t *dev_src_nodes, float *dev_x, float *dev_wn, float *dev_src_rows,
+                          const float *dev_upd_rows, const uint32_t *dev_bitmap, const int32_t *dev_wordprefix,
+                          void *stream);
+int zebra_gather_bwd_lazy(int32_t n_tppr, int64_t rows, int32_t k, const float *dev_gx, const float *dev_wn,
+                          const float *dev_gsrc, const int32_t *dev_sorted_nodes, const int64_t *dev_order,
+                          const uint32_t *dev_bitmap, const int32_t *dev_wordprefix, float *dev_gupd,
+                          int64_t num_nodes, int32_t dim_mem, int32_t dim_total, void *stream);
+
 const char *zebra_last_error(void);
 const char *zebra_build_info(void);
 

@@ -32,7 +32,30 @@ struct GatherParams {
     float *wn;                 // [n_tppr, R, k]
     float *src_rows;           // [R, Dm] or nullptr
     int32_t *status;           // [0] set to 1 on an out-of-range id (row skipped)
+    // lazy memory update (all three NULL = plain gather): nodes of the pending set read their row from
+    // upd_rows [U, Dm] instead of memory (see PendingSet below)
+    const float *upd_rows;
+    const uint32_t *bitmap;
+    const int32_t *wordprefix;
 };
+
+// Pending set of the lazy memory update (modules/memory_updater.py:61-90): a bitmap over node ids plus,
+// per 32-bit word, the number of set bits before it.  Node v is in the set iff bit v is set, and its row
+// in the compacted (ascending) arrays is wordprefix[v >> 5] + popc(bits below v).
+__device__ __forceinline__ int pending_row(const uint32_t *bitmap, const int32_t *wordprefix, int node)
+{
+    const uint32_t w = __ldg(bitmap + (node >> 5)), bit = 1u << (node & 31);
+    return (w & bit) ? __ldg(wordprefix + (node >> 5)) + __popc(w & (bit - 1u)) : -1;
+}
+
+__device__ __forceinline__ const float *memory_row(const GatherParams &p, int node)
+{
+    if (p.bitmap) {
+        const int r = pending_row(p.bitmap, p.wordprefix, node);
+        if (r >= 0) return p.upd_rows + static_cast<size_t>(r) * p.Dm;
+    }
+    return p.memory + static_cast<size_t>(node) * p.Dm;
+}
 
 // Time encoding (model/time_encoding.py:23-28).  The reference runs torch.cos on the GPU, i.e. libdevice's
 // accurate cosf; calling the same routine makes this part of X bit-identical to the reference's (an fp64
@@ -72,7 +95,7 @@ gather_fwd_kernel(const GatherParams p)
         if (node < 0 || node >= p.num_nodes || eidx < 0 || eidx >= p.n_edge_rows) {
             if (lane == 0) atomicExch(p.status, 1);
         } else {
-            copy_row<VEC>(x, p.memory + static_cast<size_t>(node) * p.Dm, p.Dm, lane);
+            copy_row<VEC>(x, memory_row(p, node), p.Dm, lane);
             copy_row<VEC>(x + p.Dm, p.edge_feat + static_cast<size_t>(eidx) * p.De, p.De, lane);
             float *xt = x + p.Dm + p.De;
             if (VEC) {
@@ -102,7 +125,7 @@ gather_fwd_kernel(const GatherParams p)
         const int64_t r = warp - slots;
         const int node = p.src_nodes[r];
         if (node < 0 || node >= p.num_nodes) { if (lane == 0) atomicExch(p.status, 1); }
-        else copy_row<VEC>(p.src_rows + static_cast<size_t>(r) * p.Dm, p.memory + static_cast<size_t>(node) * p.Dm, p.Dm, lane);
+        else copy_row<VEC>(p.src_rows + static_cast<size_t>(r) * p.Dm, memory_row(p, node), p.Dm, lane);
     }
 }
 
@@ -117,6 +140,10 @@ struct GatherBwdParams {
     float *g_memory;           // [num_nodes, Dm], accumulated into
     int64_t num_nodes;
     int32_t Dm, D;
+    // lazy memory update (sorted backward only): g_memory is [U, Dm], one row per node of the pending set;
+    // gradients of nodes outside the set are not needed (memory itself takes no gradient) and are skipped
+    const uint32_t *bitmap;
+    const int32_t *wordprefix;
 };
 
 // Backward of the memory-row gathers (edge features and the time encoder are constants,
@@ -178,6 +205,11 @@ gather_bwd_sorted_kernel(const GatherBwdParams p, const int32_t *keys, const int
     const int node = keys[pos];
     if (pos > 0 && keys[pos - 1] == node) return;            // not the first source of its node
     if (node < 0 || node >= p.num_nodes) return;
+    int64_t out_row = node;
+    if (p.bitmap) {
+        out_row = pending_row(p.bitmap, p.wordprefix, node);
+        if (out_row < 0) return;
+    }
     const int64_t plane = p.R * p.k, slots = static_cast<int64_t>(p.n_tppr) * plane;
     int64_t end = pos + 1;
     while (end < total && keys[end] == node) ++end;
@@ -212,7 +244,68 @@ gather_bwd_sorted_kernel(const GatherBwdParams p, const int32_t *keys, const int
         tot = first ? acc : __fadd_rn(tot, acc);
         first = false;
     }
-    if (live) p.g_memory[static_cast<size_t>(node) * p.Dm + col] = tot;
+    if (live) p.g_memory[static_cast<size_t>(out_row) * p.Dm + col] = tot;
+}
+
+// ---- pending-set selection: np.unique(neighbour ids) restricted to the nodes with a stored message, on the device ----
+// Replaces, for the train branch of compute_embedding_tppr_ensemble (embedding_module.py:227-230), the D2H
+// of the id planes, numba_unique on the host and the flag lookup of get_updated_memory
+// (memory_updater.py:66-70).  Two launches: mark, then an ordered compaction by one block.
+__global__ void __launch_bounds__(256)
+pending_mark_kernel(const char *topk, int32_t n_tppr, int64_t plane, const uint8_t *flags, int64_t num_nodes,
+                    uint32_t *bitmap, int32_t *status)
+{
+    const int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (t >= n_tppr * plane) return;
+    const int64_t j = static_cast<uint32_t>(t) / static_cast<uint32_t>(plane), o = t - j * plane;
+    const int node = reinterpret_cast<const int32_t *>(topk + static_cast<size_t>(j) * plane * 16)[o];
+    if (node < 0 || node >= num_nodes) { atomicExch(status, 1); return; }
+    if (flags[node]) atomicOr(bitmap + (node >> 5), 1u << (node & 31));
+}
+
+// One block of 1024 threads; thread t owns the contiguous words [t*per, (t+1)*per).  Writes the per-word
+// prefix counts, the set's node ids in ascending order (what np.unique + np.where give) and the count.
+__global__ void __launch_bounds__(1024)
+pending_compact_kernel(const uint32_t *bitmap, int64_t n_words, int32_t *wordprefix, int64_t *ids, int32_t *count)
+{
+    __shared__ int32_t warp_sums[32];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int64_t per = (n_words + 1023) / 1024;
+    int64_t lo = static_cast<int64_t>(tid) * per, hi = lo + per;
+    if (lo > n_words) lo = n_words;
+    if (hi > n_words) hi = n_words;
+    int32_t s = 0;
+    for (int64_t w = lo; w < hi; ++w) s += __popc(bitmap[w]);
+    int32_t inc = s;                                            // inclusive scan inside the warp
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int32_t v = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += v;
+    }
+    if (lane == 31) warp_sums[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        const int32_t v = warp_sums[lane];
+        int32_t i2 = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int32_t u = __shfl_up_sync(0xffffffffu, i2, d);
+            if (lane >= d) i2 += u;
+        }
+        warp_sums[lane] = i2 - v;                               // exclusive over warps
+    }
+    __syncthreads();
+    int32_t base = warp_sums[wid] + inc - s;                    // set bits before this thread's words
+    if (tid == 1023) *count = base + s;
+    for (int64_t w = lo; w < hi; ++w) {
+        uint32_t bits = bitmap[w];
+        wordprefix[w] = base;
+        while (bits) {
+            const int b = __ffs(bits) - 1;
+            ids[base++] = w * 32 + b;
+            bits &= bits - 1u;
+        }
+    }
 }
 
 }  // namespace zebra

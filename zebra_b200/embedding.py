@@ -34,8 +34,22 @@ REPRODUCIBLE_BACKWARD = os.environ.get("ZEBRA_GATHER_BACKWARD", "sorted").lower(
 EXACT_WEIGHT_NORM = os.environ.get("ZEBRA_WEIGHT_NORM", "torch").lower() != "fused"
 
 
+# lazy memory update on the device (level 2): the pending set is selected by a kernel,
+# only its rows go through the memory updater, and the gather reads them in place of a cloned memory
+LAZY_MEMORY = os.environ.get("ZEBRA_LAZY_MEMORY", "0") == "1"
+
+
 def _p(t):
     return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _sorted_sources(topk, src_nodes, n_tppr, rows, k, with_src):
+    """Sources of the memory-row gathers (slots in buffer order, then the src rows) stably sorted by node."""
+    plane = rows * k
+    keys = [topk[j * plane * 16: j * plane * 16 + plane * 4].view(torch.int32) for j in range(n_tppr)]
+    if with_src:
+        keys.append(src_nodes.to(torch.int32))
+    return torch.sort(torch.cat(keys), stable=True)
 
 
 class FusedGather(torch.autograd.Function):
@@ -77,17 +91,87 @@ class FusedGather(torch.autograd.Function):
             if REPRODUCIBLE_BACKWARD:
                 # sources sorted (stably) by destination node, summed in that order: run-to-run reproducible,
                 # like the reference's sort-based index_put backward
-                plane = rows * k
-                keys = [topk[j * plane * 16: j * plane * 16 + plane * 4].view(torch.int32) for j in range(n_tppr)]
-                if gsrc is not None:
-                    keys.append(src_nodes.to(torch.int32))
-                skeys, order = torch.sort(torch.cat(keys), stable=True)
+                skeys, order = _sorted_sources(topk, src_nodes, n_tppr, rows, k, gsrc is not None)
                 check(lib().zebra_gather_bwd_sorted(n_tppr, rows, k, _p(gX), _p(wn), _p(gsrc), _p(skeys), _p(order), _p(gmem),
                                                     N, Dm, D, st))
             else:
                 check(lib().zebra_gather_bwd(_p(topk), n_tppr, rows, k, _p(gX), _p(wn), _p(gsrc),
                                              _p(src_nodes) if gsrc is not None else None, _p(gmem), N, Dm, D, st))
         return gmem, None, None, None, None, None, None, None, None
+
+
+class FusedGatherLazy(torch.autograd.Function):
+    """FusedGather over a lazily updated memory: rows of the pending set (bitmap / wordprefix from
+    zebra_pending_select) are read from `upd_rows` [U, Dm] — the memory updater's output for exactly those
+    nodes — every other row from `memory`.  Only `upd_rows` is differentiable; its gradient is the one
+    autograd hands the updater in the reference (memory_updater.py:83: the gradient of the cloned memory
+    at unique_node_ids), bit for bit, without a [num_nodes, Dm] tensor in either direction."""
+
+    @staticmethod
+    def forward(ctx, memory, upd_rows, bitmap, wordprefix, topk, src_nodes, edge_features, time_w, time_b, n_tppr, rows, k):
+        L = lib()
+        memory = memory.contiguous()
+        upd_rows = upd_rows.contiguous()
+        N, Dm = memory.shape
+        Ee, De = edge_features.shape
+        Dt = time_w.numel()
+        D = Dm + De + Dt
+        dev = memory.device
+        X = torch.empty((n_tppr, rows * k, D), dtype=torch.float32, device=dev)
+        wn = torch.empty((n_tppr, rows, k), dtype=torch.float32, device=dev)
+        src_rows = torch.empty((rows, Dm), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+            check(L.zebra_gather_fwd_lazy(_p(topk), n_tppr, rows, k, _p(memory), N, Dm, _p(edge_features), Ee, De,
+                                          _p(time_w), _p(time_b), Dt, _p(src_nodes), _p(X), _p(wn), _p(src_rows),
+                                          _p(upd_rows), _p(bitmap), _p(wordprefix), st))
+        ctx.save_for_backward(topk, src_nodes, wn, bitmap, wordprefix)
+        ctx.shape = (n_tppr, rows, k, N, Dm, D, upd_rows.shape[0])
+        ctx.mark_non_differentiable(wn)
+        return X, wn, src_rows
+
+    @staticmethod
+    def backward(ctx, gX, _gwn, gsrc):
+        topk, src_nodes, wn, bitmap, wordprefix = ctx.saved_tensors
+        n_tppr, rows, k, N, Dm, D, U = ctx.shape
+        dev = topk.device
+        gupd = torch.zeros((U, Dm), dtype=torch.float32, device=dev)
+        gX = gX.contiguous() if gX is not None else torch.zeros((n_tppr, rows * k, D), dtype=torch.float32, device=dev)
+        gsrc = gsrc.contiguous() if gsrc is not None else None
+        with torch.cuda.device(dev):
+            st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+            skeys, order = _sorted_sources(topk, src_nodes, n_tppr, rows, k, gsrc is not None)
+            check(lib().zebra_gather_bwd_lazy(n_tppr, rows, k, _p(gX), _p(wn), _p(gsrc), _p(skeys), _p(order), _p(bitmap),
+                                              _p(wordprefix), _p(gupd), N, Dm, D, st))
+        return None, gupd, None, None, None, None, None, None, None, None, None, None
+
+
+def pending_select(topk, n_tppr, rows, k, flags_dev, num_nodes):
+    """(ids int64[U] ascending, bitmap, wordprefix) of the pending set: the distinct neighbour ids of `topk`
+    whose byte in `flags_dev` (uint8[num_nodes], Memory.nodes) is set.  One 4-byte D2H for the count."""
+    dev = topk.device
+    n_words = (num_nodes + 31) // 32
+    bitmap = torch.empty(n_words, dtype=torch.int32, device=dev)
+    wordprefix = torch.empty(n_words, dtype=torch.int32, device=dev)
+    ids = torch.empty(max(1, min(num_nodes, n_tppr * rows * k)), dtype=torch.int64, device=dev)
+    count = torch.empty(1, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        check(lib().zebra_pending_select(_p(topk), n_tppr, rows, k, _p(flags_dev), num_nodes, _p(bitmap), _p(wordprefix),
+                                         _p(ids), _p(count), st))
+    return ids[:int(count.item())], bitmap, wordprefix
+
+
+def _flags_to_device(self, mem, dev):
+    """Memory.nodes (host numpy bool[num_nodes], modules/memory.py:22) through a pinned staging buffer."""
+    n = mem.nodes.shape[0]
+    pin = getattr(self, "_zebra_flags_pin", None)
+    if pin is None or pin.numel() != n:
+        pin = self._zebra_flags_pin = torch.empty(n, dtype=torch.uint8).pin_memory()
+        self._zebra_flags_dev = torch.empty(n, dtype=torch.uint8, device=dev)
+    pin.numpy()[:] = mem.nodes                  # the previous batch's copy has completed (count.item() synchronised)
+    self._zebra_flags_dev.copy_(pin, non_blocking=True)
+    return self._zebra_flags_dev
 
 
 def _query_raw(self, source_nodes, timestamps, edge_idxs):
@@ -116,8 +200,18 @@ def compute_embedding_tppr_ensemble(self, memory, source_nodes, timestamps, edge
     self.t_tppr += time.time() - t
     plane = R * k
 
-    if train:
-        # the lazy memory update (modules/memory_updater.py:61-90, out of scope) wants the distinct
+    lazy = None
+    if train and LAZY_MEMORY:
+        # level 2: pending set selected on the device; only its rows go through the reference's updater
+        # (memory_updater.py:83), nothing of size [num_nodes, Dm] is cloned or zero-filled
+        mem = memory
+        memory = mem.memory
+        idx, bitmap, wordprefix = pending_select(topk, n_tppr, R, k, _flags_to_device(self, mem, dev), memory.shape[0])
+        if idx.numel() > 0:
+            upd = memory_updater.memory_updater(mem.messages[idx], memory[idx])
+            lazy = (upd, bitmap, wordprefix)
+    elif train:
+        # the lazy memory update (modules/memory_updater.py:61-90) wants the distinct
         # neighbour ids on the host: one D2H of the id planes (n_tppr*R*k*4 bytes)
         ids = torch.stack([topk[j * plane * 16: j * plane * 16 + plane * 4].view(torch.int32) for j in range(n_tppr)])
         index = np.unique(ids.cpu().numpy())
@@ -130,7 +224,11 @@ def compute_embedding_tppr_ensemble(self, memory, source_nodes, timestamps, edge
     src_dev = torch.from_numpy(source_nodes).to(dev, non_blocking=True)
     tw = self.time_encoder.w.weight.detach().reshape(-1).contiguous()
     tb = self.time_encoder.w.bias.detach().contiguous()
-    X, wn, src_rows = FusedGather.apply(memory, topk, src_dev, self.edge_features, tw, tb, n_tppr, R, k)
+    if lazy is not None:
+        X, wn, src_rows = FusedGatherLazy.apply(memory, lazy[0], lazy[1], lazy[2], topk, src_dev, self.edge_features, tw, tb,
+                                                n_tppr, R, k)
+    else:
+        X, wn, src_rows = FusedGather.apply(memory, topk, src_dev, self.edge_features, tw, tb, n_tppr, R, k)
 
     embeddings = self.transform_source(src_rows)
     for j in range(n_tppr):
