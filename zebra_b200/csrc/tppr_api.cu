@@ -107,6 +107,8 @@ struct zebra_tppr {
     uint32_t shard_seq = 1;                    // handle-local tag sequence: identical on every rank
     int shard_max_blocks = 0;
     int32_t row_mode = 0;
+    char *plan_stage = nullptr;                // pinned staging of sharded plans, kept across plans
+    size_t plan_stage_cap = 0;
 };
 
 // A span prepared once and kept resident in HBM (edge records + dependency thresholds).
@@ -235,16 +237,48 @@ int fill_soa(zebra_tppr *h, char *host, size_t cap, const NodeT *src, const Node
     return 0;
 }
 
-// Node-sharded variant of fill_soa: a rank only ever reads and writes the records of the nodes it
-// owns, so only edges it takes part in get a staging record, and dependencies are tracked for owned
-// endpoints only (scratch indexed by local row: 1/world of the nodes, cache resident).  A non-owned
-// endpoint arrives through the mailbox, tagged with the edge itself: no prev, no reader threshold.
-// Also builds the rank's work list and, per batch, the list position of its first edge.
-int fill_soa_sharded(zebra_tppr *h, char *host, size_t cap, const int32_t *src, const int32_t *dst, const int32_t *neg,
-                     const double *ts, const int64_t *eidx, int64_t m, int64_t batch_size, std::vector<int32_t> &list,
-                     std::vector<int64_t> &batch_ofs)
+// Node-sharded variant of fill_soa, in two passes.  A rank only ever reads and writes the records of
+// the nodes it owns, so only the edges it takes part in (it owns src, dst or a distinct negative) get
+// a staging record, and the records are COMPACT: indexed by position in the rank's work list, not by
+// span index (1/3 of the span at world = 8: a third of the host writes, page faults and H2D bytes).
+//
+// Pass A builds the work list (span indices, ascending) and, per batch, the list position of its
+// first edge; it validates every id before any scratch is touched.
+int shard_work_list(zebra_tppr *h, const int32_t *src, const int32_t *dst, const int32_t *neg, const int64_t *eidx, int64_t m,
+                    int64_t batch_size, std::vector<int32_t> &list, std::vector<int64_t> &batch_ofs)
 {
     const int64_t N = h->num_nodes;
+    const int32_t pm = h->world - 1, me = h->rank;
+    const int64_t n_batches = (m + batch_size - 1) / batch_size;
+    batch_ofs.assign(static_cast<size_t>(n_batches) + 1, 0);
+    list.clear();
+    list.reserve(static_cast<size_t>(m / h->world) * 3 + 16);
+    int64_t next_batch_at = 0, bi = 0;
+    for (int64_t i = 0; i < m; ++i) {
+        if (i == next_batch_at) { batch_ofs[static_cast<size_t>(bi++)] = static_cast<int64_t>(list.size()); next_batch_at += batch_size; }
+        const int64_t a = src[i], b = dst[i], g = neg ? static_cast<int64_t>(neg[i]) : a;
+        if (a < 0 || a >= N || b < 0 || b >= N || g < 0 || g >= N)
+            return fail("node id out of range at edge %lld (num_nodes=%lld)", (long long)i, (long long)N);
+        if (!((a & pm) == me || (b & pm) == me || (neg && g != a && g != b && (g & pm) == me))) continue;
+        const int64_t e = eidx[i];
+        if (e < 0 || e > 0x7fffffffLL) return fail("edge id %lld does not fit int32", (long long)e);
+        list.push_back(static_cast<int32_t>(i));
+    }
+    batch_ofs[static_cast<size_t>(n_batches)] = static_cast<int64_t>(list.size());
+    return 0;
+}
+
+// Pass B fills the compact staging image (arrays of `cap` >= list.size() entries, entry q describes
+// edge list[q]) and derives the dependencies of OWNED endpoints (scratch indexed by local row: 1/world
+// of the nodes, cache resident).  A non-owned endpoint arrives through the mailbox, tagged with the
+// edge itself: no prev, no reader threshold.  prev_x are SPAN indices (the kernel turns them into
+// tags); reader chains and the "both endpoints here" bookkeeping use list positions.
+// kFlagDstFirst (only meaningful when both endpoints are owned): set iff dst is rewritten strictly
+// before src.  NodeDep::pad remembers, per node, the latest such edge still waiting for that answer;
+// the first later write of either endpoint settles it (a single edge rewriting both: no preference).
+void fill_soa_sharded(zebra_tppr *h, char *host, size_t cap, const int32_t *src, const int32_t *dst, const int32_t *neg,
+                      const double *ts, const int64_t *eidx, const std::vector<int32_t> &list)
+{
     const int32_t pm = h->world - 1, me = h->rank, lg = h->world_log2;
     int32_t *o_src = reinterpret_cast<int32_t *>(host);
     int32_t *o_dst = o_src + cap, *o_neg = o_dst + cap, *o_e = o_neg + cap;
@@ -252,72 +286,59 @@ int fill_soa_sharded(zebra_tppr *h, char *host, size_t cap, const int32_t *src, 
     uint32_t *r_s = reinterpret_cast<uint32_t *>(p_n + cap), *r_d = r_s + cap, *flg = r_d + cap;
     double *o_ts = reinterpret_cast<double *>(flg + cap);
     NodeDep *dep = h->dep.data();                                     // sized num_nodes >= local rows
-    const int64_t n_batches = (m + batch_size - 1) / batch_size;
-    batch_ofs.assign(static_cast<size_t>(n_batches) + 1, 0);
-    list.clear();
-    list.reserve(static_cast<size_t>(m / h->world) * 3 + 16);
-    // rnext is indexed by list position here (readers are list members)
-    std::vector<int32_t> &rnext_v = h->rnext;
-    for (int64_t i = 0; i < m; ++i) {
-        if (i % batch_size == 0) batch_ofs[static_cast<size_t>(i / batch_size)] = static_cast<int64_t>(list.size());
-        const int64_t a64 = src[i], b64 = dst[i], g64 = neg ? static_cast<int64_t>(neg[i]) : a64;
-        if (a64 < 0 || a64 >= N || b64 < 0 || b64 >= N || g64 < 0 || g64 >= N)
-            return fail("node id out of range at edge %lld (num_nodes=%lld)", (long long)i, (long long)N);
-        const int32_t a = static_cast<int32_t>(a64), b = static_cast<int32_t>(b64), g = static_cast<int32_t>(g64);
-        const bool oa = (a & pm) == me, ob = (b & pm) == me;
+    const size_t L = list.size();
+    if (h->rnext.size() < L) h->rnext.resize(L);
+    int32_t *rnext = h->rnext.data();
+    auto settle = [&](uint32_t qe, int32_t x) {                       // node x of edge qe is the first to be rewritten
+        const int32_t s = o_src[qe], d = o_dst[qe];
+        if (x == d) flg[qe] |= zebra::kFlagDstFirst;
+        NodeDep &other = dep[(x == d ? s : d) >> lg];
+        if (other.pad == qe + 1) other.pad = 0;
+        dep[x >> lg].pad = 0;
+    };
+    auto overwrite = [&](NodeDep &n, int32_t i, int32_t &prev, uint32_t &rthr) {
+        prev = n.lastw; rthr = n.rcount;
+        if (n.rcount) {                                               // its pending negative reads must signal
+            for (int32_t r = n.rhead; r >= 0; r = rnext[r]) flg[r] |= zebra::kFlagSignal;
+            n.rhead = -1; n.rcount = 0;
+        }
+        n.lastw = i;
+    };
+    constexpr size_t kAhead = 12;                                     // the scratch look-ups are cache misses: fetch ahead
+    for (size_t q = 0; q < L; ++q) {
+        if (q + kAhead < L) {
+            const int32_t i2 = list[q + kAhead];
+            const int32_t a2 = src[i2], b2 = dst[i2];
+            if ((a2 & pm) == me) __builtin_prefetch(dep + (a2 >> lg), 1);
+            if ((b2 & pm) == me) __builtin_prefetch(dep + (b2 >> lg), 1);
+            if (neg && (neg[i2] & pm) == me) __builtin_prefetch(dep + (neg[i2] >> lg), 1);
+        }
+        const int32_t i = list[q];
+        const int32_t a = src[i], b = dst[i], g = neg ? neg[i] : a;
+        const bool oa = (a & pm) == me, wb = b != a && (b & pm) == me;
         const bool og = neg && g != a && g != b && (g & pm) == me;
-        if (!(oa || ob || og)) continue;
-        const int64_t e = eidx[i];
-        if (e < 0 || e > 0x7fffffffLL) return fail("edge id %lld does not fit int32", (long long)e);
-        const int32_t li = static_cast<int32_t>(list.size());
-        list.push_back(static_cast<int32_t>(i));
-        if (rnext_v.size() <= static_cast<size_t>(li)) rnext_v.resize(static_cast<size_t>(li) * 2 + 1024);
-        int32_t *rnext = rnext_v.data();
-        o_src[i] = a; o_dst[i] = b; o_neg[i] = g; o_e[i] = static_cast<int32_t>(e); o_ts[i] = ts[i];
-        flg[i] = 0; p_s[i] = -1; p_d[i] = -1; p_n[i] = -1; r_s[i] = 0; r_d[i] = 0;
+        o_src[q] = a; o_dst[q] = b; o_neg[q] = g; o_e[q] = static_cast<int32_t>(eidx[i]); o_ts[q] = ts[i];
+        flg[q] = 0; p_s[q] = -1; p_d[q] = -1; p_n[q] = -1; r_s[q] = 0; r_d[q] = 0;
         if (og) {
-            const int32_t gl = g >> lg;
-            p_n[i] = dep[gl].lastw;
-            rnext[li] = dep[gl].rhead; dep[gl].rhead = li; dep[gl].rcount++;
+            NodeDep &n = dep[g >> lg];
+            p_n[q] = n.lastw;
+            rnext[q] = n.rhead; n.rhead = static_cast<int32_t>(q); n.rcount++;
         }
-        if (oa) {
-            const int32_t al = a >> lg;
-            p_s[i] = dep[al].lastw; r_s[i] = dep[al].rcount;
-            if (dep[al].rcount) {
-                for (int32_t r = dep[al].rhead; r >= 0; r = rnext[r]) flg[list[static_cast<size_t>(r)]] |= zebra::kFlagSignal;
-                dep[al].rhead = -1; dep[al].rcount = 0;
-            }
-            dep[al].lastw = static_cast<int32_t>(i);
+        NodeDep *da = oa ? dep + (a >> lg) : nullptr, *db = wb ? dep + (b >> lg) : nullptr;
+        const uint32_t qa = da ? da->pad : 0u, qb = db ? db->pad : 0u;
+        if (qa && qa == qb) {
+            da->pad = 0; db->pad = 0;
+        } else {
+            if (qa) settle(qa - 1, a);
+            if (qb) settle(qb - 1, b);
         }
-        if (ob && b != a) {
-            const int32_t bl = b >> lg;
-            p_d[i] = dep[bl].lastw; r_d[i] = dep[bl].rcount;
-            if (dep[bl].rcount) {
-                for (int32_t r = dep[bl].rhead; r >= 0; r = rnext[r]) flg[list[static_cast<size_t>(r)]] |= zebra::kFlagSignal;
-                dep[bl].rhead = -1; dep[bl].rcount = 0;
-            }
-            dep[bl].lastw = static_cast<int32_t>(i);
-        }
+        if (oa) overwrite(*da, i, p_s[q], r_s[q]);
+        if (wb) overwrite(*db, i, p_d[q], r_d[q]);
+        if (oa && wb) { da->pad = static_cast<uint32_t>(q) + 1; db->pad = static_cast<uint32_t>(q) + 1; }
     }
-    batch_ofs[static_cast<size_t>(n_batches)] = static_cast<int64_t>(list.size());
-    // backward: which owned endpoint is written again first (only matters when both are owned)
-    for (int32_t i : list) {
-        if ((o_src[i] & pm) == me) dep[o_src[i] >> lg].lastw = INT_MAX;
-        if ((o_dst[i] & pm) == me) dep[o_dst[i] >> lg].lastw = INT_MAX;
-    }
-    for (size_t q = list.size(); q-- > 0;) {
-        const int32_t i = list[q], a = o_src[i], b = o_dst[i];
-        const bool oa = (a & pm) == me, ob = (b & pm) == me;
-        if (oa && ob && a != b && dep[b >> lg].lastw < dep[a >> lg].lastw) flg[i] |= zebra::kFlagDstFirst;
-        if (oa) dep[a >> lg].lastw = i;
-        if (ob) dep[b >> lg].lastw = i;
-    }
-    for (int32_t i : list) {
-        if ((o_src[i] & pm) == me) dep[o_src[i] >> lg].lastw = -1;
-        if ((o_dst[i] & pm) == me) dep[o_dst[i] >> lg].lastw = -1;
-        if ((o_neg[i] & pm) == me) { dep[o_neg[i] >> lg].rhead = -1; dep[o_neg[i] >> lg].rcount = 0; }
-    }
-    return 0;
+    // the scratch goes back to "no writer, no reader": the local rows are few enough to refill wholesale
+    const size_t local_rows = static_cast<size_t>((h->num_nodes - 1) >> lg) + 1;
+    std::fill(dep, dep + local_rows, NodeDep{-1, -1, 0u, 0u});
 }
 
 struct BatchOut {
@@ -586,6 +607,7 @@ int zebra_tppr_destroy(zebra_tppr_t *h)
     if (h->prof) cudaFree(h->prof);
     if (h->out_dev) cudaFree(h->out_dev);
     if (h->out_pinned) cudaFreeHost(h->out_pinned);
+    if (h->plan_stage) cudaFreeHost(h->plan_stage);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     delete h;
@@ -731,23 +753,39 @@ int zebra_tppr_plan_create(zebra_tppr_t *h, const int32_t *host_src, const int32
     pl->n_batches = (n + batch_size - 1) / batch_size;
     pl->cap = (static_cast<size_t>(n) + 7) & ~static_cast<size_t>(7);
     if (n >= 0x70000000LL || batch_size >= 0x70000000LL) { delete pl; return fail("plan too long"); }
-    // staging image of the span (uninitialised: a sharded rank fills only the records it takes part in)
-    std::unique_ptr<char[]> host(new char[pl->cap * kEdgeBytes]);
     std::vector<int32_t> list;
-    const int rc = h->world > 1
-        ? fill_soa_sharded(h, host.get(), pl->cap, host_src, host_dst, rows_per_edge == 3 ? host_neg : nullptr, host_ts, host_eidx,
-                           n, batch_size, list, pl->batch_ofs)
-        : fill_soa<int32_t>(h, host.get(), pl->cap, host_src, host_dst, rows_per_edge == 3 ? host_neg : nullptr, host_ts,
-                            host_eidx, n);
-    if (rc) {
-        delete pl;
-        return 1;
-    }
-    cudaError_t e = cudaMalloc(&pl->dev, pl->cap * kEdgeBytes);
-    if (e == cudaSuccess) e = cudaMemcpy(pl->dev, host.get(), pl->cap * kEdgeBytes, cudaMemcpyHostToDevice);
-    if (e == cudaSuccess && h->world > 1) {
-        e = cudaMalloc(&pl->dev_list, std::max<size_t>(list.size(), 1) * sizeof(int32_t));
+    cudaError_t e = cudaSuccess;
+    if (h->world > 1) {
+        // compact records, one per edge of this rank's work list, staged in a pinned buffer the handle keeps
+        if (shard_work_list(h, host_src, host_dst, rows_per_edge == 3 ? host_neg : nullptr, host_eidx, n, batch_size, list,
+                            pl->batch_ofs)) {
+            delete pl;
+            return 1;
+        }
+        pl->cap = (list.size() + 8) & ~static_cast<size_t>(7);
+        const size_t bytes = pl->cap * kEdgeBytes;
+        if (h->plan_stage_cap < bytes) {
+            if (h->plan_stage) cudaFreeHost(h->plan_stage);
+            h->plan_stage = nullptr; h->plan_stage_cap = 0;
+            e = cudaMallocHost(&h->plan_stage, bytes + bytes / 8);
+            if (e != cudaSuccess) { delete pl; return fail("pinned staging of %zu bytes: %s", bytes, cudaGetErrorString(e)); }
+            h->plan_stage_cap = bytes + bytes / 8;
+        }
+        fill_soa_sharded(h, h->plan_stage, pl->cap, host_src, host_dst, rows_per_edge == 3 ? host_neg : nullptr, host_ts, host_eidx, list);
+        e = cudaMalloc(&pl->dev, bytes);
+        if (e == cudaSuccess) e = cudaMemcpy(pl->dev, h->plan_stage, bytes, cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = cudaMalloc(&pl->dev_list, std::max<size_t>(list.size(), 1) * sizeof(int32_t));
         if (e == cudaSuccess) e = cudaMemcpy(pl->dev_list, list.data(), list.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
+    } else {
+        // staging image of the span
+        std::unique_ptr<char[]> host(new char[pl->cap * kEdgeBytes]);
+        if (fill_soa<int32_t>(h, host.get(), pl->cap, host_src, host_dst, rows_per_edge == 3 ? host_neg : nullptr, host_ts,
+                              host_eidx, n)) {
+            delete pl;
+            return 1;
+        }
+        e = cudaMalloc(&pl->dev, pl->cap * kEdgeBytes);
+        if (e == cudaSuccess) e = cudaMemcpy(pl->dev, host.get(), pl->cap * kEdgeBytes, cudaMemcpyHostToDevice);
     }
     if (e != cudaSuccess) {
         if (pl->dev) cudaFree(pl->dev);
@@ -807,12 +845,14 @@ int zebra_tppr_plan_run(zebra_tppr_t *h, zebra_plan_t *pl, int64_t first_batch, 
         const int64_t be = std::min(last, b + batches_per_launch);
         const int64_t lo = b * pl->batch_size, hi = std::min(pl->n, be * pl->batch_size);
         const int32_t *list = nullptr;
-        int64_t n_list = 0;
+        int64_t n_list = 0, rec0 = lo;                 // rec0: first staging record of the launch
         if (h->world > 1) {
-            list = pl->dev_list + pl->batch_ofs[static_cast<size_t>(b)];
-            n_list = pl->batch_ofs[static_cast<size_t>(be)] - pl->batch_ofs[static_cast<size_t>(b)];
+            // sharded plans hold compact records: entry q of the work list describes edge list[q]
+            rec0 = pl->batch_ofs[static_cast<size_t>(b)];
+            list = pl->dev_list + rec0;
+            n_list = pl->batch_ofs[static_cast<size_t>(be)] - rec0;
         }
-        if (launch_kernel(h, pl->dev, pl->cap, lo, hi - lo, pl->n, lo, pl->rows_per_edge, (1 << h->n_tppr) - 1,
+        if (launch_kernel(h, pl->dev, pl->cap, rec0, hi - lo, pl->n, lo, pl->rows_per_edge, (1 << h->n_tppr) - 1,
                           static_cast<char *>(dev_out), bo, pl->seq0, lo, st, list, n_list)) {
             h->plan_active = nullptr;          // a failed launch abandons the run
             return 1;

@@ -15,7 +15,8 @@
 // is ever pulled over NVLink, and no version can be overwritten under a remote reader.
 //
 // Work list.  The host gives every rank the (sorted) list of edges it takes part in — it owns src,
-// dst or a distinct negative — and the tickets run over that list only.
+// dst or a distinct negative — and the tickets run over that list only.  The staging records are
+// compact as well: entry q of the arrays (src, dst, ..., ts) describes edge list[q].
 //
 // Mailboxes are indexed by launch-local item and double-buffered by launch parity: a rank can run
 // at most one launch ahead of a peer that still has to read a slot (a rank finishing launch n needs
@@ -74,26 +75,27 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
         const int64_t li = tk / static_cast<uint32_t>(p.n_tppr);    // 32-bit division: items < 2^32
         const int j = tk - li * p.n_tppr;
         if (!((p.inst_mask >> j) & 1)) continue;
+        // the staging records of a sharded plan are compact: entry li describes edge list[li]
         const int64_t i = static_cast<int64_t>(p.list[li]) - p.i_offset;     // launch-local edge index
-        const int sN = p.src[i], dN = p.dst[i];
+        const int sN = p.src[li], dN = p.dst[li];
         const bool has_neg = p.rows_per_edge == 3;
-        const int gN = has_neg ? p.neg[i] : sN;
+        const int gN = has_neg ? p.neg[li] : sN;
         const bool loop = sN == dN;
         const bool neg_own = has_neg && gN != sN && gN != dN;
         const bool oS = (sN & pmask) == me, oD = loop ? oS : (dN & pmask) == me;
         const bool oG = neg_own && (gN & pmask) == me;
         if (!(oS || oD || oG)) continue;          // nothing of this edge lives here
-        const uint32_t flags = p.flags[i];
+        const uint32_t flags = p.flags[li];
         int32_t *rcnt = p.rcnt[j];
-        const int32_t pS = p.prev_s[i], pD = loop ? -1 : p.prev_d[i], pG = neg_own ? p.prev_n[i] : -1;
+        const int32_t pS = p.prev_s[li], pD = loop ? -1 : p.prev_d[li], pG = neg_own ? p.prev_n[li] : -1;
         char *table = p.tables[j];
         char *recS = table + static_cast<size_t>(sN >> lg) * p.stride;
         char *recD = table + static_cast<size_t>(dN >> lg) * p.stride;
         const char *recG = table + static_cast<size_t>(gN >> lg) * p.stride;
         const uint32_t my_tag = tag_base + static_cast<uint32_t>(i);
-        const double t = p.ts[i];
-        const int e = p.eidx[i];
-        const uint32_t rwS = p.rthr_s[i], rwD = loop ? 0u : p.rthr_d[i];
+        const double t = p.ts[li];
+        const int e = p.eidx[li];
+        const uint32_t rwS = p.rthr_s[li], rwD = loop ? 0u : p.rthr_d[li];
 
         const bool needSD = oS || oD;
         const bool cross = needSD && !(oS && oD);              // the other endpoint lives on another rank
