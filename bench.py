@@ -243,6 +243,9 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
         launches = f.counters()["launches"] - l0
         res = {"E": E, "N": N, "ms": ms, "launches": launches, "n_launch": n_win, "n_batches": plan.n_batches,
                "record_bytes": f._record_bytes}
+        pb = torch.tensor([float(plan.device_bytes)], dtype=torch.float64, device=dev)
+        dist.all_reduce(pb)                       # H2D of a plan, summed over the ranks
+        res["plan_bytes"] = int(pb[0])
         if e2e:
             # end to end: host arrays in (dependency pass + H2D of the replicated span on every rank), the
             # complete rows of every batch back in pinned host memory on EVERY rank.  Per window: kernel,
@@ -335,8 +338,8 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
                          f"outputs exceed the 126 MB L2 (inputs larger than L2)",
                    "tie_path_prunes_last_step_rank0": weak["tie_prunes"]},
         "e2e": {"value": E * args.steps / weak["e2e_s"], "unit": UNIT,
-                "h2d_bytes_per_step": world * ((E + 7) // 8 * 8) * 48, "d2h_bytes_per_step": len(ALPHAS) * 16 * 3 * E * K,
-                "step": f"per rank: plan built from host arrays (ownership-aware dependency pass + H2D of the replicated span), sharded "
+                "h2d_bytes_per_step": weak["plan_bytes"], "d2h_bytes_per_step": len(ALPHAS) * 16 * 3 * E * K,
+                "step": f"per rank: plan built from host arrays (ownership-aware dependency pass + H2D of the records of the edges the rank takes part in), sharded "
                         f"run in windows of {window} batches, a one-element all-reduce per window as cross-rank completion, rank r copies "
                         f"the rows of its batches (b % {world} == r) to pinned host memory (every batch read back once)"},
         "gpu_launches": weak["launches"] * world,

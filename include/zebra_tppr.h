@@ -112,6 +112,9 @@ int zebra_tppr_plan_create(zebra_tppr_t *h, const int32_t *host_src, const int32
                            int64_t n, int32_t rows_per_edge, int64_t batch_size, zebra_plan_t **out);
 int zebra_tppr_plan_destroy(zebra_plan_t *plan);
 int64_t zebra_tppr_plan_batches(const zebra_plan_t *plan);
+/* Bytes the plan uploaded and keeps in HBM: 48 per staged edge record (on a node-sharded handle only
+ * the edges this rank takes part in are staged, plus 4 per entry of its work list). */
+size_t zebra_tppr_plan_bytes(const zebra_plan_t *plan);
 int zebra_tppr_plan_run(zebra_tppr_t *h, zebra_plan_t *plan, int64_t first_batch, int64_t n_batches,
                         int64_t batches_per_launch, void *dev_out, int64_t out_slots, void *stream);
 

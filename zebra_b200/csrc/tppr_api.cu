@@ -809,6 +809,12 @@ int zebra_tppr_plan_destroy(zebra_plan_t *pl)
 
 int64_t zebra_tppr_plan_batches(const zebra_plan_t *pl) { return pl ? pl->n_batches : 0; }
 
+size_t zebra_tppr_plan_bytes(const zebra_plan_t *pl)
+{
+    if (!pl) return 0;
+    return pl->cap * kEdgeBytes + (pl->dev_list ? static_cast<size_t>(pl->batch_ofs.back()) * sizeof(int32_t) : 0);
+}
+
 int zebra_tppr_plan_run(zebra_tppr_t *h, zebra_plan_t *pl, int64_t first_batch, int64_t n_batches,
                         int64_t batches_per_launch, void *dev_out, int64_t out_slots, void *stream)
 {

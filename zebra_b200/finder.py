@@ -298,6 +298,7 @@ class StreamPlan:
                                                    self.rows_per_edge, self.batch_size, C.byref(h)))
         self._p = h
         self.n_batches = int(finder._L.zebra_tppr_plan_batches(h))
+        self.device_bytes = int(finder._L.zebra_tppr_plan_bytes(h))        # what the plan uploaded (H2D) and keeps in HBM
         self.slot_bytes = int(finder._L.zebra_tppr_out_bytes(finder._h, self.batch_size, self.rows_per_edge))
 
     def alloc_out(self, out_slots):
