@@ -307,6 +307,16 @@ int zebra_gather_bwd_lazy(int32_t n_tppr, int64_t rows, int32_t k, const float *
                           const uint32_t *dev_bitmap, const int32_t *dev_wordprefix, float *dev_gupd,
                           int64_t num_nodes, int32_t dim_mem, int32_t dim_total, void *stream);
 
+/* Test hook, host only (no CUDA call, works without a GPU): the staging records zebra_tppr_plan_create
+ * would upload for this span on rank `rank` of `world` (world = 1: the single-GPU pass).  out_fields is
+ * int32 [10][count]: src, dst, neg, eidx, prev_s, prev_d, prev_n, rthr_s, rthr_d, flags (bit 0: this
+ * edge's negative read must signal, bit 1: update dst first); out_ts f64 [count]; out_list int32 [count]
+ * span index of every record; out_batch_ofs int64 [n_batches+1]; all sized for count = n by the caller. */
+int zebra_debug_host_pass(int64_t num_nodes, int32_t world, int32_t rank, const int32_t *host_src,
+                          const int32_t *host_dst, const int32_t *host_neg, const double *host_ts,
+                          const int64_t *host_eidx, int64_t n, int64_t batch_size, int32_t *out_fields,
+                          double *out_ts, int32_t *out_list, int64_t *out_batch_ofs, int64_t *out_count);
+
 const char *zebra_last_error(void);
 const char *zebra_build_info(void);
 

@@ -809,6 +809,53 @@ int zebra_tppr_plan_destroy(zebra_plan_t *pl)
 
 int64_t zebra_tppr_plan_batches(const zebra_plan_t *pl) { return pl ? pl->n_batches : 0; }
 
+// Test hook (host only, no CUDA call): the staging records a plan would upload for this span.
+int zebra_debug_host_pass(int64_t num_nodes, int32_t world, int32_t rank, const int32_t *host_src, const int32_t *host_dst,
+                          const int32_t *host_neg, const double *host_ts, const int64_t *host_eidx, int64_t n,
+                          int64_t batch_size, int32_t *out_fields, double *out_ts, int32_t *out_list, int64_t *out_batch_ofs,
+                          int64_t *out_count)
+{
+    if (num_nodes <= 0 || n <= 0 || batch_size <= 0 || world < 1 || (world & (world - 1)) || world > zebra::kMaxRanks ||
+        rank < 0 || rank >= world)
+        return fail("bad host-pass geometry");
+    if (!host_src || !host_dst || !host_ts || !host_eidx || !out_fields || !out_ts || !out_list || !out_batch_ofs || !out_count)
+        return fail("null argument");
+    zebra_tppr h;
+    h.num_nodes = num_nodes; h.world = world; h.rank = rank;
+    while ((1 << h.world_log2) < world) ++h.world_log2;
+    h.dep.assign(static_cast<size_t>(num_nodes), NodeDep{-1, -1, 0u, 0u});
+    std::vector<int32_t> list;
+    std::vector<int64_t> ofs;
+    size_t cap = 0, count = 0;
+    std::unique_ptr<char[]> img;
+    if (world > 1) {
+        if (shard_work_list(&h, host_src, host_dst, host_neg, host_eidx, n, batch_size, list, ofs)) return 1;
+        count = list.size();
+        cap = (count + 8) & ~static_cast<size_t>(7);
+        img.reset(new char[cap * kEdgeBytes]);
+        fill_soa_sharded(&h, img.get(), cap, host_src, host_dst, host_neg, host_ts, host_eidx, list);
+    } else {
+        count = static_cast<size_t>(n);
+        cap = (count + 7) & ~static_cast<size_t>(7);
+        img.reset(new char[cap * kEdgeBytes]);
+        if (fill_soa<int32_t>(&h, img.get(), cap, host_src, host_dst, host_neg, host_ts, host_eidx, n)) return 1;
+        list.resize(count);
+        for (size_t q = 0; q < count; ++q) list[q] = static_cast<int32_t>(q);
+        const int64_t nb = (n + batch_size - 1) / batch_size;
+        ofs.resize(static_cast<size_t>(nb) + 1);
+        for (int64_t b = 0; b <= nb; ++b) ofs[static_cast<size_t>(b)] = std::min(n, b * batch_size);
+    }
+    for (const NodeDep &d : h.dep)
+        if (d.lastw != -1 || d.rhead != -1 || d.rcount != 0 || d.pad != 0) return fail("host pass left its scratch dirty");
+    const int32_t *f = reinterpret_cast<const int32_t *>(img.get());
+    for (int a = 0; a < 10; ++a) memcpy(out_fields + static_cast<size_t>(a) * count, f + static_cast<size_t>(a) * cap, count * sizeof(int32_t));
+    memcpy(out_ts, f + 10 * cap, count * sizeof(double));
+    memcpy(out_list, list.data(), count * sizeof(int32_t));
+    memcpy(out_batch_ofs, ofs.data(), ofs.size() * sizeof(int64_t));
+    *out_count = static_cast<int64_t>(count);
+    return 0;
+}
+
 size_t zebra_tppr_plan_bytes(const zebra_plan_t *pl)
 {
     if (!pl) return 0;
