@@ -247,22 +247,54 @@ int fill_soa(zebra_tppr *h, char *host, size_t cap, const NodeT *src, const Node
 int shard_work_list(zebra_tppr *h, const int32_t *src, const int32_t *dst, const int32_t *neg, const int64_t *eidx, int64_t m,
                     int64_t batch_size, std::vector<int32_t> &list, std::vector<int64_t> &batch_ofs)
 {
-    const int64_t N = h->num_nodes;
+    const uint32_t N = static_cast<uint32_t>(std::min<int64_t>(h->num_nodes, 0x7fffffffLL));
     const int32_t pm = h->world - 1, me = h->rank;
-    const int64_t n_batches = (m + batch_size - 1) / batch_size;
-    batch_ofs.assign(static_cast<size_t>(n_batches) + 1, 0);
     list.clear();
     list.reserve(static_cast<size_t>(m / h->world) * 3 + 16);
-    int64_t next_batch_at = 0, bi = 0;
-    for (int64_t i = 0; i < m; ++i) {
-        if (i == next_batch_at) { batch_ofs[static_cast<size_t>(bi++)] = static_cast<int64_t>(list.size()); next_batch_at += batch_size; }
-        const int64_t a = src[i], b = dst[i], g = neg ? static_cast<int64_t>(neg[i]) : a;
-        if (a < 0 || a >= N || b < 0 || b >= N || g < 0 || g >= N)
-            return fail("node id out of range at edge %lld (num_nodes=%lld)", (long long)i, (long long)N);
-        if (!((a & pm) == me || (b & pm) == me || (neg && g != a && g != b && (g & pm) == me))) continue;
-        const int64_t e = eidx[i];
-        if (e < 0 || e > 0x7fffffffLL) return fail("edge id %lld does not fit int32", (long long)e);
-        list.push_back(static_cast<int32_t>(i));
+    // chunks of 1024 edges, no data-dependent branch inside: ownership is a coin flip per edge
+    constexpr int64_t kChunk = 1024;
+    int32_t tmp[kChunk];
+    for (int64_t lo = 0; lo < m; lo += kChunk) {
+        const int64_t hi = std::min(m, lo + kChunk);
+        uint32_t bad = 0;
+        int cnt = 0;
+        if (neg) {
+            for (int64_t i = lo; i < hi; ++i) {
+                const int32_t a = src[i], b = dst[i], g = neg[i];
+                bad |= (static_cast<uint32_t>(a) >= N) | (static_cast<uint32_t>(b) >= N) | (static_cast<uint32_t>(g) >= N);
+                const int own = ((a & pm) == me) | ((b & pm) == me) | ((g != a) & (g != b) & ((g & pm) == me));
+                tmp[cnt] = static_cast<int32_t>(i);
+                cnt += own;
+            }
+        } else {
+            for (int64_t i = lo; i < hi; ++i) {
+                const int32_t a = src[i], b = dst[i];
+                bad |= (static_cast<uint32_t>(a) >= N) | (static_cast<uint32_t>(b) >= N);
+                tmp[cnt] = static_cast<int32_t>(i);
+                cnt += ((a & pm) == me) | ((b & pm) == me);
+            }
+        }
+        if (bad) {
+            for (int64_t i = lo; i < hi; ++i) {
+                const int64_t a = src[i], b = dst[i], g = neg ? static_cast<int64_t>(neg[i]) : a;
+                if (a < 0 || a >= h->num_nodes || b < 0 || b >= h->num_nodes || g < 0 || g >= h->num_nodes)
+                    return fail("node id out of range at edge %lld (num_nodes=%lld)", (long long)i, (long long)h->num_nodes);
+            }
+        }
+        for (int c = 0; c < cnt; ++c) {
+            const int64_t e = eidx[tmp[c]];
+            if (e < 0 || e > 0x7fffffffLL) return fail("edge id %lld does not fit int32", (long long)e);
+        }
+        list.insert(list.end(), tmp, tmp + cnt);
+    }
+    // per batch, the list position of its first edge (the list is ascending)
+    const int64_t n_batches = (m + batch_size - 1) / batch_size;
+    batch_ofs.assign(static_cast<size_t>(n_batches) + 1, 0);
+    size_t pos = 0;
+    for (int64_t b = 0; b < n_batches; ++b) {
+        const int64_t first = b * batch_size;
+        while (pos < list.size() && list[pos] < first) ++pos;
+        batch_ofs[static_cast<size_t>(b)] = static_cast<int64_t>(pos);
     }
     batch_ofs[static_cast<size_t>(n_batches)] = static_cast<int64_t>(list.size());
     return 0;
