@@ -166,7 +166,7 @@ int ensure_staging(zebra_tppr *h, Staging &s, size_t edges)
     return 0;
 }
 
-// Fills one staging slot for m edges and derives their dependencies (one forward and one backward
+// Fills one staging slot for m edges and derives their dependencies (one forward pass and a clean-up
 // pass, host scratch only — no state survives the call):
 //   prev_x   index (within these m edges) of the previous edge that wrote endpoint x, -1 = none;
 //   rthr_x   negative-sample reads of x's current version that must finish before it is overwritten;
@@ -183,7 +183,15 @@ int fill_soa(zebra_tppr *h, char *host, size_t cap, const NodeT *src, const Node
     int32_t *p_s = o_e + cap, *p_d = p_s + cap, *p_n = p_d + cap;
     uint32_t *r_s = reinterpret_cast<uint32_t *>(p_n + cap), *r_d = r_s + cap, *flg = r_d + cap;
     double *o_ts = reinterpret_cast<double *>(flg + cap);
-    for (int64_t i = 0; i < m; ++i) {   // validate before touching the scratch
+    // validate before touching the scratch (one branch-free sweep; the culprit is looked for only on failure)
+    const uint64_t uN = static_cast<uint64_t>(N);
+    uint64_t bad = 0;
+    for (int64_t i = 0; i < m; ++i) {
+        const uint64_t a = static_cast<uint64_t>(static_cast<int64_t>(src[i])), b = static_cast<uint64_t>(static_cast<int64_t>(dst[i]));
+        const uint64_t g = neg ? static_cast<uint64_t>(static_cast<int64_t>(neg[i])) : a;
+        bad |= (a >= uN) | (b >= uN) | (g >= uN) | (static_cast<uint64_t>(eidx[i]) > 0x7fffffffULL);
+    }
+    for (int64_t i = 0; bad && i < m; ++i) {
         const int64_t a = src[i], b = dst[i], g = neg ? static_cast<int64_t>(neg[i]) : a;
         const int64_t e = eidx[i];
         if (a < 0 || a >= N || b < 0 || b >= N || g < 0 || g >= N)
@@ -193,7 +201,31 @@ int fill_soa(zebra_tppr *h, char *host, size_t cap, const NodeT *src, const Node
     NodeDep *dep = h->dep.data();
     if (h->rnext.size() < static_cast<size_t>(m)) h->rnext.resize(static_cast<size_t>(m));
     int32_t *rnext = h->rnext.data();
+    // kFlagDstFirst without a backward pass: NodeDep::pad remembers, per node, the latest edge (index + 1)
+    // that wrote it and does not know yet which of its endpoints is rewritten first; the first later
+    // write of either endpoint settles it (one edge rewriting both: no preference)
+    auto settle = [&](uint32_t qe, int32_t x) {
+        const int32_t s = o_src[qe], d = o_dst[qe];
+        if (x == d) flg[qe] |= zebra::kFlagDstFirst;
+        NodeDep &other = dep[x == d ? s : d];
+        if (other.pad == qe + 1) other.pad = 0;
+        dep[x].pad = 0;
+    };
+    auto overwrite = [&](NodeDep &n, int64_t i, int32_t &prev, uint32_t &rthr) {
+        prev = n.lastw; rthr = n.rcount;
+        if (n.rcount) {                                               // its pending negative reads must signal
+            for (int32_t r = n.rhead; r >= 0; r = rnext[r]) flg[r] |= zebra::kFlagSignal;
+            n.rhead = -1; n.rcount = 0;
+        }
+        n.lastw = static_cast<int32_t>(i);
+    };
+    constexpr int64_t kAhead = 12;                                    // the scratch look-ups are cache misses: fetch ahead
     for (int64_t i = 0; i < m; ++i) {
+        if (i + kAhead < m) {
+            __builtin_prefetch(dep + src[i + kAhead], 1);
+            __builtin_prefetch(dep + dst[i + kAhead], 1);
+            if (neg) __builtin_prefetch(dep + neg[i + kAhead], 1);
+        }
         const int32_t a = static_cast<int32_t>(src[i]), b = static_cast<int32_t>(dst[i]);
         const int32_t g = neg ? static_cast<int32_t>(neg[i]) : a;
         o_src[i] = a; o_dst[i] = b; o_neg[i] = g;
@@ -206,32 +238,25 @@ int fill_soa(zebra_tppr *h, char *host, size_t cap, const NodeT *src, const Node
         } else {
             p_n[i] = -1;
         }
-        p_s[i] = dep[a].lastw; r_s[i] = dep[a].rcount;
-        if (dep[a].rcount) {
-            for (int32_t r = dep[a].rhead; r >= 0; r = rnext[r]) flg[r] |= zebra::kFlagSignal;
-            dep[a].rhead = -1; dep[a].rcount = 0;
+        NodeDep *da = dep + a, *db = b != a ? dep + b : nullptr;
+        const uint32_t qa = da->pad, qb = db ? db->pad : 0u;
+        if (qa && qa == qb) {
+            da->pad = 0; db->pad = 0;
+        } else {
+            if (qa) settle(qa - 1, a);
+            if (qb) settle(qb - 1, b);
         }
-        dep[a].lastw = static_cast<int32_t>(i);
-        if (b != a) {
-            p_d[i] = dep[b].lastw; r_d[i] = dep[b].rcount;
-            if (dep[b].rcount) {
-                for (int32_t r = dep[b].rhead; r >= 0; r = rnext[r]) flg[r] |= zebra::kFlagSignal;
-                dep[b].rhead = -1; dep[b].rcount = 0;
-            }
-            dep[b].lastw = static_cast<int32_t>(i);
+        overwrite(*da, i, p_s[i], r_s[i]);
+        if (db) {
+            overwrite(*db, i, p_d[i], r_d[i]);
+            da->pad = static_cast<uint32_t>(i) + 1; db->pad = static_cast<uint32_t>(i) + 1;
         } else {
             p_d[i] = -1; r_d[i] = 0;
         }
     }
-    // backward: which endpoint is written again first (lastw doubles as "next write", INT_MAX = never)
-    for (int64_t i = 0; i < m; ++i) { dep[o_src[i]].lastw = INT_MAX; dep[o_dst[i]].lastw = INT_MAX; }
-    for (int64_t i = m - 1; i >= 0; --i) {
-        const int32_t a = o_src[i], b = o_dst[i];
-        if (a != b && dep[b].lastw < dep[a].lastw) flg[i] |= zebra::kFlagDstFirst;
-        dep[a].lastw = static_cast<int32_t>(i); dep[b].lastw = static_cast<int32_t>(i);
-    }
-    for (int64_t i = 0; i < m; ++i) {
-        dep[o_src[i]].lastw = -1; dep[o_dst[i]].lastw = -1;
+    for (int64_t i = 0; i < m; ++i) {                                 // the scratch goes back to "no writer, no reader"
+        dep[o_src[i]].lastw = -1; dep[o_src[i]].pad = 0;
+        dep[o_dst[i]].lastw = -1; dep[o_dst[i]].pad = 0;
         dep[o_neg[i]].rhead = -1; dep[o_neg[i]].rcount = 0;
     }
     return 0;
