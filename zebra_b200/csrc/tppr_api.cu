@@ -19,6 +19,9 @@
 #include <string>
 #include <vector>
 
+#include <stdlib.h>
+#include <sys/mman.h>
+
 namespace {
 thread_local std::string g_err;
 }
@@ -54,13 +57,45 @@ struct Staging {
 // the current version and their count (all -1 / 0 between passes)
 struct NodeDep { int32_t lastw, rhead; uint32_t rcount, pad; };
 
+// The per-node scratch of the host dependency pass is read at random (negative samples are uniform
+// over the nodes): with 4 KB pages nearly every look-up is a TLB miss on top of the cache miss, and a
+// software prefetch that misses the TLB is dropped.  2 MB-aligned and madvise(MADV_HUGEPAGE): a handful
+// of huge pages when the kernel grants them, plain memory otherwise.
+template <typename T>
+struct HugeArray {
+    T *p = nullptr;
+    size_t n = 0;
+    HugeArray() = default;
+    HugeArray(const HugeArray &) = delete;
+    HugeArray &operator=(const HugeArray &) = delete;
+    ~HugeArray() { free(p); }
+    void assign(size_t count, const T &v)
+    {
+        if (count != n) {
+            free(p);
+            p = nullptr; n = 0;
+            constexpr size_t kHuge = size_t(2) << 20;
+            const size_t bytes = (std::max<size_t>(count, 1) * sizeof(T) + kHuge - 1) / kHuge * kHuge;
+            void *q = nullptr;
+            if (posix_memalign(&q, kHuge, bytes) != 0) throw std::bad_alloc();
+            madvise(q, bytes, MADV_HUGEPAGE);
+            p = static_cast<T *>(q); n = count;
+        }
+        std::fill(p, p + n, v);
+    }
+    T *data() { return p; }
+    size_t size() const { return n; }
+    const T *begin() const { return p; }
+    const T *end() const { return p + n; }
+};
+
 struct zebra_tppr {
     int64_t num_nodes = 0;
     int32_t k = 0, n_tppr = 0, stride = 0, device = 0;
     double alpha[zebra::kMaxInst], beta[zebra::kMaxInst];
     char *tables[zebra::kMaxInst] = {};
     int32_t *rcnt = nullptr;                  // [n_tppr][num_nodes] negative reads finished, not yet consumed by a writer
-    std::vector<NodeDep> dep;                 // host scratch of the dependency pass, one cache line touch per node
+    HugeArray<NodeDep> dep;                   // host scratch of the dependency pass, one cache line touch per node
     std::vector<int32_t> rnext;
     uint32_t epoch = 0;                       // tag epoch the bound tables were last written in
     zebra::DecayStep *decay[zebra::kMaxInst] = {};   // device: update factors by update count
