@@ -1,9 +1,9 @@
 #!/bin/bash
 # One gpurun call: GPU parity tests, perf probe, bench (ours + reference arm), ncu launch list + full capture.
-# Usage (from the repo root on the GPU box): bash tools/gpu_check.sh [tests|bench|ncu ...]
+# Usage (from the repo root on the GPU box): bash tools/gpu_check.sh [tests|probe|bench|ncu|kernels|lazy|e2e ...]
 set -u
 mkdir -p gpurun_out
-WHAT="${*:-tests probe bench ncu kernels}"
+WHAT="${*:-tests probe bench ncu kernels lazy}"
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/gpu.txt 2>&1
 lscpu | head -20 > gpurun_out/lscpu.txt 2>&1
 for w in $WHAT; do
@@ -27,5 +27,13 @@ kernels)
   timeout 600 python tools/perf_kernels.py > gpurun_out/kernels.log 2>&1; echo "kernels rc=$?"; cat gpurun_out/kernels.log
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:"gather_fwd|prune_topk" -c 6 -f -o gpurun_out/prof_kernels python tools/perf_kernels.py > gpurun_out/ncu_kernels.log 2>&1
   echo "ncu kernels rc=$?" ;;
+lazy)
+  # lazy memory update (level 2): microbench + launch list of the selection / lazy gather kernels
+  timeout 300 python tools/perf_lazy.py > gpurun_out/perf_lazy.log 2>&1; echo "perf_lazy rc=$?"; cat gpurun_out/perf_lazy.log
+  timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"pending_|gather_" -c 60 --csv --log-file gpurun_out/launches_lazy.csv python tools/perf_lazy.py > gpurun_out/ncu_lazy.log 2>&1
+  echo "ncu lazy rc=$?" ;;
+e2e)
+  # the reference's train.py, reference arm against levels 1 and 2 (three configs would take ~6 GPU-minutes: one here)
+  timeout 900 python tools/e2e_train.py --ref baseline/_ref --name wikipedia --epochs 3 --levels ref 1 2 --out gpurun_out/e2e 2>&1 | tail -4 ;;
 esac
 done
