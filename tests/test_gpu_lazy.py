@@ -175,3 +175,53 @@ def test_level2_embedding_equals_level1_in_training():
                     torch.testing.assert_close(x, y, rtol=1e-5, atol=1e-6)
     finally:
         E.LAZY_MEMORY = old
+
+
+@pytest.mark.skipif(__import__("os").environ.get("ZEBRA_NEW_GPU_TESTS") != "1",
+                    reason="recorded from the reference after the last GPU session of round 1; first B200 run pending "
+                           "(ZEBRA_NEW_GPU_TESTS=1 enables it)")
+@pytest.mark.parametrize("lazy", [False, True])
+def test_train_branch_matches_reference_recording(lazy):
+    """Levels 1 and 2 against a recording of the reference's own train branch (its Memory, its
+    GRUMemoryUpdater.get_updated_memory, its GraphDiffusionEmbedding; tests/golden/make_golden_embedding_train.py).
+    Tolerance 2e-5 / 1e-4 (the recording's GEMMs ran on the CPU)."""
+    from tests import helpers as H
+    from zebra_b200 import embedding as E
+    g = H.load("embedding_train_streaming_wikipedia")
+    n_edges, d_e = int(g["n_edges"]), int(g["d_e"])
+    st, neg, N, ef, memory = H.embedding_inputs("wikipedia", n_edges, d_e)
+    assert N == int(g["num_nodes"]) and np.isclose(float(memory.sum()), float(g["mem_sum"]))
+    dev = torch.device("cuda")
+    args = types.SimpleNamespace(alpha_list=[0.1, 0.1], beta_list=[0.5, 0.95], topk=20, tppr_strategy="streaming", n_degree=10, n_layer=2)
+    mod = E.GraphDiffusionEmbedding(torch.from_numpy(ef).to(dev), None, d_e, 100, 100, dev, args, N).to(dev)
+    mod.load_state_dict({k[3:]: torch.from_numpy(g[k]) for k in g.files if k.startswith("sd.")})
+    mod.train()
+    mod.drop.p = 0.0
+    d_msg = 2 * 100 + d_e + 100
+    cell = torch.nn.GRUCell(d_msg, 100).to(dev)
+    cell.load_state_dict({k[7:]: torch.from_numpy(g[k]) for k in g.files if k.startswith("gru_sd.")})
+    rng = np.random.default_rng(int(g["msg_seed"]))
+    messages = (rng.standard_normal((N, d_msg)) * 0.3).astype(np.float32)
+    flags = np.unpackbits(g["flags"], axis=1)[:, :N].astype(bool)
+    mem = types.SimpleNamespace(memory=torch.from_numpy(memory).to(dev), messages=torch.from_numpy(messages).to(dev),
+                                last_update=torch.zeros(N, device=dev), timestamps=torch.zeros(N, device=dev), nodes=None)
+    params = {**{f"mod.{k}": v for k, v in mod.named_parameters()}, **{f"gru.memory_updater.{k}": v for k, v in cell.named_parameters()}}
+    old = E.LAZY_MEMORY
+    E.LAZY_MEMORY = lazy
+    try:
+        for b, lo in enumerate(range(0, n_edges, 200)):
+            hi = lo + 200
+            mem.nodes = flags[b].copy()
+            nodes = np.concatenate([st.src[lo:hi], st.dst[lo:hi], neg[lo:hi]])
+            ts = np.concatenate([st.ts[lo:hi]] * 3)
+            for p in params.values():
+                p.grad = None
+            emb = mod.compute_embedding_tppr_ensemble(mem, nodes, ts, st.eidx[lo:hi].astype(np.int64), _Updater(cell), True)
+            emb.square().sum().backward()
+            if f"emb_{b}" in g.files:
+                torch.testing.assert_close(emb.detach().cpu(), torch.from_numpy(g[f"emb_{b}"]), rtol=2e-5, atol=2e-5)
+                for k in g.files:
+                    if k.startswith(f"grad_{b}."):
+                        torch.testing.assert_close(params[k[len(f"grad_{b}."):]].grad.cpu(), torch.from_numpy(g[k]), rtol=1e-4, atol=1e-4)
+    finally:
+        E.LAZY_MEMORY = old
