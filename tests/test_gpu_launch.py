@@ -1,0 +1,53 @@
+"""Row A12: the reference's own, unmodified train.py (a copy under baseline/_ref, made by
+__graft_entry__.build()) driven through `python -m zebra_b200.launch` at levels 0, 1 and 2, one
+epoch on a tiny Wikipedia-shaped stream, against `--level ref` (the reference's numba finder).
+Same seed, same flags: validation / new-node validation / test AP must agree within 0.2 points
+(north_star), and level 0 — which only swaps the finder classes — to the last printed digit.
+Reference: train.py:188-306, modules/embedding_module.py:217-278."""
+import os
+import re
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.path.join(ROOT, "baseline", "_ref")
+
+
+def _run(level, work, name, strategy):
+    cmd = [sys.executable, "-m", "zebra_b200.launch", "--ref", REF, "--level", level, "--workdir", work, "--",
+           "-d", name, "--bs", "200", "--n_epoch", "1", "--tppr_strategy", strategy, "--topk", "20",
+           "--alpha_list", "0.1", "0.1", "--beta_list", "0.5", "0.95", "--gpu", "0", "--n_degree", "10", "--n_layer", "2"]
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""), PYTHONDONTWRITEBYTECODE="1")
+    r = subprocess.run(cmd, env=env, cwd=ROOT, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-3000:]
+    text = ""
+    logdir = os.path.join(work, "log", name)
+    for f in sorted(os.listdir(logdir)):
+        text += open(os.path.join(logdir, f)).read()
+    val = re.findall(r"val ap: ([\d.]+), new node val ap: ([\d.]+)", text)
+    test = re.findall(r"Test statistics: (Old|New) nodes -- auc: ([\d.]+), ap: ([\d.]+)", text)
+    assert val and len(test) == 2, text[-2000:]
+    return [float(x) for x in val[-1]] + [float(ap) for _, _, ap in test], [x for x in val[-1]] + [ap for _, _, ap in test]
+
+
+@pytest.mark.parametrize("strategy", ["streaming", "pruning"])
+def test_train_py_through_launcher_matches_reference(tmp_path, strategy):
+    assert os.path.exists(os.path.join(REF, "train.py")), "baseline/_ref missing: run __graft_entry__.build() in the build container"
+    from zebra_b200 import synth
+    name = "wikipedia"
+    st = synth.make_stream(name, n_edges=4000)
+    synth.write_ml_format(st, str(tmp_path / "data"), name)
+    res = {}
+    for level in ("ref", "0", "1", "2"):
+        work = tmp_path / f"run_{level}"
+        work.mkdir()
+        res[level] = _run(level, str(work), name, strategy)
+    ref_v, ref_s = res["ref"]
+    assert res["0"][1] == ref_s, f"level 0 must print the reference's AP digits: {res['0'][1]} vs {ref_s}"
+    for level in ("1", "2"):
+        for a, b in zip(res[level][0], ref_v):
+            assert abs(a - b) <= 0.002, (level, res[level][1], ref_s)       # 0.2 AP points

@@ -177,9 +177,6 @@ def test_level2_embedding_equals_level1_in_training():
         E.LAZY_MEMORY = old
 
 
-@pytest.mark.skipif(__import__("os").environ.get("ZEBRA_NEW_GPU_TESTS") != "1",
-                    reason="recorded from the reference after the last GPU session of round 1; first B200 run pending "
-                           "(ZEBRA_NEW_GPU_TESTS=1 enables it)")
 @pytest.mark.parametrize("lazy", [False, True])
 def test_train_branch_matches_reference_recording(lazy):
     """Levels 1 and 2 against a recording of the reference's own train branch (its Memory, its

@@ -6,7 +6,7 @@ import oracle
 from tests import helpers as H
 
 
-@pytest.mark.parametrize("name", H.STREAM_CASES + H.STREAM_CASES_LATE)
+@pytest.mark.parametrize("name", H.STREAM_CASES)
 def test_stream_bit_exact_vs_reference(name):
     g = H.load(name)
     f = oracle.OracleFinder(int(g["num_nodes"]), int(g["k"]), len(g["alphas"]), list(g["alphas"]), list(g["betas"]))

@@ -32,6 +32,15 @@ lazy)
   timeout 300 python tools/perf_lazy.py > gpurun_out/perf_lazy.log 2>&1; echo "perf_lazy rc=$?"; cat gpurun_out/perf_lazy.log
   timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"pending_|gather_" -c 60 --csv --log-file gpurun_out/launches_lazy.csv python tools/perf_lazy.py > gpurun_out/ncu_lazy.log 2>&1
   echo "ncu lazy rc=$?" ;;
+sanitize)
+  # compute-sanitizer over smoke() (streaming path against the oracle): memcheck, racecheck (shared memory), synccheck
+  for tool in memcheck racecheck synccheck; do
+    timeout 900 compute-sanitizer --tool $tool --log-file gpurun_out/sanitizer_$tool.log python __graft_entry__.py smoke > gpurun_out/sanitizer_$tool.out 2>&1
+    echo "sanitizer $tool rc=$?"; tail -3 gpurun_out/sanitizer_$tool.log; tail -1 gpurun_out/sanitizer_$tool.out
+  done ;;
+star)
+  ZEBRA_TPPR_LIB=zebra_b200/lib/libzebra_tppr_prof.so timeout 600 python tools/perf_probe.py --star > gpurun_out/star_prof.log 2>&1; echo "star prof rc=$?"; cat gpurun_out/star_prof.log
+  timeout 600 python tools/perf_probe.py --star > gpurun_out/star.log 2>&1; echo "star rc=$?"; cat gpurun_out/star.log ;;
 e2e)
   # the reference's train.py, reference arm against levels 1 and 2 (three configs would take ~6 GPU-minutes: one here)
   timeout 900 python tools/e2e_train.py --ref baseline/_ref --name wikipedia --epochs 3 --levels ref 1 2 --out gpurun_out/e2e 2>&1 | tail -4 ;;

@@ -66,9 +66,9 @@ SIGNATURES = {
 def lib():
     global _lib
     if _lib is None:
-        so = os.environ.get("ZEBRA_TPPR_LIB") or _build.SO     # developer override (e.g. the -DZEBRA_PROFILE build)
-        if not os.path.exists(so):
-            so = _build.build()
+        so = os.environ.get("ZEBRA_TPPR_LIB")                  # developer override (e.g. the -DZEBRA_PROFILE build)
+        if not so:
+            so = _build.build()                                # compiles only when csrc/ or include/ is newer than the .so
         L = C.CDLL(so)
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(L, name)

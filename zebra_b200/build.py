@@ -21,12 +21,22 @@ def sources():
     return sorted(glob.glob(os.path.join(CSRC, "*.cu")))
 
 
+def source_digest() -> str:
+    """SHA-256 over the contents of csrc/ and include/ (and the flags): what the shipped .so must match.
+    Content, not mtimes: a snapshot copied to the GPU box keeps the bytes but not necessarily the times."""
+    import hashlib
+    h = hashlib.sha256(" ".join(NVCC_FLAGS).encode())
+    for d in sorted(glob.glob(os.path.join(CSRC, "*")) + glob.glob(os.path.join(HERE, "..", "include", "*.h"))):
+        h.update(os.path.basename(d).encode())
+        h.update(open(d, "rb").read())
+    return h.hexdigest()
+
+
 def stale() -> bool:
-    if not os.path.exists(SO):
+    stamp = SO + ".stamp"
+    if not os.path.exists(SO) or not os.path.exists(stamp):
         return True
-    t = os.path.getmtime(SO)
-    deps = glob.glob(os.path.join(CSRC, "*")) + glob.glob(os.path.join(HERE, "..", "include", "*.h"))
-    return any(os.path.getmtime(d) > t for d in deps)
+    return open(stamp).read().strip() != source_digest()
 
 
 def build(force: bool = False, verbose: bool = False, profile: bool = False, ablate: int = 0) -> str:
@@ -38,9 +48,19 @@ def build(force: bool = False, verbose: bool = False, profile: bool = False, abl
         return SO
     os.makedirs(LIBDIR, exist_ok=True)
     nvcc = os.environ.get("NVCC") or ("/usr/local/cuda/bin/nvcc" if os.path.exists("/usr/local/cuda/bin/nvcc") else "nvcc")
-    cmd = ([nvcc] + NVCC_FLAGS + (["-DZEBRA_PROFILE"] if profile else []) + ([f"-DZEBRA_ABLATE={ablate}"] if ablate else []) + (["-Xptxas", "-v"] if verbose else [])
-           + ["-o", out] + sources())
-    subprocess.check_call(cmd)
+    import fcntl
+    with open(os.path.join(LIBDIR, ".build.lock"), "w") as lock:      # several ranks may import at once
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        if not force and not profile and not ablate and not stale():
+            return SO                                                 # another process built it meanwhile
+        tmp = out + f".tmp{os.getpid()}"
+        cmd = ([nvcc] + NVCC_FLAGS + (["-DZEBRA_PROFILE"] if profile else []) + ([f"-DZEBRA_ABLATE={ablate}"] if ablate else [])
+               + (["-Xptxas", "-v"] if verbose else []) + ["-o", tmp] + sources())
+        subprocess.check_call(cmd)
+        os.replace(tmp, out)
+        if out == SO:
+            with open(SO + ".stamp", "w") as f:
+                f.write(source_digest())
     return out
 
 

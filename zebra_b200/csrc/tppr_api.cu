@@ -116,6 +116,7 @@ struct zebra_tppr {
     int max_blocks = 0;
     int64_t launches = 0, last_items = 0, last_ties = 0, last_merge = 0, timeouts = 0;
     struct zebra_plan *plan_active = nullptr;   // a plan is part-way through its batches
+    bool rcnt_dirty = false;                    // a span was abandoned part-way: unconsumed negative-read counts may remain
     int64_t plan_next = 0;
     struct zebra_epoch *epoch_active = nullptr; // a pipelined epoch is part-way through its windows
     // window ring of the pipelined epoch path, kept across epochs (pinned allocations are slow)
@@ -575,6 +576,18 @@ int check_status(zebra_tppr *h, cudaStream_t st)
     return 0;
 }
 
+// Every way of streaming a span starts here.  The per-node counters of finished negative reads return
+// to zero by themselves over a COMPLETE span (the host marks exactly the reads a later writer consumes);
+// a span abandoned part-way (plan destroyed or re-started, failed launch, epoch closed early) leaves
+// counts behind that would let a later writer overwrite a version its real readers have not loaded yet,
+// so the counters are cleared whenever the previous span did not run to its end.
+int begin_span(zebra_tppr *h, cudaStream_t st)
+{
+    if (h->rcnt_dirty) CU(cudaMemsetAsync(h->rcnt, 0, sizeof(int32_t) * h->num_nodes * h->n_tppr, st));
+    h->rcnt_dirty = true;
+    return 0;
+}
+
 template <typename NodeT>
 int run_span(zebra_tppr *h, const NodeT *src, const NodeT *dst, const NodeT *neg, const double *ts, const int64_t *eidx,
              int64_t n, int32_t rows_per_edge, int32_t inst_mask, char *out, cudaStream_t st)
@@ -584,8 +597,9 @@ int run_span(zebra_tppr *h, const NodeT *src, const NodeT *dst, const NodeT *neg
     if (h->world > 1) return fail("node-sharded handles stream through plans (zebra_tppr_plan_run): dependencies must be span-global across ranks");
     if (h->plan_active || h->epoch_active) return fail("a plan or epoch is part-way through its batches; finish it before streaming other spans");
     CU(cudaSetDevice(h->device));
-    CU(cudaMemsetAsync(h->status + 1, 0, 3 * sizeof(int32_t), st));   // [0] (time-out) is sticky
+    CU(cudaMemsetAsync(h->status + 1, 0, 3 * sizeof(int32_t), st));   // [0] (time-out) is sticky until a reset
     h->last_items = 0;
+    if (begin_span(h, st)) return 1;
     for (int64_t lo = 0; lo < n; lo += kChunk) {
         const int64_t m = std::min(kChunk, n - lo);
         Staging &s = h->stg[h->stg_next];
@@ -597,6 +611,7 @@ int run_span(zebra_tppr *h, const NodeT *src, const NodeT *dst, const NodeT *neg
     }
     CU(cudaEventRecord(h->ev1, st));
     h->timed = true;
+    h->rcnt_dirty = false;
     return 0;
 }
 
@@ -728,7 +743,9 @@ int zebra_tppr_reset_tickets(zebra_tppr_t *h, void *stream)
     CU(cudaSetDevice(h->device));
     CU(cudaStreamSynchronize(st));
     CU(cudaMemsetAsync(h->rcnt, 0, sizeof(int32_t) * h->num_nodes * h->n_tppr, st));
+    CU(cudaMemsetAsync(h->status, 0, 4 * sizeof(int32_t), st));       // also clears a recorded wait time-out
     h->plan_active = nullptr;
+    h->rcnt_dirty = false;
     return 0;
 }
 
@@ -966,8 +983,7 @@ int zebra_tppr_plan_run(zebra_tppr_t *h, zebra_plan_t *pl, int64_t first_batch, 
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     CU(cudaSetDevice(h->device));
     if (first_batch == 0) {
-        // a run abandoned part-way may have left unconsumed read counts behind
-        if (h->plan_active) CU(cudaMemsetAsync(h->rcnt, 0, sizeof(int32_t) * h->num_nodes * h->n_tppr, st));
+        if (begin_span(h, st)) return 1;   // clears what a run abandoned part-way left behind
         if (alloc_seq(h, pl->n, st, &pl->seq0)) return 1;
         h->plan_active = pl;
         h->plan_next = 0;
@@ -1006,7 +1022,7 @@ int zebra_tppr_plan_run(zebra_tppr_t *h, zebra_plan_t *pl, int64_t first_batch, 
     CU(cudaEventRecord(h->ev1, st));
     h->timed = true;
     h->plan_next = last;
-    if (last == pl->n_batches) h->plan_active = nullptr;
+    if (last == pl->n_batches) { h->plan_active = nullptr; h->rcnt_dirty = false; }
     return 0;
 }
 
@@ -1094,6 +1110,7 @@ int zebra_tppr_epoch_begin(zebra_tppr_t *h, const int32_t *host_src, const int32
     ep->st = static_cast<cudaStream_t>(stream);
     CU(cudaMemsetAsync(h->status + 1, 0, 3 * sizeof(int32_t), ep->st));
     h->last_items = 0;
+    if (begin_span(h, ep->st)) { delete ep; return 1; }
     h->epoch_active = ep;
     // two windows in flight before the caller asks for the first
     for (int q = 0; q < 2 && ep->issued < ep->n_windows; ++q)
@@ -1129,6 +1146,7 @@ int zebra_tppr_epoch_next(zebra_epoch_t *ep, void **host_rows, int64_t *first_ba
         h->last_ties = h->status_host[1];
         h->last_merge = h->status_host[2];
         if (h->status_host[0] != 0) { h->timeouts++; return fail("T-PPR span kernel: dependency wait timed out"); }
+        h->rcnt_dirty = false;
     }
     return 0;
 }

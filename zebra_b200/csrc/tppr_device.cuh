@@ -142,23 +142,36 @@ __device__ __forceinline__ VecR vsel(bool c, const VecR &a, const VecR &b)
     return r;
 }
 
+// Tagged chunks are read and written with the scalar 128-bit forms (ld/st.relaxed.*.b128, PTX ISA 8.3):
+// the PTX memory model defines a .b128 access as ONE access, so a chunk's tag can never be seen with
+// a payload of another version (a .v4.u32 access is formally four scalar accesses in unspecified order;
+// both compile to LDG/STG.E.128.STRONG on sm_100a).
 template <bool kSys = false>
 __device__ __forceinline__ uint4 ld_chunk(const char *p)
 {
-    uint4 v;
+    unsigned long long lo, hi;
     if (kSys)   // memory another GPU writes into (mailboxes of the node-sharded mode)
-        asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+        asm volatile("{\n\t.reg .b128 r;\n\tld.relaxed.sys.global.b128 r, [%2];\n\tmov.b128 {%0, %1}, r;\n\t}" : "=l"(lo), "=l"(hi) : "l"(p) : "memory");
     else
-        asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+        asm volatile("{\n\t.reg .b128 r;\n\tld.relaxed.gpu.global.b128 r, [%2];\n\tmov.b128 {%0, %1}, r;\n\t}" : "=l"(lo), "=l"(hi) : "l"(p) : "memory");
+    uint4 v;
+    v.x = static_cast<uint32_t>(lo); v.y = static_cast<uint32_t>(lo >> 32);
+    v.z = static_cast<uint32_t>(hi); v.w = static_cast<uint32_t>(hi >> 32);
     return v;
 }
 
-__device__ __forceinline__ void st_chunk(char *p, double d, int i, uint32_t tag)
+template <bool kSys = false>
+__device__ __forceinline__ void st_chunk_t(char *p, double d, int i, uint32_t tag)
 {
-    const unsigned long long b = static_cast<unsigned long long>(__double_as_longlong(d));
-    asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(static_cast<uint32_t>(b)),
-                 "r"(static_cast<uint32_t>(b >> 32)), "r"(i), "r"(tag) : "memory");
+    const unsigned long long lo = static_cast<unsigned long long>(__double_as_longlong(d));
+    const unsigned long long hi = (static_cast<unsigned long long>(tag) << 32) | static_cast<uint32_t>(i);
+    if (kSys)
+        asm volatile("{\n\t.reg .b128 r;\n\tmov.b128 r, {%1, %2};\n\tst.relaxed.sys.global.b128 [%0], r;\n\t}" ::"l"(p), "l"(lo), "l"(hi) : "memory");
+    else
+        asm volatile("{\n\t.reg .b128 r;\n\tmov.b128 r, {%1, %2};\n\tst.relaxed.gpu.global.b128 [%0], r;\n\t}" ::"l"(p), "l"(lo), "l"(hi) : "memory");
 }
+
+__device__ __forceinline__ void st_chunk(char *p, double d, int i, uint32_t tag) { st_chunk_t<false>(p, d, i, tag); }
 
 __device__ __forceinline__ double chunk_f64(const uint4 &c)
 {

@@ -31,17 +31,6 @@
 
 namespace zebra {
 
-template <bool kSys>
-__device__ __forceinline__ void st_chunk_t(char *p, double d, int i, uint32_t tag)
-{
-    const unsigned long long b = static_cast<unsigned long long>(__double_as_longlong(d));
-    if (kSys)
-        asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(static_cast<uint32_t>(b)),
-                     "r"(static_cast<uint32_t>(b >> 32)), "r"(i), "r"(tag) : "memory");
-    else
-        st_chunk(p, d, i, tag);
-}
-
 // Copy of a vector held in registers into a mailbox slot of a peer (or of this rank, world = 1 tests).
 __device__ __forceinline__ void push_vector(char *slot, int k, const VecR &v, uint32_t tag, int lane)
 {
