@@ -50,7 +50,7 @@ def test_full_size_config_vs_oracle(name):
     assert next(epoch, None) is None
     rng = np.random.default_rng(3)
     deg = np.bincount(np.concatenate([st.src, st.dst]), minlength=N)
-    sample = np.unique(np.concatenate([np.argsort(deg)[-500:], rng.choice(np.nonzero(deg)[0], min(6000, int((deg > 0).sum())))]))
+    sample = np.unique(np.concatenate([np.argsort(deg)[-500:], rng.choice(np.nonzero(deg)[0], min(6000, int((deg > 0).sum())), replace=False)]))
     assert len(sample) >= min(5000, int((deg > 0).sum()) // 2)
     for f in (f_plan, f_epoch):
         for j in range(2):
