@@ -197,7 +197,8 @@ int zebra_tppr_sync_check(zebra_tppr_t *h, void *stream);
 
 /* Counters (8 entries) of the last zebra_tppr_stream / update_only / plan_run / epoch: [0] work
  * items, [1] prunes that took the exact tie path, [2] kernel launches so far on this handle,
- * [3] spin time-outs (must be 0), [4] prunes ranked by the sorted-merge fast path, [5..7] zero. */
+ * [3] spin time-outs (must be 0), [4] prunes ranked by the sorted-merge fast path, [5] edges with a chain-node endpoint,
+ * [6] steps walked by resident chain warps (tppr_device.cuh "hub chains"), [7] zero. */
 int zebra_tppr_counters(zebra_tppr_t *h, int64_t *out8);
 
 /* Developer builds (-DZEBRA_PROFILE) accumulate clock64 cycles per kernel phase; this reads and

@@ -145,6 +145,37 @@ struct zebra_tppr {
     int32_t row_mode = 0;
     char *plan_stage = nullptr;                // pinned staging of sharded plans, kept across plans
     size_t plan_stage_cap = 0;
+    // hub chains (tppr_device.cuh "hub chains"): the chain nodes of the span being streamed
+    bool chains_enabled = true;
+    int32_t max_chains = zebra::kMaxChains;
+    std::vector<int32_t> chain_cnt;            // [num_nodes] scratch of the detection pass (zero between passes)
+    char *cmbox = nullptr;                     // chain mailbox (device), grown on demand
+    size_t cmbox_cap = 0;
+    unsigned long long wait_ns = 20000000000ull;
+    int64_t chain_items = 0, chain_steps = 0;  // statistics of the last span
+};
+
+// The chain nodes of one span (chosen once per span, used by every dependency pass over its edges).
+struct ChainSet {
+    int32_t n = 0;
+    int32_t node[zebra::kMaxChains] = {};
+    std::vector<uint8_t> map;                  // [num_nodes] 0 = ordinary node, q + 1 = chain q; empty when n == 0
+};
+
+// What one host dependency pass found out about the chain nodes of its edges.
+struct ChainBuild {
+    std::vector<zebra::ChainStep> steps[zebra::kMaxChains];
+    int32_t n_items = 0;
+    void clear() { for (auto &v : steps) v.clear(); n_items = 0; }
+    size_t total() const { size_t t = 0; for (auto &v : steps) t += v.size(); return t; }
+};
+
+// Chain geometry of one kernel launch.
+struct ChainLaunch {
+    int32_t n = 0;
+    int32_t node[zebra::kMaxChains], begin[zebra::kMaxChains], end[zebra::kMaxChains];
+    const zebra::ChainStep *dev_steps = nullptr;
+    int32_t cidx_base = 0, n_items = 0;
 };
 
 // A span prepared once and kept resident in HBM (edge records + dependency thresholds).
@@ -159,6 +190,14 @@ struct zebra_plan {
     // position in that list of its first edge
     int32_t *dev_list = nullptr;
     std::vector<int64_t> batch_ofs;
+    // hub chains of the span: per chain the span indices of its steps (ascending) and where its step records
+    // start inside the device image; per chain item the span index of its edge
+    int32_t chain_n = 0;
+    int32_t chain_node[zebra::kMaxChains] = {};
+    std::vector<int32_t> chain_edges[zebra::kMaxChains];
+    int32_t chain_off[zebra::kMaxChains + 1] = {};
+    std::vector<int32_t> item_edge;
+    size_t steps_bytes = 0;
 };
 
 // A pipelined pass over a host-resident span: windows of whole batches are staged, computed and
@@ -174,6 +213,8 @@ struct zebra_epoch {
     size_t slot_bytes = 0;          // one batch's rows
     int64_t issued = 0, consumed = 0;
     cudaStream_t st = nullptr;
+    ChainSet cs;                    // chain nodes of the span, chosen at epoch_begin
+    ChainBuild cb;
 };
 
 namespace {
@@ -181,7 +222,11 @@ namespace {
 size_t record_bytes(int k) { return zebra::record_stride(k); }
 
 // bytes per edge in a staging slot: src,dst,neg,eidx,prev_s,prev_d,prev_n,rthr_s,rthr_d,flags (4 B each) + ts (8 B)
-constexpr size_t kEdgeBytes = 10 * 4 + 8;
+// + cidx (4 B, chain item index); the chain step records of the slot follow the arrays
+constexpr size_t kEdgeBytes = 10 * 4 + 8 + 4;
+constexpr size_t kCidxOffset = 10 * 4 + 8;          // byte offset of the cidx array, per unit of `cap`
+constexpr size_t kStepBytesPerEdge = 2 * sizeof(zebra::ChainStep);   // worst case: both endpoints are chain nodes
+constexpr int64_t kChainMinEdges = 4096;            // shorter spans are streamed without chain warps
 
 // Tags are edge sequence numbers drawn from one process-wide counter, so a table written through one
 // handle can be bound to another.  Tag 0 is what a zero-filled table carries.
@@ -195,11 +240,57 @@ int ensure_staging(zebra_tppr *h, Staging &s, size_t edges)
     if (s.host) CU(cudaFreeHost(s.host));
     if (s.dev) CU(cudaFree(s.dev));
     size_t cap = std::max<size_t>(edges, 1024);
-    CU(cudaMallocHost(&s.host, cap * kEdgeBytes));
-    CU(cudaMalloc(&s.dev, cap * kEdgeBytes));
+    CU(cudaMallocHost(&s.host, cap * (kEdgeBytes + kStepBytesPerEdge)));
+    CU(cudaMalloc(&s.dev, cap * (kEdgeBytes + kStepBytesPerEdge)));
     if (!s.free_ev) CU(cudaEventCreateWithFlags(&s.free_ev, cudaEventDisableTiming));
     s.cap = cap;
     return 0;
+}
+
+// Picks the chain nodes of a span: the nodes with the most incident edges (sampled count), at most
+// h->max_chains of them, none below 1/16 of the hottest node or below 64 edges.  The choice (`cs`) is handed
+// to the dependency passes over the span's edges.
+template <typename NodeT>
+void detect_chains(zebra_tppr *h, const NodeT *src, const NodeT *dst, int64_t n, ChainSet &cs)
+{
+    cs.n = 0;
+    if (!h->chains_enabled || h->world > 1 || n < kChainMinEdges || h->max_chains <= 0) return;
+    const uint64_t N = static_cast<uint64_t>(h->num_nodes);
+    if (h->chain_cnt.size() != N) h->chain_cnt.assign(N, 0);
+    int32_t *cnt = h->chain_cnt.data();
+    const int64_t stride = std::max<int64_t>(1, n >> 20);
+    int32_t top = 0;
+    for (int64_t i = 0; i < n; i += stride) {
+        const uint64_t a = static_cast<uint64_t>(static_cast<int64_t>(src[i])), b = static_cast<uint64_t>(static_cast<int64_t>(dst[i]));
+        if (a < N) top = std::max(top, ++cnt[a]);
+        if (b < N && b != a) top = std::max(top, ++cnt[b]);
+    }
+    const int32_t thr = std::max<int32_t>({4, top / 16, static_cast<int32_t>((64 + stride - 1) / stride)});
+    std::vector<std::pair<int32_t, int32_t>> found;          // (count, node)
+    for (int64_t i = 0; i < n; i += stride) {
+        const uint64_t ab[2] = {static_cast<uint64_t>(static_cast<int64_t>(src[i])), static_cast<uint64_t>(static_cast<int64_t>(dst[i]))};
+        for (uint64_t v : ab) {
+            if (v >= N) continue;
+            if (cnt[v] >= thr) { found.emplace_back(cnt[v], static_cast<int32_t>(v)); cnt[v] = -cnt[v]; }
+        }
+    }
+    for (int64_t i = 0; i < n; i += stride) {                 // the scratch goes back to zero
+        const uint64_t a = static_cast<uint64_t>(static_cast<int64_t>(src[i])), b = static_cast<uint64_t>(static_cast<int64_t>(dst[i]));
+        if (a < N) cnt[a] = 0;
+        if (b < N) cnt[b] = 0;
+    }
+    std::sort(found.begin(), found.end(), [](const std::pair<int32_t, int32_t> &x, const std::pair<int32_t, int32_t> &y) {
+        return x.first != y.first ? x.first > y.first : x.second < y.second;
+    });
+    // every chain warp must be resident next to the ticket warps
+    const int room = std::max(0, h->max_blocks * zebra::kWarpsPerBlock / 2 / std::max(1, h->n_tppr));
+    const int keep = std::min<int>({static_cast<int>(found.size()), h->max_chains, zebra::kMaxChains, room});
+    if (keep > 0) cs.map.assign(N, 0);
+    for (int q = 0; q < keep; ++q) {
+        cs.node[q] = found[static_cast<size_t>(q)].second;
+        cs.map[static_cast<size_t>(cs.node[q])] = static_cast<uint8_t>(q + 1);
+    }
+    cs.n = keep;
 }
 
 // Fills one staging slot for m edges and derives their dependencies (one forward pass and a clean-up
@@ -209,9 +300,12 @@ int ensure_staging(zebra_tppr *h, Staging &s, size_t edges)
 //   flags    kFlagSignal  : this edge's negative read is waited for by a later writer;
 //            kFlagDstFirst: dst is written again sooner than src -> update it first.
 // A negative equal to src or dst is served from the writer's registers.
+// With a non-empty chain set `cs` the pass also marks the endpoints that are chain nodes (kFlagSrcChain /
+// kFlagDstChain), numbers the edges that have one (cidx) and writes, per chain, the step records its
+// resident warp walks.
 template <typename NodeT>
 int fill_soa(zebra_tppr *h, char *host, size_t cap, const NodeT *src, const NodeT *dst, const NodeT *neg,
-             const double *ts, const int64_t *eidx, int64_t m)
+             const double *ts, const int64_t *eidx, int64_t m, const ChainSet *cs = nullptr, ChainBuild *cb = nullptr)
 {
     const int64_t N = h->num_nodes;
     int32_t *o_src = reinterpret_cast<int32_t *>(host);
@@ -219,6 +313,9 @@ int fill_soa(zebra_tppr *h, char *host, size_t cap, const NodeT *src, const Node
     int32_t *p_s = o_e + cap, *p_d = p_s + cap, *p_n = p_d + cap;
     uint32_t *r_s = reinterpret_cast<uint32_t *>(p_n + cap), *r_d = r_s + cap, *flg = r_d + cap;
     double *o_ts = reinterpret_cast<double *>(flg + cap);
+    int32_t *o_cidx = reinterpret_cast<int32_t *>(o_ts + cap);
+    const uint8_t *cmap = (cb && cs && cs->n > 0) ? cs->map.data() : nullptr;
+    if (cb) cb->clear();
     // validate before touching the scratch (one branch-free sweep; the culprit is looked for only on failure)
     const uint64_t uN = static_cast<uint64_t>(N);
     uint64_t bad = 0;
@@ -288,6 +385,25 @@ int fill_soa(zebra_tppr *h, char *host, size_t cap, const NodeT *src, const Node
             da->pad = static_cast<uint32_t>(i) + 1; db->pad = static_cast<uint32_t>(i) + 1;
         } else {
             p_d[i] = -1; r_d[i] = 0;
+        }
+        o_cidx[i] = -1;
+        if (cmap) {
+            const uint8_t ca = cmap[a], cbq = db ? cmap[b] : 0;
+            if (ca | cbq) {
+                const int32_t ci = cb->n_items++;
+                o_cidx[i] = ci;
+                const int32_t ei = static_cast<int32_t>(i), ee = static_cast<int32_t>(eidx[i]);
+                if (ca) {
+                    flg[i] |= zebra::kFlagSrcChain;
+                    cb->steps[ca - 1].push_back(zebra::ChainStep{ei, b, ee, db ? p_d[i] : -1, r_s[i],
+                                                                 (db ? 0u : zebra::kStepLoop) | (cbq ? zebra::kStepPeerChain : 0u), ci, p_s[i], ts[i], 0});
+                }
+                if (cbq) {
+                    flg[i] |= zebra::kFlagDstChain;
+                    cb->steps[cbq - 1].push_back(zebra::ChainStep{ei, a, ee, p_s[i], r_d[i],
+                                                                  zebra::kStepDst | (ca ? zebra::kStepPeerChain : 0u), ci, p_d[i], ts[i], 0});
+                }
+            }
         }
     }
     for (int64_t i = 0; i < m; ++i) {                                 // the scratch goes back to "no writer, no reader"
@@ -473,6 +589,7 @@ int alloc_seq(zebra_tppr *h, int64_t n, cudaStream_t st, uint32_t *base)
             zebra::tppr_retag_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(h->tables[j], h->stride, h->k,
                                                                                                 h->table_rows);
         CU(cudaGetLastError());
+        if (h->cmbox) CU(cudaMemsetAsync(h->cmbox, 0, h->cmbox_cap, st));    // stale mailbox tags could repeat as well
         h->epoch = epoch;
     }
     return 0;
@@ -480,16 +597,16 @@ int alloc_seq(zebra_tppr *h, int64_t n, cudaStream_t st, uint32_t *base)
 
 template <typename NodeT>
 int prepare_chunk(zebra_tppr *h, Staging &s, const NodeT *src, const NodeT *dst, const NodeT *neg, const double *ts,
-                  const int64_t *eidx, int64_t m)
+                  const int64_t *eidx, int64_t m, const ChainSet &cs, ChainBuild &cb)
 {
     const size_t cap = (static_cast<size_t>(m) + 7) & ~static_cast<size_t>(7);   // SoA stride of this launch
-    return fill_soa<NodeT>(h, s.host, cap, src, dst, neg, ts, eidx, m);
+    return fill_soa<NodeT>(h, s.host, cap, src, dst, neg, ts, eidx, m, &cs, &cb);
 }
 
 // Launches the span kernel over m edges whose SoA arrays (stride `cap`) start at `dev`+`lo`.
 int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_t m, int64_t n_total, int64_t i_offset,
                   int32_t rows_per_edge, int32_t inst_mask, char *out, const BatchOut &bo, uint32_t seq0, int64_t tag_offset,
-                  cudaStream_t st, const int32_t *list = nullptr, int64_t n_list = 0)
+                  cudaStream_t st, const int32_t *list = nullptr, int64_t n_list = 0, const ChainLaunch *cl = nullptr)
 {
     zebra::SpanParams p;
     memset(&p, 0, sizeof p);
@@ -510,6 +627,27 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
         p.decay[j] = h->decay[j]; p.decay_len[j] = h->decay_len[j]; p.decay_fixed[j] = h->decay_fixed[j];
     }
     p.out = out; p.ticket = h->ticket; p.status = h->status; p.prof = h->prof;
+    p.wait_ns = h->wait_ns;
+    p.cidx = reinterpret_cast<const int32_t *>(dev + cap * kCidxOffset) + lo;
+    int chain_warps = 0;
+    if (cl && cl->n > 0) {
+        // the mailbox of this launch: one slot per (chain item, instance, side)
+        const size_t need = static_cast<size_t>(std::max(cl->n_items, 1)) * h->n_tppr * 2 * h->stride;
+        if (h->cmbox_cap < need) {
+            CU(cudaStreamSynchronize(st));
+            if (h->cmbox) CU(cudaFree(h->cmbox));
+            h->cmbox = nullptr; h->cmbox_cap = 0;
+            const size_t grow = need + need / 4;
+            CU(cudaMalloc(&h->cmbox, grow));
+            CU(cudaMemsetAsync(h->cmbox, 0, grow, st));
+            h->cmbox_cap = grow;
+        }
+        p.csteps = cl->dev_steps; p.cmbox = h->cmbox; p.cidx_base = cl->cidx_base; p.n_chains = cl->n;
+        for (int q = 0; q < cl->n; ++q) p.chains[q] = zebra::ChainDesc{cl->node[q], cl->begin[q], cl->end[q], 0};
+        chain_warps = cl->n * h->n_tppr;
+        h->chain_items += cl->n_items;
+        for (int q = 0; q < cl->n; ++q) h->chain_steps += cl->end[q] - cl->begin[q];
+    }
     p.batch_size = bo.batch_size; p.first_batch = bo.first_batch; p.out_slots = bo.out_slots; p.slot_bytes = bo.slot_bytes;
     const bool sharded = h->world > 1;
     if (sharded && !list) return fail("node-sharded launch without a work list");
@@ -518,6 +656,11 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
     int blocks = static_cast<int>(std::min<int64_t>((items + zebra::kWarpsPerBlock - 1) / zebra::kWarpsPerBlock,
                                                     sharded ? h->shard_max_blocks : h->max_blocks));
     if (blocks < 1) blocks = 1;
+    if (chain_warps) {
+        // one chain warp per block where the grid allows it; all of them resident in any case
+        blocks = std::max(blocks, std::min(chain_warps, h->max_blocks));
+        if (chain_warps > blocks * zebra::kWarpsPerBlock) return fail("%d chain warps do not fit a grid of %d blocks", chain_warps, blocks);
+    }
     if (sharded) {
         if (m > h->max_window_edges) return fail("sharded launch of %lld edges exceeds the mailbox window (%lld)", (long long)m, (long long)h->max_window_edges);
         const size_t out_off = reinterpret_cast<size_t>(out);   // sharded: dev_out carries a byte OFFSET into the region
@@ -549,15 +692,39 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
     return 0;
 }
 
+// Appends the chain step records of a single-launch staging image right behind its arrays (chain after
+// chain) and describes them for the launch.  Returns the bytes of the image to upload.
+size_t place_chain_steps(const ChainSet &cs, char *host, char *dev, size_t cap, const ChainBuild &cb, ChainLaunch &cl)
+{
+    size_t bytes = cap * kEdgeBytes;
+    cl.n = 0;
+    if (cs.n == 0 || cb.n_items == 0) return bytes;
+    zebra::ChainStep *dst = reinterpret_cast<zebra::ChainStep *>(host + bytes);
+    int32_t pos = 0;
+    cl.n = cs.n;
+    for (int q = 0; q < cs.n; ++q) {
+        cl.node[q] = cs.node[q];
+        cl.begin[q] = pos;
+        if (!cb.steps[q].empty()) memcpy(dst + pos, cb.steps[q].data(), cb.steps[q].size() * sizeof(zebra::ChainStep));
+        pos += static_cast<int32_t>(cb.steps[q].size());
+        cl.end[q] = pos;
+    }
+    cl.dev_steps = reinterpret_cast<const zebra::ChainStep *>(dev + bytes);
+    cl.cidx_base = 0; cl.n_items = cb.n_items;
+    return bytes + static_cast<size_t>(pos) * sizeof(zebra::ChainStep);
+}
+
 int launch_chunk(zebra_tppr *h, Staging &s, int64_t m, int64_t n_total, int64_t i_offset, int32_t rows_per_edge,
-                 int32_t inst_mask, char *out, cudaStream_t st)
+                 int32_t inst_mask, char *out, cudaStream_t st, const ChainSet &cs, const ChainBuild &cb)
 {
     const size_t cap = (static_cast<size_t>(m) + 7) & ~static_cast<size_t>(7);
     uint32_t seq0 = 0;
     if (alloc_seq(h, m, st, &seq0)) return 1;
-    CU(cudaMemcpyAsync(s.dev, s.host, cap * kEdgeBytes, cudaMemcpyHostToDevice, st));
+    ChainLaunch cl;
+    const size_t bytes = place_chain_steps(cs, s.host, s.dev, cap, cb, cl);
+    CU(cudaMemcpyAsync(s.dev, s.host, bytes, cudaMemcpyHostToDevice, st));
     if (i_offset == 0) CU(cudaEventRecord(h->ev0, st));
-    if (launch_kernel(h, s.dev, cap, 0, m, n_total, i_offset, rows_per_edge, inst_mask, out, BatchOut(), seq0, 0, st)) return 1;
+    if (launch_kernel(h, s.dev, cap, 0, m, n_total, i_offset, rows_per_edge, inst_mask, out, BatchOut(), seq0, 0, st, nullptr, 0, &cl)) return 1;
     CU(cudaEventRecord(s.free_ev, st));
     s.pending = true;
     return 0;
@@ -600,14 +767,18 @@ int run_span(zebra_tppr *h, const NodeT *src, const NodeT *dst, const NodeT *neg
     CU(cudaMemsetAsync(h->status + 1, 0, 3 * sizeof(int32_t), st));   // [0] (time-out) is sticky until a reset
     h->last_items = 0;
     if (begin_span(h, st)) return 1;
+    ChainSet cs;
+    detect_chains<NodeT>(h, src, dst, n, cs);
+    h->chain_items = 0; h->chain_steps = 0;
+    ChainBuild cb;
     for (int64_t lo = 0; lo < n; lo += kChunk) {
         const int64_t m = std::min(kChunk, n - lo);
         Staging &s = h->stg[h->stg_next];
         h->stg_next ^= 1;
         if (ensure_staging(h, s, static_cast<size_t>(m) + 8)) return 1;
         if (s.pending) { CU(cudaEventSynchronize(s.free_ev)); s.pending = false; }
-        if (prepare_chunk(h, s, src + lo, dst + lo, neg ? neg + lo : nullptr, ts + lo, eidx + lo, m)) return 1;
-        if (launch_chunk(h, s, m, n, lo, rows_per_edge, inst_mask, out, st)) return 1;
+        if (prepare_chunk(h, s, src + lo, dst + lo, neg ? neg + lo : nullptr, ts + lo, eidx + lo, m, cs, cb)) return 1;
+        if (launch_chunk(h, s, m, n, lo, rows_per_edge, inst_mask, out, st, cs, cb)) return 1;
     }
     CU(cudaEventRecord(h->ev1, st));
     h->timed = true;
@@ -677,6 +848,11 @@ int zebra_tppr_create(zebra_tppr_t **out, int64_t num_nodes, int32_t k, int32_t 
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, zebra::tppr_span_kernel, zebra::kWarpsPerBlock * 32, 0));
     CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
     h->max_blocks = std::max(1, per_sm * sms);
+    if (const char *e = getenv("ZEBRA_CHAINS")) {
+        h->max_chains = std::max(0, std::min(atoi(e), zebra::kMaxChains));
+        h->chains_enabled = h->max_chains > 0;
+    }
+    if (const char *e = getenv("ZEBRA_WAIT_TIMEOUT_MS")) h->wait_ns = static_cast<unsigned long long>(std::max(1, atoi(e))) * 1000000ull;
     *out = h;
     return 0;
 }
@@ -707,6 +883,7 @@ int zebra_tppr_destroy(zebra_tppr_t *h)
     if (h->own_tables)
         for (auto &t : h->tables) if (t) cudaFree(t);
     if (h->rcnt) cudaFree(h->rcnt);
+    if (h->cmbox) cudaFree(h->cmbox);
     for (auto d : h->decay) if (d) cudaFree(d);
     if (h->ticket) cudaFree(h->ticket);
     if (h->status) cudaFree(h->status);
@@ -886,15 +1063,38 @@ int zebra_tppr_plan_create(zebra_tppr_t *h, const int32_t *host_src, const int32
         if (e == cudaSuccess) e = cudaMalloc(&pl->dev_list, std::max<size_t>(list.size(), 1) * sizeof(int32_t));
         if (e == cudaSuccess) e = cudaMemcpy(pl->dev_list, list.data(), list.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
     } else {
-        // staging image of the span
+        // staging image of the span, followed by the step records of its chain nodes (chain after chain)
         std::unique_ptr<char[]> host(new char[pl->cap * kEdgeBytes]);
+        ChainSet cs;
+        ChainBuild cb;
+        detect_chains<int32_t>(h, host_src, host_dst, n, cs);
         if (fill_soa<int32_t>(h, host.get(), pl->cap, host_src, host_dst, rows_per_edge == 3 ? host_neg : nullptr, host_ts,
-                              host_eidx, n)) {
+                              host_eidx, n, &cs, &cb)) {
             delete pl;
             return 1;
         }
-        e = cudaMalloc(&pl->dev, pl->cap * kEdgeBytes);
+        std::vector<zebra::ChainStep> all;
+        if (cs.n > 0 && cb.n_items > 0) {
+            pl->chain_n = cs.n;
+            all.reserve(cb.total());
+            pl->item_edge.assign(static_cast<size_t>(cb.n_items), 0);
+            for (int q = 0; q < cs.n; ++q) {
+                pl->chain_node[q] = cs.node[q];
+                pl->chain_off[q] = static_cast<int32_t>(all.size());
+                pl->chain_edges[q].reserve(cb.steps[q].size());
+                for (const zebra::ChainStep &st : cb.steps[q]) {
+                    pl->chain_edges[q].push_back(st.edge);
+                    pl->item_edge[static_cast<size_t>(st.cidx)] = st.edge;
+                    all.push_back(st);
+                }
+            }
+            pl->chain_off[cs.n] = static_cast<int32_t>(all.size());
+        }
+        pl->steps_bytes = all.size() * sizeof(zebra::ChainStep);
+        e = cudaMalloc(&pl->dev, pl->cap * kEdgeBytes + std::max<size_t>(pl->steps_bytes, 16));
         if (e == cudaSuccess) e = cudaMemcpy(pl->dev, host.get(), pl->cap * kEdgeBytes, cudaMemcpyHostToDevice);
+        if (e == cudaSuccess && pl->steps_bytes)
+            e = cudaMemcpy(pl->dev + pl->cap * kEdgeBytes, all.data(), pl->steps_bytes, cudaMemcpyHostToDevice);
     }
     if (e != cudaSuccess) {
         if (pl->dev) cudaFree(pl->dev);
@@ -968,7 +1168,7 @@ int zebra_debug_host_pass(int64_t num_nodes, int32_t world, int32_t rank, const 
 size_t zebra_tppr_plan_bytes(const zebra_plan_t *pl)
 {
     if (!pl) return 0;
-    return pl->cap * kEdgeBytes + (pl->dev_list ? static_cast<size_t>(pl->batch_ofs.back()) * sizeof(int32_t) : 0);
+    return pl->cap * kEdgeBytes + pl->steps_bytes + (pl->dev_list ? static_cast<size_t>(pl->batch_ofs.back()) * sizeof(int32_t) : 0);
 }
 
 int zebra_tppr_plan_run(zebra_tppr_t *h, zebra_plan_t *pl, int64_t first_batch, int64_t n_batches,
@@ -1000,6 +1200,7 @@ int zebra_tppr_plan_run(zebra_tppr_t *h, zebra_plan_t *pl, int64_t first_batch, 
     bo.slot_bytes = static_cast<int64_t>(zebra_tppr_out_bytes(h, pl->batch_size, pl->rows_per_edge));
     CU(cudaMemsetAsync(h->status + 1, 0, 3 * sizeof(int32_t), st));
     h->last_items = 0;
+    h->chain_items = 0; h->chain_steps = 0;
     CU(cudaEventRecord(h->ev0, st));
     const int64_t last = first_batch + n_batches;
     for (int64_t b = first_batch; b < last; b += batches_per_launch) {
@@ -1013,8 +1214,23 @@ int zebra_tppr_plan_run(zebra_tppr_t *h, zebra_plan_t *pl, int64_t first_batch, 
             list = pl->dev_list + rec0;
             n_list = pl->batch_ofs[static_cast<size_t>(be)] - rec0;
         }
+        ChainLaunch cl;
+        if (pl->chain_n > 0) {
+            // the chain steps and chain items of this launch: sub-ranges of the plan's (ascending) lists
+            cl.n = pl->chain_n;
+            const int32_t lo32 = static_cast<int32_t>(lo), hi32 = static_cast<int32_t>(hi);
+            for (int q = 0; q < pl->chain_n; ++q) {
+                const std::vector<int32_t> &ce = pl->chain_edges[q];
+                cl.node[q] = pl->chain_node[q];
+                cl.begin[q] = pl->chain_off[q] + static_cast<int32_t>(std::lower_bound(ce.begin(), ce.end(), lo32) - ce.begin());
+                cl.end[q] = pl->chain_off[q] + static_cast<int32_t>(std::lower_bound(ce.begin(), ce.end(), hi32) - ce.begin());
+            }
+            cl.dev_steps = reinterpret_cast<const zebra::ChainStep *>(pl->dev + pl->cap * kEdgeBytes);
+            cl.cidx_base = static_cast<int32_t>(std::lower_bound(pl->item_edge.begin(), pl->item_edge.end(), lo32) - pl->item_edge.begin());
+            cl.n_items = static_cast<int32_t>(std::lower_bound(pl->item_edge.begin(), pl->item_edge.end(), hi32) - pl->item_edge.begin()) - cl.cidx_base;
+        }
         if (launch_kernel(h, pl->dev, pl->cap, rec0, hi - lo, pl->n, lo, pl->rows_per_edge, (1 << h->n_tppr) - 1,
-                          static_cast<char *>(dev_out), bo, pl->seq0, lo, st, list, n_list)) {
+                          static_cast<char *>(dev_out), bo, pl->seq0, lo, st, list, n_list, &cl)) {
             h->plan_active = nullptr;          // a failed launch abandons the run
             return 1;
         }
@@ -1056,16 +1272,18 @@ static int epoch_issue(zebra_epoch *ep)
     }
     const size_t cap = (static_cast<size_t>(m) + 7) & ~static_cast<size_t>(7);
     if (fill_soa<int32_t>(h, sl.stg.host, cap, ep->src + lo, ep->dst + lo, ep->neg ? ep->neg + lo : nullptr, ep->ts + lo,
-                          ep->eidx + lo, m)) return 1;
+                          ep->eidx + lo, m, &ep->cs, &ep->cb)) return 1;
     uint32_t seq0 = 0;
     if (alloc_seq(h, m, ep->st, &seq0)) return 1;
-    CU(cudaMemcpyAsync(sl.stg.dev, sl.stg.host, cap * kEdgeBytes, cudaMemcpyHostToDevice, ep->st));
+    ChainLaunch cl;
+    const size_t img_bytes = place_chain_steps(ep->cs, sl.stg.host, sl.stg.dev, cap, ep->cb, cl);
+    CU(cudaMemcpyAsync(sl.stg.dev, sl.stg.host, img_bytes, cudaMemcpyHostToDevice, ep->st));
     if (w == 0) CU(cudaEventRecord(h->ev0, ep->st));
     BatchOut bo;
     bo.batch_size = ep->batch_size; bo.first_batch = b0; bo.out_slots = ep->window;
     bo.slot_bytes = static_cast<int64_t>(ep->slot_bytes);
     if (launch_kernel(h, sl.stg.dev, cap, 0, m, ep->n, lo, ep->rows_per_edge, (1 << h->n_tppr) - 1, sl.out_dev, bo, seq0, 0,
-                      ep->st)) return 1;
+                      ep->st, nullptr, 0, &cl)) return 1;
     CU(cudaEventRecord(sl.ev_kernel, ep->st));
     if (ep->rows_per_edge) {
         CU(cudaStreamWaitEvent(h->copy_stream, sl.ev_kernel, 0));
@@ -1108,6 +1326,8 @@ int zebra_tppr_epoch_begin(zebra_tppr_t *h, const int32_t *host_src, const int32
     ep->n_windows = (ep->n_batches + ep->window - 1) / ep->window;
     ep->slot_bytes = zebra_tppr_out_bytes(h, batch_size, rows_per_edge);
     ep->st = static_cast<cudaStream_t>(stream);
+    detect_chains<int32_t>(h, host_src, host_dst, n, ep->cs);
+    h->chain_items = 0; h->chain_steps = 0;
     CU(cudaMemsetAsync(h->status + 1, 0, 3 * sizeof(int32_t), ep->st));
     h->last_items = 0;
     if (begin_span(h, ep->st)) { delete ep; return 1; }
@@ -1303,7 +1523,7 @@ int zebra_tppr_counters(zebra_tppr_t *h, int64_t *out8)
     if (!h || !out8) return fail("null argument");
     for (int q = 0; q < 8; ++q) out8[q] = 0;
     out8[0] = h->last_items; out8[1] = h->last_ties; out8[2] = h->launches; out8[3] = h->timeouts;
-    out8[4] = h->last_merge;
+    out8[4] = h->last_merge; out8[5] = h->chain_items; out8[6] = h->chain_steps;
     return 0;
 }
 

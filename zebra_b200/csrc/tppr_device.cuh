@@ -42,7 +42,35 @@ constexpr uint32_t kNear = 192;          // edges: closer than this to our turn 
 //                B[k] {f64 ts, i32 node, u32 tag} | pad to 128 B
 __host__ __device__ inline size_t record_stride(int k) { return (static_cast<size_t>(32) * k + 16 + 127) / 128 * 128; }
 
-enum : uint32_t { kFlagSignal = 1u, kFlagDstFirst = 2u };
+enum : uint32_t { kFlagSignal = 1u, kFlagDstFirst = 2u,
+                  kFlagSrcChain = 4u, kFlagDstChain = 8u };   // that endpoint is updated by a resident chain warp
+
+// ---- hub chains -------------------------------------------------------------------------------
+// A node with many edges in one launch serialises them through its vector: every update needs the
+// previous one (the top-k prune is a non-linear recurrence).  With one warp per work item that chain
+// pays, per step, an L2 round trip (writer's stores -> next reader's loads) plus the update of BOTH
+// endpoints.  The host therefore marks the hottest nodes of a span as CHAIN nodes; each (chain node,
+// instance) gets a resident warp that walks the node's edges in order with the vector in REGISTERS and
+// computes only that node's side.  Everything else of such an edge (the partner's update, the three
+// output rows) stays with the ordinary ticket warp, which receives the chain node's OLD vector through
+// a launch-local mailbox slot (tagged 16-byte chunks, pushed from the chain warp's registers before it
+// computes).  Every version is still published to the node's table record, so negative-sample readers
+// and later launches see exactly what they saw before.
+constexpr int kMaxChains = 24;
+struct alignas(16) ChainStep {
+    int32_t edge;        // index of the edge in the span the tags are drawn from (tag = seq0 + edge)
+    int32_t peer;        // the other endpoint
+    int32_t eidx;
+    int32_t prev_peer;   // previous writer of the peer (span index), -1 = none
+    uint32_t rthr;       // negative reads of the version this step overwrites
+    uint32_t flags;      // kStepDst | kStepLoop | kStepPeerChain
+    int32_t cidx;        // chain item index of the edge (mailbox slot = cidx - cidx_base)
+    int32_t prev_self;   // previous writer of the chain node itself (used by the first step of a launch)
+    double ts;
+    int64_t pad;
+};
+enum : uint32_t { kStepDst = 1u, kStepLoop = 2u, kStepPeerChain = 4u };
+struct ChainDesc { int32_t node, begin, end, pad; };   // steps [begin, end) of SpanParams::csteps
 
 // The norm of a node depends only on how many updates it has seen (norm <- norm*beta + beta,
 // utils/util.py:522,574), so the factors of its next update are tabulated per update count instead
@@ -104,6 +132,13 @@ struct SpanParams {
     int64_t mbox_half_bytes;                        // bytes of one parity half of a mailbox
     char *mbox_peer[kMaxRanks];                     // every rank's mailbox (peer-mapped), own included
     char *out_peer[kMaxRanks];                      // every rank's output region (peer-mapped), own included
+    // hub chains (single-GPU kernel)
+    const int32_t *cidx;                            // per launch-local edge: chain item index, -1 = no chain endpoint
+    const ChainStep *csteps;
+    char *cmbox;                                    // [(cidx - cidx_base) * n_tppr + j][2 sides] records
+    int32_t cidx_base, n_chains;
+    unsigned long long wait_ns;                     // dependency-wait time-out (globaltimer)
+    ChainDesc chains[kMaxChains];
 };
 
 constexpr int kKeySlotBits = 11, kKeySlots = 1 << kKeySlotBits;
@@ -115,6 +150,7 @@ __device__ __forceinline__ unsigned key_slot(int e, int n)
 
 struct alignas(16) WarpScratch {
     unsigned long long V[64];   // candidate scores by candidate index (fp64 bit patterns in integer order)
+    unsigned long long NK[32], NT[32], NS[32];   // chain warps: the new vector by slot (key, ts, score)
     unsigned long long K[32];   // peer keys of the duplicate scan
     // exact-tie path: numba's quicksort is replayed on (rank << 8 | candidate) items, the rank (number
     // of strictly smaller scores) being an order-isomorphic 6-bit stand-in for the fp64 score
@@ -185,24 +221,73 @@ __device__ __forceinline__ int32_t ld_relaxed_s32(const int32_t *p)
     return v;
 }
 
+__device__ __forceinline__ unsigned long long gtime()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// Bounded waiting: every 256 polls look at the abort flag and at the clock.  The limit is wall time
+// (SpanParams::wait_ns, ZEBRA_WAIT_TIMEOUT_MS), not a poll count: a peer GPU that launches late or a
+// long producer chain must not be mistaken for a dead-lock.
+struct Waiter {
+    unsigned spins = 0;
+    unsigned long long t0 = 0;
+    __device__ __forceinline__ bool expired(const int32_t *status, unsigned long long limit)
+    {
+        if ((++spins & 0xff) != 0) return false;
+        if (*reinterpret_cast<const volatile int32_t *>(status) != 0) return true;
+        const unsigned long long now = gtime();
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > limit) { atomicExch(const_cast<int32_t *>(status), 1); return true; }
+        return false;
+    }
+};
+
 // One attempt to read a whole record.  `any`: the record has no writer earlier in this span, so it
 // is stable and any self-consistent content is the wanted version; otherwise every chunk must carry
 // `expect`.  `cur` returns the header tag seen (progress estimate for the back-off).
+struct RawRec { uint4 h, a, b; };   // header and this lane's two chunks, as loaded
+
+template <bool kSys = false>
+__device__ __forceinline__ RawRec load_raw(const char *rec, int k, int lane)
+{
+    const int l = lane < k ? lane : k - 1;
+    RawRec r;
+    r.h = ld_chunk<kSys>(rec);
+    r.a = ld_chunk<kSys>(rec + 16 + 16 * l);
+    r.b = ld_chunk<kSys>(rec + 16 + 16 * (k + l));
+    return r;
+}
+
+__device__ __forceinline__ bool check_raw(const RawRec &r, int lane, bool any, uint32_t expect, VecR &v, uint32_t &cur)
+{
+    cur = r.h.w;
+    const uint32_t want = any ? r.h.w : expect;
+    const int cnt = static_cast<int>(r.h.z & ((1u << kCountBits) - 1));
+    const bool ok = r.h.w == want && (lane >= cnt || (r.a.w == want && r.b.w == want));
+    v.sc = chunk_f64(r.a); v.e = static_cast<int>(r.a.z);
+    v.ts = chunk_f64(r.b); v.n = static_cast<int>(r.b.z);
+    v.norm = chunk_f64(r.h); v.cnt = cnt; v.upd = static_cast<int>(r.h.z >> kCountBits);
+    return __all_sync(kFull, ok);
+}
+
 template <bool kSys = false>
 __device__ __forceinline__ bool try_load(const char *rec, int k, int lane, bool any, uint32_t expect, VecR &v, uint32_t &cur)
 {
-    const int l = lane < k ? lane : k - 1;
-    const uint4 h = ld_chunk<kSys>(rec);
-    const uint4 a = ld_chunk<kSys>(rec + 16 + 16 * l);
-    const uint4 b = ld_chunk<kSys>(rec + 16 + 16 * (k + l));
-    cur = h.w;
-    const uint32_t want = any ? h.w : expect;
-    const int cnt = static_cast<int>(h.z & ((1u << kCountBits) - 1));
-    const bool ok = h.w == want && (lane >= cnt || (a.w == want && b.w == want));
-    v.sc = chunk_f64(a); v.e = static_cast<int>(a.z);
-    v.ts = chunk_f64(b); v.n = static_cast<int>(b.z);
-    v.norm = chunk_f64(h); v.cnt = cnt; v.upd = static_cast<int>(h.z >> kCountBits);
-    return __all_sync(kFull, ok);
+    return check_raw(load_raw<kSys>(rec, k, lane), lane, any, expect, v, cur);
+}
+
+// Copy of a vector held in registers into a mailbox slot (a peer GPU's: kSys; a chain item's: gpu scope).
+template <bool kSys>
+__device__ __forceinline__ void push_vector(char *slot, int k, const VecR &v, uint32_t tag, int lane)
+{
+    if (lane == 0) st_chunk_t<kSys>(slot, v.norm, v.cnt | (v.upd << kCountBits), tag);
+    if (lane < v.cnt) {
+        st_chunk_t<kSys>(slot + 16 + 16 * lane, v.sc, v.e, tag);
+        st_chunk_t<kSys>(slot + 16 + 16 * (k + lane), v.ts, v.n, tag);
+    }
 }
 
 __device__ __forceinline__ uint32_t ld_tag(const char *rec) { return ld_chunk(rec).w; }
@@ -379,9 +464,12 @@ __device__ __forceinline__ void st_entry(char *rec, int k, int pos, int e, int n
 // `rwait` > 0: that many negative-sample reads of the old version must have finished first.
 // This function is the step of every hub's dependency chain: it is written for the latency of a
 // single warp (independent shared-memory loads, unrolled compare loops), not for throughput.
+// kKeep (chain warps): the new vector is also returned in registers, in slot order, through `newv`.
+template <bool kKeep = false>
 __device__ __forceinline__ bool update_endpoint(const SpanParams &p, WarpScratch &s, const VecR &A, const VecR &B,
                                                 int peer_id, int e_new, double t_new, int j,
-                                                char *rec, uint32_t tag, int32_t *rcnt, uint32_t rwait, int lane)
+                                                char *rec, uint32_t tag, int32_t *rcnt, uint32_t rwait, int lane,
+                                                VecR *newv = nullptr)
 {
     ZP_DECL;
     const int k = p.k;
@@ -580,11 +668,9 @@ __device__ __forceinline__ bool update_endpoint(const SpanParams &p, WarpScratch
     // ---- the version being overwritten may still have negative-sample readers ----
     bool ok = true;
     if (rwait != 0) {
-        unsigned spins = 0;
+        Waiter w;
         while (ld_relaxed_s32(rcnt) < static_cast<int32_t>(rwait)) {
-            if ((++spins & 0xff) == 0) {
-                if (*reinterpret_cast<volatile int32_t *>(p.status) != 0 || spins > (1u << 21)) { ok = false; break; }
-            }
+            if (w.expired(p.status, p.wait_ns)) { ok = false; break; }
             __nanosleep(64);
         }
         if (lane == 0) atomicSub(rcnt, static_cast<int32_t>(rwait));
@@ -594,6 +680,24 @@ __device__ __forceinline__ bool update_endpoint(const SpanParams &p, WarpScratch
     if (lane == 0) st_chunk(rec, new_norm, n | (upd << kCountBits), tag);
     if (keep0) st_entry(rec, k, pos0, A.e, A.n, A.ts, vA, tag);
     if (keep1) st_entry(rec, k, pos1, e1, n1, ts1, v1, tag);
+    if (kKeep) {
+        // the chain warp carries the new vector in registers: scatter by slot, read back by lane
+        __syncwarp();
+        if (keep0) {
+            s.NK[pos0] = keyA; s.NT[pos0] = static_cast<unsigned long long>(__double_as_longlong(A.ts));
+            s.NS[pos0] = static_cast<unsigned long long>(__double_as_longlong(vA));
+        }
+        if (keep1) {
+            s.NK[pos1] = pack_key(e1, n1); s.NT[pos1] = static_cast<unsigned long long>(__double_as_longlong(ts1));
+            s.NS[pos1] = static_cast<unsigned long long>(__double_as_longlong(v1));
+        }
+        __syncwarp();
+        const unsigned long long kk = s.NK[lane];
+        newv->e = static_cast<int>(kk >> 32); newv->n = static_cast<int>(kk & 0xffffffffu);
+        newv->ts = __longlong_as_double(static_cast<long long>(s.NT[lane]));
+        newv->sc = __longlong_as_double(static_cast<long long>(s.NS[lane]));
+        newv->cnt = n; newv->upd = upd; newv->norm = new_norm;
+    }
     ZP_MARK(12);
     return ok;
 }
@@ -612,7 +716,110 @@ __device__ __forceinline__ unsigned backoff_ns(uint32_t dist)
     return ns > 4000u ? 4000u : ns;
 }
 
-__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+__device__ __forceinline__ char *chain_slot(const SpanParams &p, int32_t cidx, int j, int side)
+{
+    return p.cmbox + ((static_cast<size_t>(cidx - p.cidx_base) * p.n_tppr + j) * 2 + side) * p.stride;
+}
+
+// word w (0..11) of a 48-byte chain step record sits in lane w; fields are broadcast on demand
+__device__ __forceinline__ uint32_t load_step_word(const ChainStep *st, int lane)
+{
+    return lane < 12 ? __ldg(reinterpret_cast<const uint32_t *>(st) + lane) : 0u;
+}
+
+// The resident warp of chain `q`, instance `j`: walks the node's edges of this launch in order with the
+// node's vector in registers (no L2 hand-off between consecutive edges of a hub) and computes only that
+// node's side of each edge (utils/util.py:509-559).  Per step: take the partner's OLD vector (its table
+// record, tagged by its previous writer; for a partner that is itself a chain node, the mailbox slot its
+// chain warp pushes), push the own OLD vector into the item's mailbox slot for the ticket warp that does
+// the rest of the edge, update, publish the new version to the table record.  The next partner's record
+// is loaded into registers before the update, so that its latency overlaps the update.
+__device__ __noinline__ void run_chain(const SpanParams &p, WarpScratch &s, int q, int j, int lane)
+{
+    const ChainDesc c = p.chains[q];
+    if (c.begin >= c.end) return;
+    const int k = p.k;
+    char *table = p.tables[j];
+    char *recH = table + static_cast<size_t>(c.node) * p.stride;
+    int32_t *rcntH = p.rcnt[j] + c.node;
+    const ChainStep *steps = p.csteps;
+    uint32_t w0 = load_step_word(steps + c.begin, lane);
+    uint32_t w1 = c.begin + 1 < c.end ? load_step_word(steps + c.begin + 1, lane) : 0u;
+    VecR H;
+    {
+        const int32_t prev_self = static_cast<int32_t>(__shfl_sync(kFull, w0, 7));
+        uint32_t cur;
+        Waiter wt;
+        while (!try_load(recH, k, lane, prev_self < 0, p.seq0 + static_cast<uint32_t>(prev_self), H, cur)) {
+            if (wt.expired(p.status, p.wait_ns)) return;
+            __nanosleep(100);
+        }
+    }
+    // the first partner record (later ones are loaded one step ahead)
+    RawRec raw;
+    {
+        const uint32_t fl = __shfl_sync(kFull, w0, 5);
+        const int peer = static_cast<int>(__shfl_sync(kFull, w0, 1));
+        raw = load_raw(table + static_cast<size_t>((fl & (kStepLoop | kStepPeerChain)) ? c.node : peer) * p.stride, k, lane);
+    }
+    for (int x = c.begin; x < c.end; ++x) {
+        const uint32_t w2 = x + 2 < c.end ? load_step_word(steps + x + 2, lane) : 0u;   // used two steps from now
+        const int32_t edge = static_cast<int32_t>(__shfl_sync(kFull, w0, 0));
+        const int peer = static_cast<int>(__shfl_sync(kFull, w0, 1));
+        const int e_new = static_cast<int>(__shfl_sync(kFull, w0, 2));
+        const int32_t prev_peer = static_cast<int32_t>(__shfl_sync(kFull, w0, 3));
+        const uint32_t rthr = __shfl_sync(kFull, w0, 4);
+        const uint32_t fl = __shfl_sync(kFull, w0, 5);
+        const int32_t cidx = static_cast<int32_t>(__shfl_sync(kFull, w0, 6));
+        const double t_new = __hiloint2double(static_cast<int>(__shfl_sync(kFull, w0, 9)), static_cast<int>(__shfl_sync(kFull, w0, 8)));
+        const uint32_t tag = p.seq0 + static_cast<uint32_t>(edge);
+        const int side = static_cast<int>(fl & kStepDst);
+        char *my_slot = chain_slot(p, cidx, j, side);
+        VecR B;
+        bool alive = true;
+        if (fl & kStepLoop) {
+            B = vsel(true, H, H);
+            push_vector<false>(my_slot, k, H, tag, lane);
+        } else if (fl & kStepPeerChain) {
+            // both endpoints are chain nodes: each chain warp pushes first, then takes the other's push
+            push_vector<false>(my_slot, k, H, tag, lane);
+            const char *other = chain_slot(p, cidx, j, side ^ 1);
+            uint32_t cur;
+            Waiter wt;
+            while (!try_load(other, k, lane, false, tag, B, cur)) {
+                if (wt.expired(p.status, p.wait_ns)) { alive = false; break; }
+                __nanosleep(40);
+            }
+        } else {
+            const char *recP = table + static_cast<size_t>(peer) * p.stride;
+            const uint32_t expect = p.seq0 + static_cast<uint32_t>(prev_peer);
+            uint32_t cur;
+            bool ok = check_raw(raw, lane, prev_peer < 0, expect, B, cur);
+            Waiter wt;
+            while (!ok) {
+                if (wt.expired(p.status, p.wait_ns)) { alive = false; break; }
+                __nanosleep(40);
+                ok = try_load(recP, k, lane, prev_peer < 0, expect, B, cur);
+            }
+            // only now: the ticket warp overwrites the partner's record as soon as it has our old vector
+            if (alive) push_vector<false>(my_slot, k, H, tag, lane);
+        }
+        if (!alive) return;
+        // next step's partner record on its way while this step computes
+        if (x + 1 < c.end) {
+            const uint32_t nfl = __shfl_sync(kFull, w1, 5);
+            const int npeer = static_cast<int>(__shfl_sync(kFull, w1, 1));
+            raw = load_raw(table + static_cast<size_t>((nfl & (kStepLoop | kStepPeerChain)) ? c.node : npeer) * p.stride, k, lane);
+        }
+        VecR Hn;
+        const bool ok = update_endpoint<true>(p, s, H, B, peer, e_new, t_new, j, recH, tag, rcntH, rthr, lane, &Hn);
+        if (!ok) { atomicExch(p.status, 1); return; }
+        H = Hn;
+        w0 = w1; w1 = w2;
+    }
+}
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, 2)
 tppr_span_kernel(const __grid_constant__ SpanParams p)
 {
     __shared__ WarpScratch scratch[kWarpsPerBlock];
@@ -622,6 +829,15 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
     const unsigned long long total = static_cast<unsigned long long>(p.n_chunk) * p.n_tppr;
     const int k = p.k;
     const uint32_t tag_base = p.seq0 + static_cast<uint32_t>(p.tag_offset);   // tag of launch-local edge 0
+
+    // resident chain warps first (warp 0 of the first blocks, then warp 1, ...: spread over the SMs)
+    if (p.n_chains > 0) {
+        const unsigned cw = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
+        if (cw < static_cast<unsigned>(p.n_chains * p.n_tppr)) {
+            const int q = cw / p.n_tppr, j = cw - q * p.n_tppr;
+            if ((p.inst_mask >> j) & 1) run_chain(p, s, q, j, lane);
+        }
+    }
 
     for (;;) {
         uint32_t tk = 0;
@@ -640,6 +856,8 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
         int32_t *rcnt = p.rcnt[j];
 
         if (!((p.inst_mask >> j) & 1)) continue;   // instance not selected: its tables are not touched
+        // update-only span and every side of the edge belongs to a chain warp: nothing to do here
+        if (p.rows_per_edge == 0 && (flags & kFlagSrcChain) && (loop || (flags & kFlagDstChain))) continue;
 
         const int32_t pS = p.prev_s[i], pD = loop ? -1 : p.prev_d[i], pG = neg_own ? p.prev_n[i] : -1;
         char *table = p.tables[j];
@@ -651,24 +869,36 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
         const double t = p.ts[i];
         const int e = p.eidx[i];
         const uint32_t rwS = p.rthr_s[i], rwD = loop ? 0u : p.rthr_d[i];
+        // an endpoint that is a chain node: its OLD vector arrives in the item's mailbox slot, tagged with
+        // this edge, and its update is the chain warp's business
+        const bool cS = (flags & kFlagSrcChain) != 0, cD = !loop && (flags & kFlagDstChain) != 0;
+        const char *srcS = recS, *srcD = recD;
+        uint32_t expS = p.seq0 + static_cast<uint32_t>(pS), expD = p.seq0 + static_cast<uint32_t>(pD);
+        bool anyS = pS < 0, anyD = pD < 0;
+        if (cS | cD) {
+            const int32_t ci = p.cidx[i];
+            if (cS) { srcS = chain_slot(p, ci, j, 0); expS = my_tag; anyS = false; }
+            if (cD) { srcD = chain_slot(p, ci, j, 1); expD = my_tag; anyD = false; }
+        }
 
         // ---- read the three vectors; wait for the producers of src and dst (the chain) ----
         VecR S, D, G;
         uint32_t curS = 0, curD = 0, curG = 0;
-        bool okS = try_load(recS, k, lane, pS < 0, p.seq0 + static_cast<uint32_t>(pS), S, curS);
-        bool okD = loop ? true : try_load(recD, k, lane, pD < 0, p.seq0 + static_cast<uint32_t>(pD), D, curD);
+        bool okS = try_load(srcS, k, lane, anyS, expS, S, curS);
+        bool okD = loop ? true : try_load(srcD, k, lane, anyD, expD, D, curD);
         bool okG = neg_own ? try_load(recG, k, lane, pG < 0, p.seq0 + static_cast<uint32_t>(pG), G, curG) : true;
         bool alive = true;
-        unsigned spins = 0;
+        Waiter wt;
+        unsigned nap = 64;
         ZP_MARK(0);
         while (!(okS && okD)) {
-            // distance (in edges) of the farther unsatisfied producer from the version visible now
+            // distance (in edges) of the farther unsatisfied table producer from the version visible now
             uint32_t dist = 0;
-            if (!okS) {
+            if (!okS && !cS) {
                 const uint32_t d = curS - tag_base, pe = static_cast<uint32_t>(pS - p.tag_offset);
                 dist = (d < static_cast<uint32_t>(p.n_chunk) && d <= pe) ? pe - d : pe + 1;
             }
-            if (!okD) {
+            if (!okD && !cD) {
                 const uint32_t d = curD - tag_base, pe = static_cast<uint32_t>(pD - p.tag_offset);
                 const uint32_t dd = (d < static_cast<uint32_t>(p.n_chunk) && d <= pe) ? pe - d : pe + 1;
                 dist = dd > dist ? dd : dist;
@@ -676,25 +906,30 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
             if (dist > kNear) {
                 // far from our turn: sleep, then look at the header tags only
                 __nanosleep(backoff_ns(dist));
-                if (!okS) curS = ld_tag(recS);
-                if (!okD) curD = ld_tag(recD);
-                const bool nearS = okS || curS == p.seq0 + static_cast<uint32_t>(pS);
-                const bool nearD = okD || curD == p.seq0 + static_cast<uint32_t>(pD);
+                if (!okS && !cS) curS = ld_tag(recS);
+                if (!okD && !cD) curD = ld_tag(recD);
+                const bool nearS = okS || cS || curS == expS;
+                const bool nearD = okD || cD || curD == expD;
                 if (!(nearS && nearD)) {
-                    if ((++spins & 0xff) == 0) {
-                        if (*reinterpret_cast<volatile int32_t *>(p.status) != 0) { alive = false; break; }
-                        if (spins > (1u << 20)) { atomicExch(p.status, 1); alive = false; break; }
-                    }
+                    if (wt.expired(p.status, p.wait_ns)) { alive = false; break; }
+                    continue;
+                }
+            } else if ((!okS && cS) || (!okD && cD)) {
+                // waiting for a chain warp to reach this edge: off the chain, so poll the slot header
+                // only, a little less often each time
+                __nanosleep(nap);
+                if (nap < 2048) nap <<= 1;
+                const bool hS = okS || !cS || ld_tag(srcS) == my_tag;
+                const bool hD = okD || !cD || ld_tag(srcD) == my_tag;
+                if (!(hS && hD)) {
+                    if (wt.expired(p.status, p.wait_ns)) { alive = false; break; }
                     continue;
                 }
             }
-            if (!okS) okS = try_load(recS, k, lane, false, p.seq0 + static_cast<uint32_t>(pS), S, curS);
-            if (!okD) okD = try_load(recD, k, lane, false, p.seq0 + static_cast<uint32_t>(pD), D, curD);
+            if (!okS) okS = try_load(srcS, k, lane, false, expS, S, curS);
+            if (!okD) okD = try_load(srcD, k, lane, false, expD, D, curD);
             if (!okG) okG = try_load(recG, k, lane, false, p.seq0 + static_cast<uint32_t>(pG), G, curG);
-            if ((++spins & 0xff) == 0) {
-                if (*reinterpret_cast<volatile int32_t *>(p.status) != 0) { alive = false; break; }
-                if (spins > (1u << 22)) { atomicExch(p.status, 1); alive = false; break; }
-            }
+            if (wt.expired(p.status, p.wait_ns)) { alive = false; break; }
         }
         if (!alive) continue;
         ZP_MARK(1);
@@ -710,6 +945,7 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
 #pragma unroll 1
         for (int h = 0; h < (loop ? 1 : 2); ++h) {
             const bool isD = (h == 0) ? df : !df;
+            if (isD ? cD : cS) continue;            // a chain node's side is computed by its chain warp
             const VecR A = vsel(isD, D, S), B = vsel(isD, S, D);
             ok &= update_endpoint(p, s, A, B, isD ? sN : dN, e, t, j, isD ? recD : recS, my_tag,
                                   rcnt + (isD ? dN : sN), isD ? rwD : rwS, lane);
@@ -721,10 +957,7 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
         while (!okG) {
             __nanosleep(64);
             okG = try_load(recG, k, lane, false, p.seq0 + static_cast<uint32_t>(pG), G, curG);
-            if ((++spins & 0xff) == 0) {
-                if (*reinterpret_cast<volatile int32_t *>(p.status) != 0) break;
-                if (spins > (1u << 22)) { atomicExch(p.status, 1); break; }
-            }
+            if (wt.expired(p.status, p.wait_ns)) break;
         }
         if (!okG) continue;
         if (!sigG && neg_own && (flags & kFlagSignal) && lane == 0) atomicAdd(rcnt + gN, 1);

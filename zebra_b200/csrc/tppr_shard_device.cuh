@@ -31,16 +31,6 @@
 
 namespace zebra {
 
-// Copy of a vector held in registers into a mailbox slot of a peer (or of this rank, world = 1 tests).
-__device__ __forceinline__ void push_vector(char *slot, int k, const VecR &v, uint32_t tag, int lane)
-{
-    if (lane == 0) st_chunk_t<true>(slot, v.norm, v.cnt | (v.upd << kCountBits), tag);
-    if (lane < v.cnt) {
-        st_chunk_t<true>(slot + 16 + 16 * lane, v.sc, v.e, tag);
-        st_chunk_t<true>(slot + 16 + 16 * (k + lane), v.ts, v.n, tag);
-    }
-}
-
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
 {
@@ -102,7 +92,7 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
         uint32_t curS = 0, curD = 0, curG = 0;
         bool okS = !needSD, okD = !needSD || loop, okG = !oG;
         bool pushed = !cross, alive = true;
-        unsigned spins = 0;
+        Waiter wt;
         for (;;) {
             if (!okS) okS = oS ? try_load<false>(recS, k, lane, pS < 0, p.seq0 + static_cast<uint32_t>(pS), S, curS)
                                : try_load<true>(mslot, k, lane, false, my_tag, S, curS);
@@ -110,7 +100,7 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
                                : try_load<true>(mslot, k, lane, false, my_tag, D, curD);
             if (!okG) okG = try_load<false>(recG, k, lane, pG < 0, p.seq0 + static_cast<uint32_t>(pG), G, curG);
             if (!pushed && (oS ? okS : okD)) {      // our endpoint's OLD vector is here: send it before computing
-                push_vector(pslot, k, oS ? S : D, my_tag, lane);
+                push_vector<true>(pslot, k, oS ? S : D, my_tag, lane);
                 pushed = true;
             }
             if (okS && okD) break;
@@ -127,10 +117,7 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
             }
             if (dist > kNear) __nanosleep(backoff_ns(dist));
             else if ((!okS && !oS) || (!okD && !oD)) __nanosleep(100);   // waiting for a peer's push
-            if ((++spins & 0xff) == 0) {
-                if (*reinterpret_cast<volatile int32_t *>(p.status) != 0) { alive = false; break; }
-                if (spins > (1u << 22)) { atomicExch(p.status, 1); alive = false; break; }
-            }
+            if (wt.expired(p.status, p.wait_ns)) { alive = false; break; }
         }
         if (!alive) continue;
         if (loop) D = vsel(true, S, S);
@@ -155,10 +142,7 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
         while (!okG) {
             __nanosleep(64);
             okG = try_load<false>(recG, k, lane, pG < 0, p.seq0 + static_cast<uint32_t>(pG), G, curG);
-            if ((++spins & 0xff) == 0) {
-                if (*reinterpret_cast<volatile int32_t *>(p.status) != 0) break;
-                if (spins > (1u << 22)) { atomicExch(p.status, 1); break; }
-            }
+            if (wt.expired(p.status, p.wait_ns)) break;
         }
         if (!okG) continue;
         if (!sigG && oG && (flags & kFlagSignal) && lane == 0) atomicAdd(rcnt + gN, 1);

@@ -257,7 +257,7 @@ class tppr_finder:  # noqa: N801  (name kept from the reference)
         o = np.zeros(8, np.int64)
         check(self._L.zebra_tppr_counters(self._h, _ptr(o)))
         return {"items": int(o[0]), "tie_prunes": int(o[1]), "launches": int(o[2]), "timeouts": int(o[3]),
-                "merge_ranked": int(o[4])}
+                "merge_ranked": int(o[4]), "chain_items": int(o[5]), "chain_steps": int(o[6])}
 
     def profile(self):
         o = np.zeros(16, np.uint64)

@@ -163,7 +163,7 @@ class ShardedFinder:
         o = np.zeros(8, np.int64)
         self._check(self._L.zebra_tppr_counters(self._h, _ptr(o)))
         return {"items": int(o[0]), "tie_prunes": int(o[1]), "launches": int(o[2]), "timeouts": int(o[3]),
-                "merge_ranked": int(o[4])}
+                "merge_ranked": int(o[4]), "chain_items": int(o[5]), "chain_steps": int(o[6])}
 
     def last_kernel_ms(self):
         return float(self._L.zebra_tppr_last_kernel_ms(self._h))
