@@ -112,9 +112,19 @@ int zebra_tppr_plan_create(zebra_tppr_t *h, const int32_t *host_src, const int32
                            int64_t n, int32_t rows_per_edge, int64_t batch_size, zebra_plan_t **out);
 int zebra_tppr_plan_destroy(zebra_plan_t *plan);
 int64_t zebra_tppr_plan_batches(const zebra_plan_t *plan);
-/* Bytes the plan uploaded and keeps in HBM: 48 per staged edge record (on a node-sharded handle only
- * the edges this rank takes part in are staged, plus 4 per entry of its work list). */
+/* Bytes the plan uploaded and keeps in HBM: 52 per staged edge record plus 48 per step of a chain node
+ * (on a node-sharded handle only the edges this rank takes part in are staged, plus 4 per entry of its
+ * work list). */
 size_t zebra_tppr_plan_bytes(const zebra_plan_t *plan);
+/* Test / debug hook: copies the raw record of `node` in instance `inst` (zebra_tppr_record_bytes bytes:
+ * header chunk and 2k entry chunks, each ending in its 32-bit tag) to host memory.  Synchronous. */
+int zebra_debug_read_record(zebra_tppr_t *h, int32_t inst, int64_t node, void *host_out);
+/* Test hook (GPU): the prune's exact-tie ordering in isolation.  host_values holds n_cases rows of
+ * `stride` (>= 64) int32, row c uses its first host_n[c] (2..63) entries as stand-ins for scores; on return
+ * host_ranks[c*stride + i] is the position of candidate i in numba's np.argsort of that row (reference:
+ * utils/util.py:555 through numba.misc.quicksort). */
+int zebra_debug_tie_order(const int32_t *host_values, const int32_t *host_n, int32_t n_cases, int32_t stride,
+                          int32_t *host_ranks);
 int zebra_tppr_plan_run(zebra_tppr_t *h, zebra_plan_t *plan, int64_t first_batch, int64_t n_batches,
                         int64_t batches_per_launch, void *dev_out, int64_t out_slots, void *stream);
 

@@ -75,7 +75,7 @@ def star(n_edges=100000, n_nodes=200000, pool=None, insts=((1, [0.1], [0.5]), (1
         ms = f.last_kernel_ms()
         pr = f.profile()
         if pr.any():
-            names = ["claim+load", "wait", "upd_hot", "upd_2nd", "emit", "", "", "", "u.dup", "u.pos", "u.rank", "u.tie", "u.store"]
+            names = ["claim+load", "wait", "upd_hot", "upd_2nd", "emit", "c.get+push", "c.prefetch", "c.update", "u.dup", "u.pos", "u.rank", "u.tie", "u.store"]
             print("   cycles/item:", {nm: round(float(v) / (n_edges * n_t), 1) for nm, v in zip(names, pr) if nm})
         print(f"star chain pool={pool} n_tppr={n_t} beta={be}: {ms*1e3/n_edges:.2f} us per hub step ({n_edges/ms/1e3:.2f} M edges/s) {f.counters()}", flush=True)
 

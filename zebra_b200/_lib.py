@@ -26,6 +26,8 @@ SIGNATURES = {
     "zebra_tppr_plan_batches": (_I64, [_VP]),
     "zebra_tppr_plan_bytes": (C.c_size_t, [_VP]),
     "zebra_debug_host_pass": (C.c_int, [_I64, _I32, _I32, _VP, _VP, _VP, _VP, _VP, _I64, _I64, _VP, _VP, _VP, _VP, _VP]),
+    "zebra_debug_read_record": (C.c_int, [_VP, _I32, _I64, _VP]),
+    "zebra_debug_tie_order": (C.c_int, [_VP, _VP, _I32, _I32, _VP]),
     "zebra_tppr_plan_run": (C.c_int, [_VP, _VP, _I64, _I64, _I64, _VP, _I64, _VP]),
     "zebra_tppr_epoch_begin": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _I64, _I32, _I64, _I64, _VP, C.POINTER(_VP)]),
     "zebra_tppr_epoch_next": (C.c_int, [_VP, C.POINTER(_VP), C.POINTER(_I64), C.POINTER(_I64)]),

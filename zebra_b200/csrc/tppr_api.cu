@@ -10,6 +10,7 @@
 #include "../../include/zebra_tppr.h"
 
 #include <algorithm>
+#include <array>
 #include <cstdarg>
 #include <cstdio>
 #include <climits>
@@ -28,7 +29,7 @@ thread_local std::string g_err;
 
 int zebra::fail(const char *fmt, ...)
 {
-    char buf[512];
+    char buf[2048];
     va_list ap;
     va_start(ap, fmt);
     vsnprintf(buf, sizeof buf, fmt, ap);
@@ -42,6 +43,7 @@ namespace {
 using zebra::fail;
 
 constexpr int64_t kChunk = 1 << 18;  // edges per launch of a long span
+constexpr int kStatusWords = 8 + 4 * zebra::kWaitLog;
 
 struct Staging {
     char *host = nullptr;   // pinned
@@ -102,8 +104,8 @@ struct zebra_tppr {
     int32_t decay_len[zebra::kMaxInst] = {}, decay_fixed[zebra::kMaxInst] = {};
     uint32_t *ticket = nullptr;
     uint32_t ticket_base = 0;
-    int32_t *status = nullptr;                // device [4]
-    int32_t *status_host = nullptr;           // pinned [4]
+    int32_t *status = nullptr;                // device [8]: [0] wait time-out, [1] tie prunes, [2] merge-ranked prunes, [4..6] what the expired wait was for
+    int32_t *status_host = nullptr;           // pinned [8]
     unsigned long long *prof = nullptr;       // device [16] phase cycle sums (ZEBRA_PROFILE builds only)
     Staging stg[2];
     int stg_next = 0;
@@ -149,6 +151,10 @@ struct zebra_tppr {
     bool chains_enabled = true;
     int32_t max_chains = zebra::kMaxChains;
     std::vector<int32_t> chain_cnt;            // [num_nodes] scratch of the detection pass (zero between passes)
+    uint32_t *dbg_owner = nullptr;             // debug (ZEBRA_DEBUG_ITEMS=1): who processed each item of the launch
+    size_t dbg_cap = 0;
+    bool dbg_items = false;
+    uint32_t *cprog = nullptr;                 // device [kMaxChains][kMaxInst]: tag of the step each chain warp is at
     char *cmbox = nullptr;                     // chain mailbox (device), grown on demand
     size_t cmbox_cap = 0;
     unsigned long long wait_ns = 20000000000ull;
@@ -282,8 +288,8 @@ void detect_chains(zebra_tppr *h, const NodeT *src, const NodeT *dst, int64_t n,
     std::sort(found.begin(), found.end(), [](const std::pair<int32_t, int32_t> &x, const std::pair<int32_t, int32_t> &y) {
         return x.first != y.first ? x.first > y.first : x.second < y.second;
     });
-    // every chain warp must be resident next to the ticket warps
-    const int room = std::max(0, h->max_blocks * zebra::kWarpsPerBlock / 2 / std::max(1, h->n_tppr));
+    // every (chain, instance) gets a block of its own, resident next to the ticket blocks
+    const int room = std::max(0, h->max_blocks / 2 / std::max(1, h->n_tppr));
     const int keep = std::min<int>({static_cast<int>(found.size()), h->max_chains, zebra::kMaxChains, room});
     if (keep > 0) cs.map.assign(N, 0);
     for (int q = 0; q < keep; ++q) {
@@ -394,12 +400,12 @@ int fill_soa(zebra_tppr *h, char *host, size_t cap, const NodeT *src, const Node
                 o_cidx[i] = ci;
                 const int32_t ei = static_cast<int32_t>(i), ee = static_cast<int32_t>(eidx[i]);
                 if (ca) {
-                    flg[i] |= zebra::kFlagSrcChain;
+                    flg[i] |= zebra::kFlagSrcChain | (static_cast<uint32_t>(ca - 1) << zebra::kFlagSrcChainShift);
                     cb->steps[ca - 1].push_back(zebra::ChainStep{ei, b, ee, db ? p_d[i] : -1, r_s[i],
                                                                  (db ? 0u : zebra::kStepLoop) | (cbq ? zebra::kStepPeerChain : 0u), ci, p_s[i], ts[i], 0});
                 }
                 if (cbq) {
-                    flg[i] |= zebra::kFlagDstChain;
+                    flg[i] |= zebra::kFlagDstChain | (static_cast<uint32_t>(cbq - 1) << zebra::kFlagDstChainShift);
                     cb->steps[cbq - 1].push_back(zebra::ChainStep{ei, a, ee, p_s[i], r_d[i],
                                                                   zebra::kStepDst | (ca ? zebra::kStepPeerChain : 0u), ci, p_d[i], ts[i], 0});
                 }
@@ -628,6 +634,17 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
     }
     p.out = out; p.ticket = h->ticket; p.status = h->status; p.prof = h->prof;
     p.wait_ns = h->wait_ns;
+    if (h->dbg_items && h->world == 1) {
+        const size_t need = static_cast<size_t>(m) * h->n_tppr * sizeof(uint32_t);
+        if (h->dbg_cap < need) {
+            CU(cudaStreamSynchronize(st));
+            if (h->dbg_owner) CU(cudaFree(h->dbg_owner));
+            CU(cudaMalloc(&h->dbg_owner, need));
+            h->dbg_cap = need;
+        }
+        CU(cudaMemsetAsync(h->dbg_owner, 0, need, st));
+        p.dbg_owner = h->dbg_owner;
+    }
     p.cidx = reinterpret_cast<const int32_t *>(dev + cap * kCidxOffset) + lo;
     int chain_warps = 0;
     if (cl && cl->n > 0) {
@@ -642,6 +659,7 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
             CU(cudaMemsetAsync(h->cmbox, 0, grow, st));
             h->cmbox_cap = grow;
         }
+        p.cprog = h->cprog;
         p.csteps = cl->dev_steps; p.cmbox = h->cmbox; p.cidx_base = cl->cidx_base; p.n_chains = cl->n;
         for (int q = 0; q < cl->n; ++q) p.chains[q] = zebra::ChainDesc{cl->node[q], cl->begin[q], cl->end[q], 0};
         chain_warps = cl->n * h->n_tppr;
@@ -657,9 +675,9 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
                                                     sharded ? h->shard_max_blocks : h->max_blocks));
     if (blocks < 1) blocks = 1;
     if (chain_warps) {
-        // one chain warp per block where the grid allows it; all of them resident in any case
-        blocks = std::max(blocks, std::min(chain_warps, h->max_blocks));
-        if (chain_warps > blocks * zebra::kWarpsPerBlock) return fail("%d chain warps do not fit a grid of %d blocks", chain_warps, blocks);
+        // one block per (chain, instance): its warp 0 walks the chain, the others help; all resident
+        blocks = std::max(blocks, chain_warps);
+        if (chain_warps > h->max_blocks) return fail("%d chain blocks do not fit a resident grid of %d blocks", chain_warps, h->max_blocks);
     }
     if (sharded) {
         if (m > h->max_window_edges) return fail("sharded launch of %lld edges exceeds the mailbox window (%lld)", (long long)m, (long long)h->max_window_edges);
@@ -730,15 +748,37 @@ int launch_chunk(zebra_tppr *h, Staging &s, int64_t m, int64_t n_total, int64_t 
     return 0;
 }
 
+// Error text of a wait time-out: the first expired wait and the abandoned waits with the smallest edge tags
+// (the root cause is normally the oldest edge that could not proceed).
+int fail_timeout(zebra_tppr *h)
+{
+    const int32_t *sh = h->status_host;
+    std::vector<std::array<int32_t, 4>> log;
+    const int cnt = std::min<int>(sh[7], zebra::kWaitLog);
+    for (int q = 0; q < cnt; ++q) log.push_back({sh[8 + 4 * q], sh[9 + 4 * q], sh[10 + 4 * q], sh[11 + 4 * q]});
+    std::sort(log.begin(), log.end(), [](const std::array<int32_t, 4> &x, const std::array<int32_t, 4> &y) {
+        return static_cast<uint32_t>(x[1]) < static_cast<uint32_t>(y[1]);
+    });
+    std::string txt;
+    char buf[96];
+    for (size_t q = 0; q < log.size() && q < 10; ++q) {
+        snprintf(buf, sizeof buf, " [kind %d tag %u detail %u node %d]", log[q][0], static_cast<unsigned>(log[q][1]),
+                 static_cast<unsigned>(log[q][2]), log[q][3]);
+        txt += buf;
+    }
+    return fail("T-PPR span kernel: dependency wait timed out (first: kind %d, edge tag %u, detail %u; %d waits abandoned, oldest:%s; kinds: see Waiter in tppr_device.cuh)",
+                sh[4], static_cast<unsigned>(sh[5]), static_cast<unsigned>(sh[6]), sh[7], txt.c_str());
+}
+
 int check_status(zebra_tppr *h, cudaStream_t st)
 {
-    CU(cudaMemcpyAsync(h->status_host, h->status, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(h->status_host, h->status, kStatusWords * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     h->last_ties = h->status_host[1];
     h->last_merge = h->status_host[2];
     if (h->status_host[0] != 0) {
         h->timeouts++;
-        return fail("T-PPR span kernel: dependency wait timed out (status=%d)", h->status_host[0]);
+        return fail_timeout(h);
     }
     return 0;
 }
@@ -835,11 +875,13 @@ int zebra_tppr_create(zebra_tppr_t **out, int64_t num_nodes, int32_t k, int32_t 
         CU(cudaMalloc(&h->decay[j], tab.size() * sizeof(zebra::DecayStep)));
         CU(cudaMemcpy(h->decay[j], tab.data(), tab.size() * sizeof(zebra::DecayStep), cudaMemcpyHostToDevice));
     }
+    CU(cudaMalloc(&h->cprog, sizeof(uint32_t) * zebra::kMaxChains * zebra::kMaxInst));
+    CU(cudaMemset(h->cprog, 0, sizeof(uint32_t) * zebra::kMaxChains * zebra::kMaxInst));
     CU(cudaMalloc(&h->ticket, sizeof(uint32_t)));
     CU(cudaMemset(h->ticket, 0, sizeof(uint32_t)));
-    CU(cudaMalloc(&h->status, 4 * sizeof(int32_t)));
-    CU(cudaMemset(h->status, 0, 4 * sizeof(int32_t)));
-    CU(cudaMallocHost(&h->status_host, 4 * sizeof(int32_t)));
+    CU(cudaMalloc(&h->status, kStatusWords * sizeof(int32_t)));
+    CU(cudaMemset(h->status, 0, kStatusWords * sizeof(int32_t)));
+    CU(cudaMallocHost(&h->status_host, kStatusWords * sizeof(int32_t)));
     CU(cudaMalloc(&h->prof, 16 * sizeof(unsigned long long)));
     CU(cudaMemset(h->prof, 0, 16 * sizeof(unsigned long long)));
     CU(cudaEventCreate(&h->ev0));
@@ -852,6 +894,7 @@ int zebra_tppr_create(zebra_tppr_t **out, int64_t num_nodes, int32_t k, int32_t 
         h->max_chains = std::max(0, std::min(atoi(e), zebra::kMaxChains));
         h->chains_enabled = h->max_chains > 0;
     }
+    if (const char *e = getenv("ZEBRA_DEBUG_ITEMS")) h->dbg_items = atoi(e) != 0;
     if (const char *e = getenv("ZEBRA_WAIT_TIMEOUT_MS")) h->wait_ns = static_cast<unsigned long long>(std::max(1, atoi(e))) * 1000000ull;
     *out = h;
     return 0;
@@ -884,6 +927,8 @@ int zebra_tppr_destroy(zebra_tppr_t *h)
         for (auto &t : h->tables) if (t) cudaFree(t);
     if (h->rcnt) cudaFree(h->rcnt);
     if (h->cmbox) cudaFree(h->cmbox);
+    if (h->cprog) cudaFree(h->cprog);
+    if (h->dbg_owner) cudaFree(h->dbg_owner);
     for (auto d : h->decay) if (d) cudaFree(d);
     if (h->ticket) cudaFree(h->ticket);
     if (h->status) cudaFree(h->status);
@@ -920,7 +965,7 @@ int zebra_tppr_reset_tickets(zebra_tppr_t *h, void *stream)
     CU(cudaSetDevice(h->device));
     CU(cudaStreamSynchronize(st));
     CU(cudaMemsetAsync(h->rcnt, 0, sizeof(int32_t) * h->num_nodes * h->n_tppr, st));
-    CU(cudaMemsetAsync(h->status, 0, 4 * sizeof(int32_t), st));       // also clears a recorded wait time-out
+    CU(cudaMemsetAsync(h->status, 0, kStatusWords * sizeof(int32_t), st));       // also clears a recorded wait time-out
     h->plan_active = nullptr;
     h->rcnt_dirty = false;
     return 0;
@@ -1165,6 +1210,42 @@ int zebra_debug_host_pass(int64_t num_nodes, int32_t world, int32_t rank, const 
     return 0;
 }
 
+// Test hook: the exact-tie ordering of the prune in isolation (tppr_device.cuh tie_order): final argsort
+// ranks of n_cases arrays of small integers, to be compared with numba's argsort on the host.
+int zebra_debug_tie_order(const int32_t *host_values, const int32_t *host_n, int32_t n_cases, int32_t stride, int32_t *host_ranks)
+{
+    if (!host_values || !host_n || !host_ranks || n_cases <= 0 || stride < 64) return fail("bad argument");
+    for (int c = 0; c < n_cases; ++c)
+        if (host_n[c] < 2 || host_n[c] > 63) return fail("case %d: n must be 2..63", c);
+    int32_t *dv = nullptr, *dn = nullptr, *dout = nullptr;
+    const size_t bytes = static_cast<size_t>(n_cases) * stride * sizeof(int32_t);
+    cudaError_t e = cudaMalloc(&dv, bytes);
+    if (e == cudaSuccess) e = cudaMalloc(&dn, n_cases * sizeof(int32_t));
+    if (e == cudaSuccess) e = cudaMalloc(&dout, bytes);
+    if (e == cudaSuccess) e = cudaMemcpy(dv, host_values, bytes, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(dn, host_n, n_cases * sizeof(int32_t), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemset(dout, 0xff, bytes);
+    if (e == cudaSuccess) {
+        zebra::tie_order_test_kernel<<<n_cases, 32>>>(dv, dn, stride, dout);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(host_ranks, dout, bytes, cudaMemcpyDeviceToHost);
+    cudaFree(dv); cudaFree(dn); cudaFree(dout);
+    if (e != cudaSuccess) return fail("tie order test: %s", cudaGetErrorString(e));
+    return 0;
+}
+
+// Test / debug hook: the raw bytes of one node record (header and chunks with their tags).
+int zebra_debug_read_record(zebra_tppr_t *h, int32_t inst, int64_t node, void *host_out)
+{
+    if (!h || !host_out || inst < 0 || inst >= h->n_tppr || !h->tables[inst]) return fail("bad argument");
+    if (node < 0 || node >= h->table_rows) return fail("node out of range");
+    CU(cudaSetDevice(h->device));
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(host_out, h->tables[inst] + static_cast<size_t>(node) * h->stride, h->stride, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
 size_t zebra_tppr_plan_bytes(const zebra_plan_t *pl)
 {
     if (!pl) return 0;
@@ -1361,11 +1442,14 @@ int zebra_tppr_epoch_next(zebra_epoch_t *ep, void **host_rows, int64_t *first_ba
     *host_rows = ep->rows_per_edge ? sl.out_host : nullptr;
     ep->consumed = w + 1;
     if (ep->consumed == ep->n_windows) {
-        CU(cudaMemcpyAsync(h->status_host, h->status, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, ep->st));
+        CU(cudaMemcpyAsync(h->status_host, h->status, kStatusWords * sizeof(int32_t), cudaMemcpyDeviceToHost, ep->st));
         CU(cudaStreamSynchronize(ep->st));
         h->last_ties = h->status_host[1];
         h->last_merge = h->status_host[2];
-        if (h->status_host[0] != 0) { h->timeouts++; return fail("T-PPR span kernel: dependency wait timed out"); }
+        if (h->status_host[0] != 0) {
+            h->timeouts++;
+            return fail_timeout(h);
+        }
         h->rcnt_dirty = false;
     }
     return 0;

@@ -44,6 +44,7 @@ __host__ __device__ inline size_t record_stride(int k) { return (static_cast<siz
 
 enum : uint32_t { kFlagSignal = 1u, kFlagDstFirst = 2u,
                   kFlagSrcChain = 4u, kFlagDstChain = 8u };   // that endpoint is updated by a resident chain warp
+constexpr int kFlagSrcChainShift = 8, kFlagDstChainShift = 13;   // 5 bits each: which chain
 
 // ---- hub chains -------------------------------------------------------------------------------
 // A node with many edges in one launch serialises them through its vector: every update needs the
@@ -137,6 +138,8 @@ struct SpanParams {
     const ChainStep *csteps;
     char *cmbox;                                    // [(cidx - cidx_base) * n_tppr + j][2 sides] records
     int32_t cidx_base, n_chains;
+    uint32_t *dbg_owner;                            // debug (ZEBRA_DEBUG_ITEMS=1): [edge][instance] who processed the item
+    uint32_t *cprog;                                // [chain][instance] tag of the step the chain warp is working on
     unsigned long long wait_ns;                     // dependency-wait time-out (globaltimer)
     ChainDesc chains[kMaxChains];
 };
@@ -231,16 +234,36 @@ __device__ __forceinline__ unsigned long long gtime()
 // Bounded waiting: every 256 polls look at the abort flag and at the clock.  The limit is wall time
 // (SpanParams::wait_ns, ZEBRA_WAIT_TIMEOUT_MS), not a poll count: a peer GPU that launches late or a
 // long producer chain must not be mistaken for a dead-lock.
+constexpr int kWaitLog = 96;   // abandoned waits listed in status[8 ...] (4 words each) after a time-out
 struct Waiter {
     unsigned spins = 0;
     unsigned long long t0 = 0;
-    __device__ __forceinline__ bool expired(const int32_t *status, unsigned long long limit)
+    // `code`, `a`, `b`: what was being waited for, recorded in status[4..6] by the first wait that expires
+    // (1 table record of src/dst, 2 chain mailbox slot, 3 negative-sample readers, 4 negative's record,
+    //  5 chain: own record, 6 chain: partner chain's push, 7 chain: partner's record, 8 peer GPU's push)
+    __device__ __forceinline__ void log_wait(int32_t *status, int code, uint32_t a, uint32_t b, int32_t c)
+    {
+        if ((threadIdx.x & 31) != 0) return;
+        const int idx = atomicAdd(status + 7, 1);          // every abandoned wait is listed (first kWaitLog of them)
+        if (idx < kWaitLog) {
+            int32_t *e = status + 8 + 4 * idx;
+            e[0] = code; e[1] = static_cast<int32_t>(a); e[2] = static_cast<int32_t>(b);
+            e[3] = c;
+        }
+    }
+    __device__ __forceinline__ bool expired(int32_t *status, unsigned long long limit, int code = 0, uint32_t a = 0, uint32_t b = 0, int32_t c = -1)
     {
         if ((++spins & 0xff) != 0) return false;
-        if (*reinterpret_cast<const volatile int32_t *>(status) != 0) return true;
+        if (*reinterpret_cast<const volatile int32_t *>(status) != 0) { log_wait(status, code, a, b, c); return true; }
         const unsigned long long now = gtime();
         if (t0 == 0) t0 = now;
-        else if (now - t0 > limit) { atomicExch(const_cast<int32_t *>(status), 1); return true; }
+        else if (now - t0 > limit) {
+            if ((threadIdx.x & 31) == 0 && atomicExch(status, 1) == 0) {
+                status[4] = code; status[5] = static_cast<int32_t>(a); status[6] = static_cast<int32_t>(b);
+            }
+            log_wait(status, code, a, b, c);
+            return true;
+        }
         return false;
     }
 };
@@ -323,6 +346,15 @@ __device__ __forceinline__ void emit_row(const SpanParams &p, char *base, size_t
     reinterpret_cast<float *>(base + plane * 8)[o] = dt;
     reinterpret_cast<float *>(base + plane * 12)[o] = w;
 }
+// ---- exact ties: numba's argsort replayed -------------------------------------------------------
+// np.argsort(values)[-k:] (utils/util.py:555) runs numba.misc.quicksort: median-of-three Hoare
+// partitions while a range is longer than 15, then one insertion sort.  The insertion sort is stable,
+// so the order inside a group of equal scores is their order after the partition phase.  The phase is
+// replayed on 16-bit items (rank << 8 | candidate) — the rank (number of strictly smaller scores) is an
+// order-isomorphic stand-in for the fp64 score.  (A register-resident variant that partitions two
+// pending ranges per round was measured 20-35 % slower on the hub chain — more selects and 64-bit mask
+// arithmetic per round than the two steps it replaces — and was dropped.)
+
 // One partition step of numba.misc.quicksort (median of three, pivot stashed at `high`, Hoare
 // scan) on positions [low, high] of the working array Q (items rank << 8 | candidate, compared by
 // rank only).  Computed warp-wide from two stopper bitmaps instead of a sequential scan; two warp
@@ -453,6 +485,58 @@ __device__ __forceinline__ void qs_partition_phase(WarpScratch &s, int n, int la
     __syncwarp();
 }
 
+// Final ranks (ascending argsort positions) of n candidates from their ranks (number of strictly
+// smaller scores), with numba's order inside groups of equal ranks; groups whose final ranks all lie
+// below `cut` keep their common rank (they are pruned anyway).  `occ` = bitmap of the occupied ranks.
+// slot 0 = candidate `lane` (valid0), slot 1 = candidate `c1` (valid1).
+__device__ __forceinline__ void tie_order(WarpScratch &s, int n, int cut, unsigned long long occ, bool valid0, int &r0,
+                                          bool valid1, int c1, int &r1, int lane)
+{
+    (void)cut; (void)occ;
+    __syncwarp();
+    s.Mlo[lane] = 0; s.Mlo[lane + 32] = 0; s.Mhi[lane] = 0; s.Mhi[lane + 32] = 0;
+    if (valid0) s.Q[lane] = static_cast<unsigned short>((r0 << 8) | lane);
+    if (valid1) s.Q[c1] = static_cast<unsigned short>((r1 << 8) | c1);
+    __syncwarp();
+    qs_partition_phase(s, n, lane);
+    // order inside a group of equal ranks = order of the positions after the partition phase: per rank a
+    // bitmap of the positions holding it, a candidate's offset = the set bits below its own position
+    const int P0 = valid0 ? s.P[lane] : 0, P1 = valid1 ? s.P[c1] : 0;
+    if (valid0) atomicOr(P0 < 32 ? &s.Mlo[r0] : &s.Mhi[r0], 1u << (P0 & 31));
+    if (valid1) atomicOr(P1 < 32 ? &s.Mlo[r1] : &s.Mhi[r1], 1u << (P1 & 31));
+    __syncwarp();
+    if (valid0) {
+        const unsigned lo = s.Mlo[r0], hi = s.Mhi[r0];
+        r0 += P0 < 32 ? __popc(lo & ((1u << P0) - 1)) : __popc(lo) + __popc(hi & ((1u << (P0 - 32)) - 1));
+    }
+    if (valid1) {
+        const unsigned lo = s.Mlo[r1], hi = s.Mhi[r1];
+        r1 += P1 < 32 ? __popc(lo & ((1u << P1) - 1)) : __popc(lo) + __popc(hi & ((1u << (P1 - 32)) - 1));
+    }
+}
+
+// Test hook: final ranks of `n` candidates (values[] = small integers standing in for scores) exactly as
+// the prune computes them; one warp per case.  candidates 0..31 in slot 0, 32..63 in slot 1.
+__global__ void tie_order_test_kernel(const int32_t *values, const int32_t *ns, int32_t stride, int32_t *out)
+{
+    __shared__ WarpScratch s;
+    const int lane = threadIdx.x;
+    const int32_t *v = values + static_cast<size_t>(blockIdx.x) * stride;
+    const int n = ns[blockIdx.x];
+    const bool valid0 = lane < n, valid1 = lane + 32 < n;
+    int r0 = 0, r1 = 0;
+    for (int c = 0; c < n; ++c) {
+        if (valid0 && v[c] < v[lane]) ++r0;
+        if (valid1 && v[c] < v[lane + 32]) ++r1;
+    }
+    const unsigned long long mine = (valid0 ? 1ull << r0 : 0ull) | (valid1 ? 1ull << r1 : 0ull);
+    const unsigned long long occ = __reduce_or_sync(kFull, static_cast<unsigned>(mine)) |
+                                   (static_cast<unsigned long long>(__reduce_or_sync(kFull, static_cast<unsigned>(mine >> 32))) << 32);
+    tie_order(s, n, 0, occ, valid0, r0, valid1, lane + 32, r1, lane);
+    if (valid0) out[static_cast<size_t>(blockIdx.x) * stride + lane] = r0;
+    if (valid1) out[static_cast<size_t>(blockIdx.x) * stride + lane + 32] = r1;
+}
+
 __device__ __forceinline__ void st_entry(char *rec, int k, int pos, int e, int n, double ts, double sc, uint32_t tag)
 {
     st_chunk(rec + 16 + 16 * pos, sc, e, tag);
@@ -461,7 +545,16 @@ __device__ __forceinline__ void st_entry(char *rec, int k, int pos, int e, int n
 
 // New vector of one endpoint from the OLD vectors of itself (A) and its peer (B)
 // (utils/util.py:509-559), written straight into the endpoint's record with tag `tag`.
-// `rwait` > 0: that many negative-sample reads of the old version must have finished first.
+// `rwait` > 0: that many negative-sample reads of the old version must have finished first.  The
+// counter of a node holds (reads finished) - (reads claimed by writers): the writer CLAIMS its `rwait`
+// reads with a returning atomic at the start of the update and, before storing, waits until the counter
+// is back to >= 0.  The claim has returned — i.e. has been performed — before the new version is stored,
+// so the next writer of the node (which starts from that version) can never see the counter without it.
+// (A fire-and-forget subtraction after the wait, as in round 1, is not ordered against the record stores:
+// the next writer could read the counter before the subtraction landed and overwrite a version whose
+// reader had not loaded it yet.)
+// `stats`: prunes that took the exact-tie path (high half) / the merge ranking (low half) are counted per
+// warp and added to the global counters once, when the warp leaves the kernel.
 // This function is the step of every hub's dependency chain: it is written for the latency of a
 // single warp (independent shared-memory loads, unrolled compare loops), not for throughput.
 // kKeep (chain warps): the new vector is also returned in registers, in slot order, through `newv`.
@@ -469,9 +562,11 @@ template <bool kKeep = false>
 __device__ __forceinline__ bool update_endpoint(const SpanParams &p, WarpScratch &s, const VecR &A, const VecR &B,
                                                 int peer_id, int e_new, double t_new, int j,
                                                 char *rec, uint32_t tag, int32_t *rcnt, uint32_t rwait, int lane,
-                                                VecR *newv = nullptr)
+                                                unsigned &stats, VecR *newv = nullptr)
 {
     ZP_DECL;
+    int claimed = 0;
+    if (rwait != 0 && lane == 0) claimed = atomicSub(rcnt, static_cast<int32_t>(rwait));   // returns the value before
     const int k = p.k;
     const int c1 = A.cnt;
     const int c2 = (B.norm != 0.0) ? B.cnt : 0;
@@ -618,7 +713,7 @@ __device__ __forceinline__ bool update_endpoint(const SpanParams &p, WarpScratch
             }
             r0 = firstA + lb + (bw < b0 ? 1 : 0);
             r1 = lane == 31 ? la + lb : firstB + la + (bw < b1 ? 1 : 0);
-            if (lane == 0) atomicAdd(p.status + 2, 1);
+            stats += 1u;
         } else {
             const ulonglong2 *V2 = reinterpret_cast<const ulonglong2 *>(s.V);
 #pragma unroll 4
@@ -638,26 +733,9 @@ __device__ __forceinline__ bool update_endpoint(const SpanParams &p, WarpScratch
         // survivor set or its slot order depends on numba's (unstable) argsort
         const unsigned long long surv = ((1ull << k) - 1) << cut;
         if ((occ & surv) != surv && !(ZEBRA_ABLATE & 4)) {
-            // numba's (unstable) argsort decides the order inside a group of equal scores: replay its
-            // partition phase on the ranks, then order equals by their position in the permuted array
-            s.Mlo[lane] = 0; s.Mlo[lane + 32] = 0; s.Mhi[lane] = 0; s.Mhi[lane + 32] = 0;
-            if (valid0) s.Q[lane] = static_cast<unsigned short>((r0 << 8) | lane);
-            if (valid1) s.Q[pos1] = static_cast<unsigned short>((r1 << 8) | pos1);
-            __syncwarp();
-            qs_partition_phase(s, n, lane);
-            const int P0 = valid0 ? s.P[lane] : 0, P1 = valid1 ? s.P[pos1] : 0;
-            if (valid0) atomicOr(P0 < 32 ? &s.Mlo[r0] : &s.Mhi[r0], 1u << (P0 & 31));
-            if (valid1) atomicOr(P1 < 32 ? &s.Mlo[r1] : &s.Mhi[r1], 1u << (P1 & 31));
-            __syncwarp();
-            if (valid0) {
-                const unsigned lo = s.Mlo[r0], hi = s.Mhi[r0];
-                r0 += P0 < 32 ? __popc(lo & ((1u << P0) - 1)) : __popc(lo) + __popc(hi & ((1u << (P0 - 32)) - 1));
-            }
-            if (valid1) {
-                const unsigned lo = s.Mlo[r1], hi = s.Mhi[r1];
-                r1 += P1 < 32 ? __popc(lo & ((1u << P1) - 1)) : __popc(lo) + __popc(hi & ((1u << (P1 - 32)) - 1));
-            }
-            if (lane == 0) atomicAdd(p.status + 1, 1);
+            // numba's (unstable) argsort decides the order inside a group of equal scores
+            tie_order(s, n, cut, occ, valid0, r0, valid1, pos1, r1, lane);
+            stats += 0x10000u;
         }
         ZP_MARK(11);
         keep0 = valid0 && r0 >= cut; pos0 = r0 - cut;
@@ -668,12 +746,15 @@ __device__ __forceinline__ bool update_endpoint(const SpanParams &p, WarpScratch
     // ---- the version being overwritten may still have negative-sample readers ----
     bool ok = true;
     if (rwait != 0) {
-        Waiter w;
-        while (ld_relaxed_s32(rcnt) < static_cast<int32_t>(rwait)) {
-            if (w.expired(p.status, p.wait_ns)) { ok = false; break; }
-            __nanosleep(64);
+        claimed = __shfl_sync(kFull, claimed, 0);
+        if (claimed < static_cast<int32_t>(rwait)) {       // some of the claimed reads had not finished yet
+            Waiter w;
+            while (ld_relaxed_s32(rcnt) < 0) {
+                if (w.expired(p.status, p.wait_ns, 3, tag, rwait, static_cast<int32_t>(rcnt - p.rcnt[j]))) { ok = false; break; }
+                __nanosleep(64);
+            }
         }
-        if (lane == 0) atomicSub(rcnt, static_cast<int32_t>(rwait));
+        if (!ok) return false;                             // (also makes the stores depend on the claim's result)
     }
     // every chunk validates itself by its tag, so the order of these stores does not matter
     const int upd = A.upd < kMaxUpdates ? A.upd + 1 : kMaxUpdates;
@@ -734,7 +815,7 @@ __device__ __forceinline__ uint32_t load_step_word(const ChainStep *st, int lane
 // chain warp pushes), push the own OLD vector into the item's mailbox slot for the ticket warp that does
 // the rest of the edge, update, publish the new version to the table record.  The next partner's record
 // is loaded into registers before the update, so that its latency overlaps the update.
-__device__ __noinline__ void run_chain(const SpanParams &p, WarpScratch &s, int q, int j, int lane)
+__device__ __noinline__ void run_chain(const SpanParams &p, WarpScratch &s, int q, int j, int lane, unsigned &stats)
 {
     const ChainDesc c = p.chains[q];
     if (c.begin >= c.end) return;
@@ -751,7 +832,7 @@ __device__ __noinline__ void run_chain(const SpanParams &p, WarpScratch &s, int 
         uint32_t cur;
         Waiter wt;
         while (!try_load(recH, k, lane, prev_self < 0, p.seq0 + static_cast<uint32_t>(prev_self), H, cur)) {
-            if (wt.expired(p.status, p.wait_ns)) return;
+            if (wt.expired(p.status, p.wait_ns, 5, static_cast<uint32_t>(c.node), static_cast<uint32_t>(prev_self))) return;
             __nanosleep(100);
         }
     }
@@ -763,6 +844,7 @@ __device__ __noinline__ void run_chain(const SpanParams &p, WarpScratch &s, int 
         raw = load_raw(table + static_cast<size_t>((fl & (kStepLoop | kStepPeerChain)) ? c.node : peer) * p.stride, k, lane);
     }
     for (int x = c.begin; x < c.end; ++x) {
+        ZP_DECL;
         const uint32_t w2 = x + 2 < c.end ? load_step_word(steps + x + 2, lane) : 0u;   // used two steps from now
         const int32_t edge = static_cast<int32_t>(__shfl_sync(kFull, w0, 0));
         const int peer = static_cast<int>(__shfl_sync(kFull, w0, 1));
@@ -773,6 +855,7 @@ __device__ __noinline__ void run_chain(const SpanParams &p, WarpScratch &s, int 
         const int32_t cidx = static_cast<int32_t>(__shfl_sync(kFull, w0, 6));
         const double t_new = __hiloint2double(static_cast<int>(__shfl_sync(kFull, w0, 9)), static_cast<int>(__shfl_sync(kFull, w0, 8)));
         const uint32_t tag = p.seq0 + static_cast<uint32_t>(edge);
+        if (lane == 0) *reinterpret_cast<volatile uint32_t *>(p.cprog + q * p.n_tppr + j) = tag;   // how far the chain is (waiters pace their polling by it)
         const int side = static_cast<int>(fl & kStepDst);
         char *my_slot = chain_slot(p, cidx, j, side);
         VecR B;
@@ -787,7 +870,7 @@ __device__ __noinline__ void run_chain(const SpanParams &p, WarpScratch &s, int 
             uint32_t cur;
             Waiter wt;
             while (!try_load(other, k, lane, false, tag, B, cur)) {
-                if (wt.expired(p.status, p.wait_ns)) { alive = false; break; }
+                if (wt.expired(p.status, p.wait_ns, 6, tag, static_cast<uint32_t>(peer))) { alive = false; break; }
                 __nanosleep(40);
             }
         } else {
@@ -797,7 +880,7 @@ __device__ __noinline__ void run_chain(const SpanParams &p, WarpScratch &s, int 
             bool ok = check_raw(raw, lane, prev_peer < 0, expect, B, cur);
             Waiter wt;
             while (!ok) {
-                if (wt.expired(p.status, p.wait_ns)) { alive = false; break; }
+                if (wt.expired(p.status, p.wait_ns, 7, tag, expect, peer)) { alive = false; break; }
                 __nanosleep(40);
                 ok = try_load(recP, k, lane, prev_peer < 0, expect, B, cur);
             }
@@ -805,17 +888,24 @@ __device__ __noinline__ void run_chain(const SpanParams &p, WarpScratch &s, int 
             if (alive) push_vector<false>(my_slot, k, H, tag, lane);
         }
         if (!alive) return;
+        ZP_MARK(5);
         // next step's partner record on its way while this step computes
         if (x + 1 < c.end) {
             const uint32_t nfl = __shfl_sync(kFull, w1, 5);
             const int npeer = static_cast<int>(__shfl_sync(kFull, w1, 1));
             raw = load_raw(table + static_cast<size_t>((nfl & (kStepLoop | kStepPeerChain)) ? c.node : npeer) * p.stride, k, lane);
         }
+        ZP_MARK(6);
         VecR Hn;
-        const bool ok = update_endpoint<true>(p, s, H, B, peer, e_new, t_new, j, recH, tag, rcntH, rthr, lane, &Hn);
+        const bool ok = update_endpoint<true>(p, s, H, B, peer, e_new, t_new, j, recH, tag, rcntH, rthr, lane, stats, &Hn);
         if (!ok) { atomicExch(p.status, 1); return; }
+        if ((stats & 0xffffu) > 0xff00u || (stats >> 16) > 0xff00u) {      // the halves are 16 bits wide
+            if (lane == 0) { atomicAdd(p.status + 2, static_cast<int>(stats & 0xffffu)); atomicAdd(p.status + 1, static_cast<int>(stats >> 16)); }
+            stats = 0;
+        }
         H = Hn;
         w0 = w1; w1 = w2;
+        ZP_MARK(7);
     }
 }
 
@@ -830,23 +920,60 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
     const int k = p.k;
     const uint32_t tag_base = p.seq0 + static_cast<uint32_t>(p.tag_offset);   // tag of launch-local edge 0
 
-    // resident chain warps first (warp 0 of the first blocks, then warp 1, ...: spread over the SMs)
-    if (p.n_chains > 0) {
-        const unsigned cw = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
-        if (cw < static_cast<unsigned>(p.n_chains * p.n_tppr)) {
-            const int q = cw / p.n_tppr, j = cw - q * p.n_tppr;
-            if ((p.inst_mask >> j) & 1) run_chain(p, s, q, j, lane);
+    // The first n_chains * n_tppr blocks each serve one (chain, instance): warp 0 walks the chain
+    // (run_chain), the other warps are its HELPERS — they take the chain's edges in turn (helper h the
+    // steps h-1, h-1+7, ...) and do everything of such an edge that is not the chain node's own update:
+    // the partner's update and the rows.  Ticket warps skip edges with a chain endpoint, so the ticket
+    // front never queues up behind a chain; when a block's chain is done all its warps draw tickets.
+    unsigned stats = 0;
+    int hx = 0, hx_end = 0, hj = 0;
+    if (p.n_chains > 0 && blockIdx.x < static_cast<unsigned>(p.n_chains * p.n_tppr)) {
+        const int q = blockIdx.x / p.n_tppr;
+        hj = blockIdx.x - q * p.n_tppr;
+        if ((p.inst_mask >> hj) & 1) {
+            if ((threadIdx.x >> 5) == 0) run_chain(p, s, q, hj, lane, stats);
+            else { hx = p.chains[q].begin + (threadIdx.x >> 5) - 1; hx_end = p.chains[q].end; }
         }
     }
 
     for (;;) {
-        uint32_t tk = 0;
-        if (lane == 0) tk = atomicAdd(p.ticket, 1u) - p.ticket_base;
-        tk = __shfl_sync(kFull, tk, 0);
-        if (tk >= total) break;
+        int64_t i;
+        int j;
+        if (hx < hx_end) {
+            // helper: the next edge of the chain that is this warp's turn
+            const ChainStep *st = p.csteps + hx;
+            hx += kWarpsPerBlock - 1;
+            const uint32_t fl = __ldg(&st->flags);
+            // an edge between two chain nodes is in both chains: the helpers of its src side take it
+            if ((fl & kStepPeerChain) && (fl & kStepDst)) continue;
+            i = static_cast<int64_t>(__ldg(&st->edge)) - p.tag_offset;
+            j = hj;
+        } else {
+            uint32_t tk = 0;
+            if (lane == 0) tk = atomicAdd(p.ticket, 1u) - p.ticket_base;
+            tk = __shfl_sync(kFull, tk, 0);
+            if (tk >= total) {
+                if (lane == 0 && stats) {
+                    if (stats & 0xffffu) atomicAdd(p.status + 2, static_cast<int>(stats & 0xffffu));
+                    if (stats >> 16) atomicAdd(p.status + 1, static_cast<int>(stats >> 16));
+                }
+                break;
+            }
+            i = tk / static_cast<uint32_t>(p.n_tppr);     // 32-bit division: items < 2^32
+            j = static_cast<int>(tk - i * p.n_tppr);
+            if (p.flags[i] & (kFlagSrcChain | kFlagDstChain)) continue;   // a chain block's helpers take it
+        }
         ZP_DECL;
-        const int64_t i = tk / static_cast<uint32_t>(p.n_tppr);     // 32-bit division: items < 2^32
-        const int j = tk - i * p.n_tppr;
+        if (p.dbg_owner && lane == 0) {
+            // debug: every (edge, instance) must be processed exactly once
+            const uint32_t me = 1u + blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5) + (hx_end ? 0x40000000u : 0u);
+            const uint32_t old = atomicExch(p.dbg_owner + i * p.n_tppr + j, me);
+            if (old != 0) {
+                atomicExch(p.status, 1);
+                Waiter w;
+                w.log_wait(p.status, 99, tag_base + static_cast<uint32_t>(i), old, static_cast<int32_t>(me));
+            }
+        }
         const int sN = p.src[i], dN = p.dst[i];
         const bool has_neg = p.rows_per_edge == 3;
         const int gN = has_neg ? p.neg[i] : sN;
@@ -889,7 +1016,6 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
         bool okG = neg_own ? try_load(recG, k, lane, pG < 0, p.seq0 + static_cast<uint32_t>(pG), G, curG) : true;
         bool alive = true;
         Waiter wt;
-        unsigned nap = 64;
         ZP_MARK(0);
         while (!(okS && okD)) {
             // distance (in edges) of the farther unsatisfied table producer from the version visible now
@@ -911,25 +1037,34 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
                 const bool nearS = okS || cS || curS == expS;
                 const bool nearD = okD || cD || curD == expD;
                 if (!(nearS && nearD)) {
-                    if (wt.expired(p.status, p.wait_ns)) { alive = false; break; }
+                    if (wt.expired(p.status, p.wait_ns, 1, my_tag, okS ? expD : expS, okS ? dN : sN)) { alive = false; break; }
                     continue;
                 }
             } else if ((!okS && cS) || (!okD && cD)) {
-                // waiting for a chain warp to reach this edge: off the chain, so poll the slot header
-                // only, a little less often each time
-                __nanosleep(nap);
-                if (nap < 2048) nap <<= 1;
-                const bool hS = okS || !cS || ld_tag(srcS) == my_tag;
-                const bool hD = okD || !cD || ld_tag(srcD) == my_tag;
-                if (!(hS && hD)) {
-                    if (wt.expired(p.status, p.wait_ns)) { alive = false; break; }
-                    continue;
+                // waiting for a chain warp to reach this edge: sleep in proportion to how far away it is
+                // (it publishes the tag of the step it is at), then look at the slot header only.  The
+                // partner's update of this edge may be the producer of the chain's NEXT step (reply
+                // edges), so once the chain is here the polling is tight.
+                uint32_t away = 0;
+                if (!okS && cS) away = my_tag - *reinterpret_cast<volatile uint32_t *>(p.cprog + ((flags >> kFlagSrcChainShift) & 31u) * p.n_tppr + j);
+                if (!okD && cD) {
+                    const uint32_t a2 = my_tag - *reinterpret_cast<volatile uint32_t *>(p.cprog + ((flags >> kFlagDstChainShift) & 31u) * p.n_tppr + j);
+                    away = a2 > away ? a2 : away;
+                }
+                if (away != 0) {
+                    __nanosleep(away > 1024u ? 4000u : 50u + away * 4u);
+                    const bool hS = okS || !cS || ld_tag(srcS) == my_tag;
+                    const bool hD = okD || !cD || ld_tag(srcD) == my_tag;
+                    if (!(hS && hD)) {
+                        if (wt.expired(p.status, p.wait_ns, 2, my_tag, away)) { alive = false; break; }
+                        continue;
+                    }
                 }
             }
             if (!okS) okS = try_load(srcS, k, lane, false, expS, S, curS);
             if (!okD) okD = try_load(srcD, k, lane, false, expD, D, curD);
             if (!okG) okG = try_load(recG, k, lane, false, p.seq0 + static_cast<uint32_t>(pG), G, curG);
-            if (wt.expired(p.status, p.wait_ns)) { alive = false; break; }
+            if (wt.expired(p.status, p.wait_ns, (!okS && cS) || (!okD && cD) ? 2 : 1, my_tag, okS ? expD : expS, okS ? dN : sN)) { alive = false; break; }
         }
         if (!alive) continue;
         ZP_MARK(1);
@@ -948,7 +1083,11 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
             if (isD ? cD : cS) continue;            // a chain node's side is computed by its chain warp
             const VecR A = vsel(isD, D, S), B = vsel(isD, S, D);
             ok &= update_endpoint(p, s, A, B, isD ? sN : dN, e, t, j, isD ? recD : recS, my_tag,
-                                  rcnt + (isD ? dN : sN), isD ? rwD : rwS, lane);
+                                  rcnt + (isD ? dN : sN), isD ? rwD : rwS, lane, stats);
+            if ((stats & 0xffffu) > 0xff00u || (stats >> 16) > 0xff00u) {      // the halves are 16 bits wide
+                if (lane == 0) { atomicAdd(p.status + 2, static_cast<int>(stats & 0xffffu)); atomicAdd(p.status + 1, static_cast<int>(stats >> 16)); }
+                stats = 0;
+            }
             ZP_MARK(2 + h);
         }
         if (!ok) { atomicExch(p.status, 1); continue; }
@@ -957,7 +1096,7 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
         while (!okG) {
             __nanosleep(64);
             okG = try_load(recG, k, lane, false, p.seq0 + static_cast<uint32_t>(pG), G, curG);
-            if (wt.expired(p.status, p.wait_ns)) break;
+            if (wt.expired(p.status, p.wait_ns, 4, my_tag, p.seq0 + static_cast<uint32_t>(pG), gN)) break;
         }
         if (!okG) continue;
         if (!sigG && neg_own && (flags & kFlagSignal) && lane == 0) atomicAdd(rcnt + gN, 1);

@@ -44,13 +44,20 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
     const int k = p.k;
     const uint32_t tag_base = p.seq0 + static_cast<uint32_t>(p.tag_offset);
     const int lg = p.world_log2, me = p.rank, pmask = (1 << lg) - 1, world = 1 << lg;
+    unsigned stats = 0;
     char *const my_mbox = p.mbox_peer[me] + static_cast<size_t>(p.mbox_parity) * p.mbox_half_bytes;
 
     for (;;) {
         uint32_t tk = 0;
         if (lane == 0) tk = atomicAdd(p.ticket, 1u) - p.ticket_base;
         tk = __shfl_sync(kFull, tk, 0);
-        if (tk >= total) break;
+        if (tk >= total) {
+            if (lane == 0 && stats) {
+                if (stats & 0xffffu) atomicAdd(p.status + 2, static_cast<int>(stats & 0xffffu));
+                if (stats >> 16) atomicAdd(p.status + 1, static_cast<int>(stats >> 16));
+            }
+            break;
+        }
         const int64_t li = tk / static_cast<uint32_t>(p.n_tppr);    // 32-bit division: items < 2^32
         const int j = tk - li * p.n_tppr;
         if (!((p.inst_mask >> j) & 1)) continue;
@@ -117,7 +124,7 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
             }
             if (dist > kNear) __nanosleep(backoff_ns(dist));
             else if ((!okS && !oS) || (!okD && !oD)) __nanosleep(100);   // waiting for a peer's push
-            if (wt.expired(p.status, p.wait_ns)) { alive = false; break; }
+            if (wt.expired(p.status, p.wait_ns, (!okS && !oS) || (!okD && !oD) ? 8 : 1, my_tag, 0)) { alive = false; break; }
         }
         if (!alive) continue;
         if (loop) D = vsel(true, S, S);
@@ -134,7 +141,11 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
                 if (!(isD ? oD : oS)) continue;
                 const VecR A = vsel(isD, D, S), B = vsel(isD, S, D);
                 ok &= update_endpoint(p, s, A, B, isD ? sN : dN, e, t, j, isD ? recD : recS, my_tag,
-                                      rcnt + (isD ? dN : sN), isD ? rwD : rwS, lane);
+                                      rcnt + (isD ? dN : sN), isD ? rwD : rwS, lane, stats);
+                if ((stats & 0xffffu) > 0xff00u || (stats >> 16) > 0xff00u) {
+                    if (lane == 0) { atomicAdd(p.status + 2, static_cast<int>(stats & 0xffffu)); atomicAdd(p.status + 1, static_cast<int>(stats >> 16)); }
+                    stats = 0;
+                }
             }
         }
         if (!ok) { atomicExch(p.status, 1); continue; }
@@ -142,7 +153,7 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
         while (!okG) {
             __nanosleep(64);
             okG = try_load<false>(recG, k, lane, pG < 0, p.seq0 + static_cast<uint32_t>(pG), G, curG);
-            if (wt.expired(p.status, p.wait_ns)) break;
+            if (wt.expired(p.status, p.wait_ns, 4, my_tag, 0)) break;
         }
         if (!okG) continue;
         if (!sigG && oG && (flags & kFlagSignal) && lane == 0) atomicAdd(rcnt + gN, 1);

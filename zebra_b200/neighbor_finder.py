@@ -73,20 +73,6 @@ class NeighborFinder:  # noqa: N801 (name kept from the reference)
         i = int(np.searchsorted(self.adj_ts[lo:hi], cut_time))
         return self.adj_node[lo:lo + i], self.adj_eidx[lo:lo + i], self.adj_ts[lo:lo + i]
 
-    def get_temporal_neighbor(self, source_nodes, timestamps, n_neighbors):
-        tmp = n_neighbors if n_neighbors > 0 else 1
-        neighbors = np.zeros((len(source_nodes), tmp), np.int32)
-        edge_times = np.zeros((len(source_nodes), tmp), np.float32)
-        edge_idxs = np.zeros((len(source_nodes), tmp), np.int32)
-        for i, (v, t) in enumerate(zip(source_nodes, timestamps)):
-            ngh, eid, ts = self.find_before(v, t)
-            if len(ngh) > 0 and n_neighbors > 0:
-                ngh, eid, ts = ngh[-n_neighbors:], eid[-n_neighbors:], ts[-n_neighbors:]
-                neighbors[i, n_neighbors - len(ngh):] = ngh
-                edge_idxs[i, n_neighbors - len(ngh):] = eid
-                edge_times[i, n_neighbors - len(ngh):] = ts
-        return neighbors, edge_idxs, edge_times
-
     # ---- the pruning-strategy query (util.py:185-276) ----
     def _query(self, source_nodes, timestamps, width, depth, alpha, beta, k, to_host=True):
         q = np.ascontiguousarray(source_nodes, dtype=np.int32)

@@ -5,7 +5,7 @@ partitioned by node id (node v lives on rank v & (world-1)); every rank streams 
 edge span through the same plan; the span kernel exchanges cross-shard endpoint vectors through
 peer-mapped mailboxes (NVLink stores issued by the kernel itself) and every owner writes its rows
 into the output region of every rank.  The result on each rank is byte-identical to the single-GPU
-`tppr_finder` (tests/test_gpu_sharded.py, tools/shard_check.py).
+`tppr_finder` (tests/test_gpu_sharded.py, tests/test_gpu_sharded_mp.py).
 
 Host-side plumbing only lives here: `torch.distributed` carries the 64-byte CUDA IPC handles and the
 barriers; there is no data-path collective.  The pure-host helpers (`owner_of`, `exchange_stats`,
