@@ -24,9 +24,11 @@ for betas in ([0.5], [0.95], [0.5, 0.95]):
     c = f.counters()
     pr = f.profile()
     names = ["claim+load", "wait", "upd_hot", "upd_2nd", "emit", "c.get+push", "c.prefetch", "c.update", "u.dup", "u.pos", "u.rank", "u.tie", "u.store"]
-    steps = max(c["chain_steps"] * len(betas), 1)
+    deg = np.bincount(np.concatenate([st.src, st.dst]))
+    steps = max(int(deg.max()) * len(betas), 1)            # chain marks are taken on the hottest chain only
     items = c["items"]
     print(f"{name} E={n} betas={betas} window={window}: {ms:.1f} ms = {n/ms/1e3:.2f} M edges/s  {c}")
     if pr.any():
-        print("   per chain step:", {nm: round(float(v) / steps, 1) for nm, v in zip(names, pr) if nm.startswith("c.")})
+        print(f"   hottest chain ({int(deg.max())} steps), per step:", {nm: round(float(v) / steps, 1) for nm, v in zip(names, pr) if nm.startswith("c.")})
+        print("   chain partner waits: steps that had to wait %.3f, polls per step %.2f" % (float(pr[14]) / steps, float(pr[13]) / steps))
         print("   per item      :", {nm: round(float(v) / items, 1) for nm, v in zip(names, pr) if not nm.startswith("c.")})

@@ -151,6 +151,8 @@ struct zebra_tppr {
     bool chains_enabled = true;
     int32_t max_chains = zebra::kMaxChains;
     std::vector<int32_t> chain_cnt;            // [num_nodes] scratch of the detection pass (zero between passes)
+    int32_t *smflag = nullptr;                 // device [2 * kSmSlots]: chain warps running per SM, ticket warps standing aside
+    bool sm_yield = true;                      // ZEBRA_SM_YIELD=0 switches the standing aside off
     uint32_t *dbg_owner = nullptr;             // debug (ZEBRA_DEBUG_ITEMS=1): who processed each item of the launch
     size_t dbg_cap = 0;
     bool dbg_items = false;
@@ -675,9 +677,13 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
                                                     sharded ? h->shard_max_blocks : h->max_blocks));
     if (blocks < 1) blocks = 1;
     if (chain_warps) {
-        // one block per (chain, instance): its warp 0 walks the chain, the others help; all resident
-        blocks = std::max(blocks, chain_warps);
-        if (chain_warps > h->max_blocks) return fail("%d chain blocks do not fit a resident grid of %d blocks", chain_warps, h->max_blocks);
+        // one block per (chain, instance): its warp 0 walks the chain, the others help; all resident, and
+        // always some blocks of ticket warps next to them (the chains wait for what those produce)
+        blocks = std::max(blocks, std::min(h->max_blocks, chain_warps + std::max(16, chain_warps)));
+        if (chain_warps + 8 > blocks) return fail("%d chain blocks do not fit a resident grid of %d blocks", chain_warps, h->max_blocks);
+        CU(cudaMemsetAsync(h->smflag, 0, 2 * zebra::kSmSlots * sizeof(int32_t), st));
+        p.smflag = h->smflag;
+        p.max_yield = h->sm_yield ? std::max(0, (blocks - chain_warps) * zebra::kWarpsPerBlock - 256) : 0;
     }
     if (sharded) {
         if (m > h->max_window_edges) return fail("sharded launch of %lld edges exceeds the mailbox window (%lld)", (long long)m, (long long)h->max_window_edges);
@@ -877,6 +883,8 @@ int zebra_tppr_create(zebra_tppr_t **out, int64_t num_nodes, int32_t k, int32_t 
     }
     CU(cudaMalloc(&h->cprog, sizeof(uint32_t) * zebra::kMaxChains * zebra::kMaxInst));
     CU(cudaMemset(h->cprog, 0, sizeof(uint32_t) * zebra::kMaxChains * zebra::kMaxInst));
+    CU(cudaMalloc(&h->smflag, 2 * zebra::kSmSlots * sizeof(int32_t)));
+    CU(cudaMemset(h->smflag, 0, 2 * zebra::kSmSlots * sizeof(int32_t)));
     CU(cudaMalloc(&h->ticket, sizeof(uint32_t)));
     CU(cudaMemset(h->ticket, 0, sizeof(uint32_t)));
     CU(cudaMalloc(&h->status, kStatusWords * sizeof(int32_t)));
@@ -894,6 +902,7 @@ int zebra_tppr_create(zebra_tppr_t **out, int64_t num_nodes, int32_t k, int32_t 
         h->max_chains = std::max(0, std::min(atoi(e), zebra::kMaxChains));
         h->chains_enabled = h->max_chains > 0;
     }
+    if (const char *e = getenv("ZEBRA_SM_YIELD")) h->sm_yield = atoi(e) != 0;
     if (const char *e = getenv("ZEBRA_DEBUG_ITEMS")) h->dbg_items = atoi(e) != 0;
     if (const char *e = getenv("ZEBRA_WAIT_TIMEOUT_MS")) h->wait_ns = static_cast<unsigned long long>(std::max(1, atoi(e))) * 1000000ull;
     *out = h;
@@ -928,6 +937,7 @@ int zebra_tppr_destroy(zebra_tppr_t *h)
     if (h->rcnt) cudaFree(h->rcnt);
     if (h->cmbox) cudaFree(h->cmbox);
     if (h->cprog) cudaFree(h->cprog);
+    if (h->smflag) cudaFree(h->smflag);
     if (h->dbg_owner) cudaFree(h->dbg_owner);
     for (auto d : h->decay) if (d) cudaFree(d);
     if (h->ticket) cudaFree(h->ticket);

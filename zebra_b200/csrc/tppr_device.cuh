@@ -27,9 +27,11 @@ namespace zebra {
 #ifdef ZEBRA_PROFILE
 #define ZP_DECL long long zp_t0 = clock64(), zp_t1
 #define ZP_MARK(slot) do { zp_t1 = clock64(); if (lane == 0) atomicAdd(reinterpret_cast<unsigned long long *>(p.prof) + (slot), static_cast<unsigned long long>(zp_t1 - zp_t0)); zp_t0 = zp_t1; } while (0)
+#define ZP_MARK_IF(c, slot) do { zp_t1 = clock64(); if ((c) && lane == 0) atomicAdd(reinterpret_cast<unsigned long long *>(p.prof) + (slot), static_cast<unsigned long long>(zp_t1 - zp_t0)); zp_t0 = zp_t1; } while (0)
 #else
 #define ZP_DECL
 #define ZP_MARK(slot)
+#define ZP_MARK_IF(c, slot)
 #endif
 
 constexpr int kMaxInst = 8;
@@ -58,6 +60,7 @@ constexpr int kFlagSrcChainShift = 8, kFlagDstChainShift = 13;   // 5 bits each:
 // computes).  Every version is still published to the node's table record, so negative-sample readers
 // and later launches see exactly what they saw before.
 constexpr int kMaxChains = 24;
+constexpr int kSmSlots = 512;            // SM ids are below this (148 on B200)
 struct alignas(16) ChainStep {
     int32_t edge;        // index of the edge in the span the tags are drawn from (tag = seq0 + edge)
     int32_t peer;        // the other endpoint
@@ -138,6 +141,8 @@ struct SpanParams {
     const ChainStep *csteps;
     char *cmbox;                                    // [(cidx - cidx_base) * n_tppr + j][2 sides] records
     int32_t cidx_base, n_chains;
+    int32_t *smflag;                                // [kSmSlots] running chain warps per SM, [kSmSlots] ticket warps yielding
+    int32_t max_yield;                              // ticket warps that may yield at the same time
     uint32_t *dbg_owner;                            // debug (ZEBRA_DEBUG_ITEMS=1): [edge][instance] who processed the item
     uint32_t *cprog;                                // [chain][instance] tag of the step the chain warp is working on
     unsigned long long wait_ns;                     // dependency-wait time-out (globaltimer)
@@ -878,8 +883,14 @@ __device__ __noinline__ void run_chain(const SpanParams &p, WarpScratch &s, int 
             const uint32_t expect = p.seq0 + static_cast<uint32_t>(prev_peer);
             uint32_t cur;
             bool ok = check_raw(raw, lane, prev_peer < 0, expect, B, cur);
+#ifdef ZEBRA_PROFILE
+            if (!ok && lane == 0 && q == 0) atomicAdd(p.prof + 14, 1ull);      // partner record not there when the step began
+#endif
             Waiter wt;
             while (!ok) {
+#ifdef ZEBRA_PROFILE
+                if (lane == 0 && q == 0) atomicAdd(p.prof + 13, 1ull);
+#endif
                 if (wt.expired(p.status, p.wait_ns, 7, tag, expect, peer)) { alive = false; break; }
                 __nanosleep(40);
                 ok = try_load(recP, k, lane, prev_peer < 0, expect, B, cur);
@@ -888,14 +899,14 @@ __device__ __noinline__ void run_chain(const SpanParams &p, WarpScratch &s, int 
             if (alive) push_vector<false>(my_slot, k, H, tag, lane);
         }
         if (!alive) return;
-        ZP_MARK(5);
+        ZP_MARK_IF(q == 0, 5);
         // next step's partner record on its way while this step computes
         if (x + 1 < c.end) {
             const uint32_t nfl = __shfl_sync(kFull, w1, 5);
             const int npeer = static_cast<int>(__shfl_sync(kFull, w1, 1));
             raw = load_raw(table + static_cast<size_t>((nfl & (kStepLoop | kStepPeerChain)) ? c.node : npeer) * p.stride, k, lane);
         }
-        ZP_MARK(6);
+        ZP_MARK_IF(q == 0, 6);
         VecR Hn;
         const bool ok = update_endpoint<true>(p, s, H, B, peer, e_new, t_new, j, recH, tag, rcntH, rthr, lane, stats, &Hn);
         if (!ok) { atomicExch(p.status, 1); return; }
@@ -905,7 +916,7 @@ __device__ __noinline__ void run_chain(const SpanParams &p, WarpScratch &s, int 
         }
         H = Hn;
         w0 = w1; w1 = w2;
-        ZP_MARK(7);
+        ZP_MARK_IF(q == 0, 7);
     }
 }
 
@@ -925,20 +936,34 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
     // steps h-1, h-1+7, ...) and do everything of such an edge that is not the chain node's own update:
     // the partner's update and the rows.  Ticket warps skip edges with a chain endpoint, so the ticket
     // front never queues up behind a chain; when a block's chain is done all its warps draw tickets.
+    // A chain warp is one warp's dependent instruction stream: every issue slot and instruction-cache line
+    // it shares with other warps lengthens the chain.  While a chain warp runs on an SM, the TICKET warps
+    // of the other block resident there stand aside (they hold no work while they do); at most max_yield
+    // ticket warps stand aside at any time, so ticket work always has takers.
     unsigned stats = 0;
     int hx = 0, hx_end = 0, hj = 0;
+    unsigned smid = 0;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    smid &= kSmSlots - 1;
+    bool may_yield = p.n_chains > 0 && p.max_yield > 0;
+    unsigned claims = 0;
     if (p.n_chains > 0 && blockIdx.x < static_cast<unsigned>(p.n_chains * p.n_tppr)) {
         const int q = blockIdx.x / p.n_tppr;
         hj = blockIdx.x - q * p.n_tppr;
+        may_yield = false;
         if ((p.inst_mask >> hj) & 1) {
-            if ((threadIdx.x >> 5) == 0) run_chain(p, s, q, hj, lane, stats);
-            else { hx = p.chains[q].begin + (threadIdx.x >> 5) - 1; hx_end = p.chains[q].end; }
+            if ((threadIdx.x >> 5) == 0) {
+                if (lane == 0) atomicAdd(p.smflag + smid, 1);
+                run_chain(p, s, q, hj, lane, stats);
+                if (lane == 0) atomicSub(p.smflag + smid, 1);
+            } else { hx = p.chains[q].begin + (threadIdx.x >> 5) - 1; hx_end = p.chains[q].end; }
         }
     }
 
     for (;;) {
         int64_t i;
         int j;
+        bool from_ticket = false;
         if (hx < hx_end) {
             // helper: the next edge of the chain that is this warp's turn
             const ChainStep *st = p.csteps + hx;
@@ -949,6 +974,19 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
             i = static_cast<int64_t>(__ldg(&st->edge)) - p.tag_offset;
             j = hj;
         } else {
+            if (may_yield && (claims < 4 || (claims & 15) == 0)) {
+                if (*reinterpret_cast<volatile int32_t *>(p.smflag + smid) > 0) {
+                    int y = 0;
+                    if (lane == 0) y = atomicAdd(p.smflag + kSmSlots, 1);
+                    y = __shfl_sync(kFull, y, 0);
+                    if (y < p.max_yield) {
+                        while (*reinterpret_cast<volatile int32_t *>(p.smflag + smid) > 0) __nanosleep(2000);
+                    }
+                    if (lane == 0) atomicSub(p.smflag + kSmSlots, 1);
+                    may_yield = false;          // the chains of this SM are done (or the quota was full)
+                }
+            }
+            ++claims;
             uint32_t tk = 0;
             if (lane == 0) tk = atomicAdd(p.ticket, 1u) - p.ticket_base;
             tk = __shfl_sync(kFull, tk, 0);
@@ -961,7 +999,7 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
             }
             i = tk / static_cast<uint32_t>(p.n_tppr);     // 32-bit division: items < 2^32
             j = static_cast<int>(tk - i * p.n_tppr);
-            if (p.flags[i] & (kFlagSrcChain | kFlagDstChain)) continue;   // a chain block's helpers take it
+            from_ticket = true;
         }
         ZP_DECL;
         if (p.dbg_owner && lane == 0) {
@@ -974,28 +1012,34 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
                 w.log_wait(p.status, 99, tag_base + static_cast<uint32_t>(i), old, static_cast<int32_t>(me));
             }
         }
+        // the whole edge record in one batch of independent loads (one memory round trip), before any branch
+        // that depends on it; a load issued after the wait below would sit on the dependency chain
         const int sN = p.src[i], dN = p.dst[i];
+        const int gN_raw = p.neg[i];
+        const uint32_t flags = p.flags[i];
+        const int32_t pS = p.prev_s[i], pD_raw = p.prev_d[i], pG_raw = p.prev_n[i];
+        const double t = p.ts[i];
+        const int e = p.eidx[i];
+        const uint32_t rwS = p.rthr_s[i], rwD_raw = p.rthr_d[i];
+        const int32_t ci = p.cidx[i];
         const bool has_neg = p.rows_per_edge == 3;
-        const int gN = has_neg ? p.neg[i] : sN;
+        const int gN = has_neg ? gN_raw : sN;
         const bool loop = sN == dN;
         const bool neg_own = has_neg && gN != sN && gN != dN;
-        const uint32_t flags = p.flags[i];
         int32_t *rcnt = p.rcnt[j];
 
+        if (from_ticket && (flags & (kFlagSrcChain | kFlagDstChain))) continue;   // a chain block's helpers take it
         if (!((p.inst_mask >> j) & 1)) continue;   // instance not selected: its tables are not touched
         // update-only span and every side of the edge belongs to a chain warp: nothing to do here
         if (p.rows_per_edge == 0 && (flags & kFlagSrcChain) && (loop || (flags & kFlagDstChain))) continue;
 
-        const int32_t pS = p.prev_s[i], pD = loop ? -1 : p.prev_d[i], pG = neg_own ? p.prev_n[i] : -1;
+        const int32_t pD = loop ? -1 : pD_raw, pG = neg_own ? pG_raw : -1;
+        const uint32_t rwD = loop ? 0u : rwD_raw;
         char *table = p.tables[j];
         char *recS = table + static_cast<size_t>(sN) * p.stride;
         char *recD = table + static_cast<size_t>(dN) * p.stride;
         const char *recG = table + static_cast<size_t>(gN) * p.stride;
         const uint32_t my_tag = tag_base + static_cast<uint32_t>(i);
-        // the rest of the edge record now: a load issued after the wait would sit on the chain
-        const double t = p.ts[i];
-        const int e = p.eidx[i];
-        const uint32_t rwS = p.rthr_s[i], rwD = loop ? 0u : p.rthr_d[i];
         // an endpoint that is a chain node: its OLD vector arrives in the item's mailbox slot, tagged with
         // this edge, and its update is the chain warp's business
         const bool cS = (flags & kFlagSrcChain) != 0, cD = !loop && (flags & kFlagDstChain) != 0;
@@ -1003,7 +1047,6 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
         uint32_t expS = p.seq0 + static_cast<uint32_t>(pS), expD = p.seq0 + static_cast<uint32_t>(pD);
         bool anyS = pS < 0, anyD = pD < 0;
         if (cS | cD) {
-            const int32_t ci = p.cidx[i];
             if (cS) { srcS = chain_slot(p, ci, j, 0); expS = my_tag; anyS = false; }
             if (cD) { srcD = chain_slot(p, ci, j, 1); expD = my_tag; anyD = false; }
         }
