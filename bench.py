@@ -1,11 +1,12 @@
 """bench.py — T-PPR maintenance throughput on B200 (see DESIGN.md "Measurement").
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload NAME]
 
-Workload (config.workload): BASELINE.json configs[4], the stream the metric's target is quoted on —
-Wiki-Talk-shaped synthetic unipartite stream (1,140,149 nodes, 7,833,140 edges), streaming T-PPR
-with negatives, topk=20, two (alpha,beta) pairs, batches of 200 edges.  One step = reset the tables
-and stream the whole span once.
+Workload (config.workload): by default BASELINE.json configs[4], the stream the metric's target is
+quoted on — Wiki-Talk-shaped synthetic unipartite stream (1,140,149 nodes, 7,833,140 edges), streaming
+T-PPR with negatives, topk=20, two (alpha,beta) pairs, batches of 200 edges.  `--workload` selects the
+shape of another BASELINE config (wikipedia, reddit, mooc, superuser) with the same line format.  One
+step = reset the tables and stream the whole span once.
 
   value   edges/s with the span resident in HBM (a "plan": edge records + dependency tickets uploaded
           once), outputs written to HBM, timed with CUDA events on the launching stream.
@@ -34,6 +35,7 @@ sys.path.insert(0, ROOT)
 K, BS = 20, 200
 ALPHAS, BETAS = [0.1, 0.1], [0.5, 0.95]
 WORKLOAD = "wikitalk"
+WORKLOADS = ("wikipedia", "reddit", "mooc", "superuser", "wikitalk")      # BASELINE.json configs[0..4] shapes
 METRIC, UNIT = "tppr_streaming_edges_per_sec", "edges/s"
 
 
@@ -153,10 +155,73 @@ def cpu_port_throughput(st, neg, sample_edges, threads):
     return n / dt, n, dt
 
 
+_NUMBA_SNIPPET = r"""
+import json, os, sys, time
+import numpy as np
+ref, root, name, n, bs = sys.argv[1], sys.argv[2], sys.argv[3], int(sys.argv[4]), int(sys.argv[5])
+sys.dont_write_bytecode = True
+sys.path.insert(0, root)
+from zebra_b200 import synth
+st = synth.make_stream(name, n_edges=n)
+neg = synth.make_negatives(st, bs)
+sys.path.insert(0, ref)
+t0 = time.perf_counter()
+from utils.util import tppr_finder                      # the reference's own numba jitclass, unmodified
+f = tppr_finder(st.shape.table_nodes, 20, 2, [0.1, 0.1], [0.5, 0.95])
+def batch(lo, hi):
+    return (np.concatenate([st.src[lo:hi], st.dst[lo:hi], neg[lo:hi]]).astype(np.int32),
+            np.concatenate([st.ts[lo:hi]] * 3), st.eidx[lo:hi].astype(np.int64))
+f.streaming_topk(*batch(0, bs))                        # compiles this argument-type signature
+compile_s = time.perf_counter() - t0
+f.reset_tppr()
+t = time.perf_counter()
+for lo in range(0, n, bs):
+    f.streaming_topk(*batch(lo, min(n, lo + bs)))
+dt = time.perf_counter() - t
+print(json.dumps({"value": n / dt, "edges": n, "seconds": dt, "compile_s": compile_s}))
+"""
+
+
+def numba_reference_throughput(sample_edges, timeout_s=240):
+    """The reference ITSELF (LuckyLYM/Zebra utils/util.py:391-576, numba jitclass, single-threaded by
+    construction) on a prefix of the workload: imported unmodified from baseline/_ref (a copy of the
+    reference tree made by __graft_entry__.build()), compiled once, then timed with perf_counter around
+    the streaming_topk calls only.  Runs in a subprocess so that a missing numba
+    or a slow compile cannot take the bench down; returns a dict for the JSON line."""
+    ref = os.path.join(ROOT, "baseline", "_ref")
+    if not os.path.exists(os.path.join(ref, "utils", "util.py")):
+        return {"unavailable": "baseline/_ref missing (made by __graft_entry__.build() where /root/reference exists)"}
+    try:
+        r = subprocess.run([sys.executable, "-c", _NUMBA_SNIPPET, ref, ROOT, WORKLOAD, str(sample_edges), str(BS)],
+                           capture_output=True, text=True, timeout=timeout_s,
+                           env=dict(os.environ, PYTHONDONTWRITEBYTECODE="1", NUMBA_NUM_THREADS="1"))
+        if r.returncode != 0:
+            return {"unavailable": (r.stderr.strip().splitlines() or ["numba run failed"])[-1][:200]}
+        d = json.loads(r.stdout.strip().splitlines()[-1])
+        return {"value": d["value"], "unit": UNIT, "cores": f"1 of {os.cpu_count()}", "kind": "reference",
+                "sample": f"first {d['edges']} edges of the workload, bs={BS}, with negatives, two (alpha,beta) instances "
+                          f"({d['seconds']:.1f} s timed after a {d['compile_s']:.0f} s import + numba compile)"}
+    except subprocess.TimeoutExpired:
+        return {"unavailable": f"numba reference did not finish within {timeout_s} s"}
+    except Exception as ex:  # noqa: BLE001
+        return {"unavailable": f"{type(ex).__name__}: {ex}"[:200]}
+
+
+def workload_text(st, world=1):
+    if world > 1:
+        return (f"{world} {WORKLOAD}-shaped communities merged into one stream, streaming T-PPR topk={K}, alpha {ALPHAS}, "
+                f"beta {BETAS}, bs={BS}, negatives included")
+    return (f"{WORKLOAD}-shaped synthetic stream ({st.shape.n_nodes} nodes, {st.shape.n_edges} edges), streaming T-PPR "
+            f"topk={K}, alpha {ALPHAS}, beta {BETAS}, bs={BS}, negatives included")
+
+
 def run_reference(args):
-    """--impl reference: the reference's own CPU implementation of the path.  The reference is
-    Python + numba and cannot travel to the GPU box, so this times oracle/ (its C port, validated
-    bit-for-bit against recordings of the reference) on the box's host cores."""
+    """--impl reference: the reference's own CPU implementation of the path on the box's host cores.
+    The line's `value` is oracle/ (the C port of the reference's single-threaded numba path, validated
+    bit-for-bit against recordings of the reference; one thread per (alpha,beta) instance — the only
+    parallelism the algorithm admits), because the numba original needs ~10 minutes for one pass over
+    this workload; the numba original itself is timed on a 50 K-edge prefix of the same workload and
+    reported next to it (cpu_baseline.reference_numba)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -167,25 +232,32 @@ def run_reference(args):
         # same workload as our arm at this N: `world` communities merged into one stream
         from zebra_b200 import synth
         st, neg = synth.make_communities(WORKLOAD, world, BS, n_edges=-(-sample // world))
+        full = synth.SHAPES[WORKLOAD]
     else:
-        st, neg = load_workload(n_edges=min(sample, 7_833_140))
-    vals = []
+        from zebra_b200 import synth
+        full = synth.SHAPES[WORKLOAD]
+        st, neg = load_workload(n_edges=min(sample, full.n_edges))
+    sample = min(sample, st.n_edges)
     for _ in range(max(1, min(args.warmup, 1))):
         cpu_port_throughput(st, neg, min(sample, 100_000), threads)
-    t_all = 0.0
+    vals, t_all = [], 0.0
     for _ in range(args.steps):
         v, n, dt = cpu_port_throughput(st, neg, sample, threads)
         vals.append(v); t_all += dt
     value = float(np.mean(vals))
+    numba = numba_reference_throughput(args.numba_sample_edges) if not args.no_numba else {"unavailable": "--no-numba"}
+    import dataclasses
+    st_full = dataclasses.replace(st, shape=full) if world == 1 else st
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * t_all / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": (f"{world} {WORKLOAD}-shaped communities merged into one stream" if world > 1 else
-                                f"{WORKLOAD}-shaped synthetic stream") + f", streaming T-PPR topk={K}, alpha {ALPHAS}, beta {BETAS}, bs={BS}",
-                   "sample": f"first {sample} edges per step"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
-                         "sample": f"first {sample} edges of the workload, bs={BS}, with negatives; one thread per (alpha,beta) instance"},
+        "config": {"workload": workload_text(st_full, world),
+                   "sample": f"each step streams the first {sample} edges of that workload (the C port needs ~26 s, the numba "
+                             f"original ~10 min for all of it)"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "of_cores": os.cpu_count(), "kind": "port",
+                         "sample": f"first {sample} edges of the workload, bs={BS}, with negatives; one thread per (alpha,beta) instance",
+                         "reference_numba": numba},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -214,12 +286,57 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
         dist.barrier()
         torch.cuda.synchronize()
 
+    def parity_check(f, plan, st, neg):
+        """Before anything is timed: the rows THIS rank is delivered for the first batches of the stream
+        (its batches b % N == rank, stored by their owners over NVLink) against the oracle, bit for bit.
+        The oracle runs on node ids compacted to the prefix (its tables would need GBs otherwise)."""
+        import oracle
+        nb = min(plan.n_batches, args.parity_batches)
+        if nb <= 0:
+            return {"edges": 0, "ok": True}
+        n = min(st.n_edges, nb * BS)
+        uniq = np.unique(np.concatenate([st.src[:n], st.dst[:n], neg[:n]]))
+        back = np.concatenate([[0], uniq]).astype(np.int32)                 # compact id -> node id (0 = padding)
+        comp = lambda a: (np.searchsorted(uniq, a) + 1).astype(np.int32)   # noqa: E731
+        cs, cd, cn = comp(st.src[:n]), comp(st.dst[:n]), comp(neg[:n])
+        o = oracle.OracleFinder(len(uniq) + 1, K, len(ALPHAS), ALPHAS, BETAS)
+        f.reset_tppr()
+        barrier()
+        ok, checked = True, 0
+        for b0 in range(0, nb, window):
+            cnt_b = min(window, nb - b0)
+            plan.run(b0, cnt_b, window, out_slots=window)
+            barrier()                                     # every owner's stores have landed
+            host = f.out[: cnt_b * slot].cpu().numpy()
+            for b in range(b0, b0 + cnt_b):
+                lo, hi = b * BS, min(n, (b + 1) * BS)
+                ref = o.streaming_topk(np.concatenate([cs[lo:hi], cd[lo:hi], cn[lo:hi]]), np.concatenate([st.ts[lo:hi]] * 3),
+                                       st.eidx[lo:hi])
+                if b % world != rank:
+                    continue
+                rows = 3 * (hi - lo)
+                buf = host[(b - b0) * slot: (b - b0) * slot + len(ALPHAS) * 16 * rows * K].view(np.int32).reshape(len(ALPHAS), 4, rows, K)
+                for j in range(len(ALPHAS)):
+                    ok &= bool(np.array_equal(buf[j, 0], back[ref[0][j]]) and np.array_equal(buf[j, 1], ref[1][j])
+                               and np.array_equal(buf[j, 2].view(np.float32), ref[2][j]) and np.array_equal(buf[j, 3].view(np.float32), ref[3][j]))
+                checked += hi - lo
+            barrier()                                     # nobody overwrites the slots before everybody has read
+        f.sync_check()
+        t = torch.tensor([1.0 if ok else 0.0, float(checked)], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        all_ok = bool(t[0] > 0.5)
+        if not all_ok:
+            raise SystemExit(f"rank {rank}: sharded rows differ from the oracle in the first {n} edges (parity check before timing)")
+        return {"edges": n, "batches": nb, "ok": True, "rows_checked_per_rank_min": int(t[1]) * 3,
+                "what": "every rank compared the rows delivered to it (batches b % N == rank) with the oracle, bit for bit, before timing"}
+
     def measure(st, neg, sampler=None, e2e=True):
         E, N = st.n_edges, st.shape.table_nodes
         # rows of batch b are delivered to rank b % N only: each data-parallel rank consumes its own batches
         f = create_sharded(N, K, len(ALPHAS), ALPHAS, BETAS, window * BS, 2 * window * slot, row_mode=1)
         plan = f.make_plan(st.src, st.dst, neg, st.ts, st.eidx, BS)
         n_win = -(-plan.n_batches // window)
+        parity = parity_check(f, plan, st, neg)
 
         def step():
             f.reset_tppr()                       # no barrier needed: records are touched by their owner only
@@ -242,7 +359,7 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
         ms = ev[0].elapsed_time(ev[1])
         launches = f.counters()["launches"] - l0
         res = {"E": E, "N": N, "ms": ms, "launches": launches, "n_launch": n_win, "n_batches": plan.n_batches,
-               "record_bytes": f._record_bytes}
+               "record_bytes": f._record_bytes, "parity": parity}
         pb = torch.tensor([float(plan.device_bytes)], dtype=torch.float64, device=dev)
         dist.all_reduce(pb)                       # H2D of a plan, summed over the ranks
         res["plan_bytes"] = int(pb[0])
@@ -314,6 +431,23 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
         st1, neg1 = load_workload(n_edges=args.edges)
         strong = measure(st1, neg1, e2e=False)
         strong["exchange"] = exchange_stats(st1.src, st1.dst, neg1, world, K, len(ALPHAS), row_mode=1)
+        # the same stream on ONE GPU (rank 0, single-GPU kernel with chain warps), measured in this very run
+        if rank == 0:
+            from zebra_b200.finder import tppr_finder
+            f1 = tppr_finder(st1.shape.table_nodes, K, len(ALPHAS), ALPHAS, BETAS, device=dev)
+            p1 = f1.make_plan(st1.src, st1.dst, neg1, st1.ts, st1.eidx, BS)
+            w1 = args.batches_per_launch
+            o1 = p1.alloc_out(w1)
+            best = 1e30
+            for _ in range(2):
+                f1.reset_tppr()
+                p1.run(0, p1.n_batches, w1, out=o1, out_slots=w1)
+                f1.sync_check()
+                best = min(best, f1.last_kernel_ms())
+            strong["single_gpu_ms"] = best
+            p1.close()
+            del f1, o1
+        barrier()
     if rank != 0:
         return
     peak, peak_src = peaks()
@@ -349,9 +483,14 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
                      "bytes_per_edge": bytes_per_edge(), "launch_ms": per_launch_ms},
     }
     if strong is not None:
+        sv = strong["E"] * args.steps / (strong["ms"] * 1e-3)
+        s1 = strong["E"] / (strong["single_gpu_ms"] * 1e-3)
         line["strong"] = {"what": f"the N=1 workload ({strong['E']} edges, one community) node-sharded over {world} GPUs",
-                          "value": strong["E"] * args.steps / (strong["ms"] * 1e-3), "unit": UNIT,
-                          "ms_per_step": strong["ms"] / args.steps, "exchange": strong["exchange"]}
+                          "value": sv, "unit": UNIT, "ms_per_step": strong["ms"] / args.steps,
+                          "single_gpu_value": s1, "speedup_vs_single_gpu": sv / s1,
+                          "target": "north_star: >= 5x at 8 GPUs; bounded by the hottest node's serial chain (DESIGN.md 7)",
+                          "parity_check": strong["parity"], "exchange": strong["exchange"]}
+    line["parity_check"] = weak["parity"]
     print(json.dumps(line), flush=True)
 
 
@@ -409,6 +548,26 @@ def run_ours(args):
     launches = f.counters()["launches"] - l0
     tie_prunes = f.counters()["tie_prunes"]
     clocks = sampler.stop() if rank == 0 else None
+    cnt = f.counters()
+    deg = np.bincount(np.concatenate([st.src, st.dst]), minlength=N)
+    hub_edges = int(deg.max())
+    chain_info = {"edges_with_a_chain_endpoint": cnt["chain_items"], "chain_steps": cnt["chain_steps"],
+                  "what": "nodes whose edges are walked by a resident warp with the vector in registers (DESIGN.md 4.1)"}
+    # the same pass with ties in insertion order (zebra_tppr_set_tie_mode 1, "ties within tolerance"): no replay of
+    # numba's argsort; reported beside the exact default
+    stable_ms = None
+    if not args.no_stable:
+        f2 = tppr_finder(N, K, len(ALPHAS), ALPHAS, BETAS, device=dev, tie_mode="stable")
+        p2 = f2.make_plan(st.src, st.dst, neg, st.ts, st.eidx, BS)
+        best = 1e30
+        for _ in range(2):
+            f2.reset_tppr()
+            p2.run(0, p2.n_batches, window, out=out, out_slots=window)
+            f2.sync_check()
+            best = min(best, f2.last_kernel_ms())
+        stable_ms = best
+        p2.close()
+        del f2
 
     # ---- e2e: host numpy arrays in, host numpy arrays out, for EVERY batch of the workload ----
     # tppr_finder.stream_epoch = the per-batch streaming_topk results of the whole span, pipelined:
@@ -468,12 +627,14 @@ def run_ours(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"{WORKLOAD}-shaped synthetic stream ({st.shape.n_nodes} nodes, {E} edges/GPU), streaming T-PPR "
-                                   f"topk={K}, alpha {ALPHAS}, beta {BETAS}, bs={BS}, negatives included",
+            "config": {"workload": workload_text(st),
+                       "edges_per_gpu": E,
                        "step": "reset tables + stream the whole span once",
                        "batches_per_launch": window, "parallelism": f"replicas x{world}" if world > 1 else "single GPU",
                        "l2": f"tables {len(ALPHAS) * N * f._record_bytes / 1e6:.0f} MB + outputs exceed the 126 MB L2 (inputs larger than L2)",
-                       "tie_path_prunes_last_step": tie_prunes},
+                       "tie_mode": "exact (numba argsort order replayed inside groups of equal scores; bit-identical to the reference)",
+                       "tie_path_prunes_last_step": tie_prunes,
+                       "chain_nodes": chain_info},
             "e2e": {"value": world * e2e_edges * args.steps / e2e_s, "unit": UNIT,
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "step": f"all {plan.n_batches} batches through tppr_finder.stream_epoch (host numpy in, host numpy out per "
@@ -486,8 +647,16 @@ def run_ours(args):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "kernel": "tppr_span_kernel",
                          "bytes_per_edge": bytes_per_edge(), "algorithmic_bytes_per_launch": alg_per_launch,
-                         "launch_ms": per_launch_ms},
+                         "launch_ms": per_launch_ms,
+                         # what actually bounds this stream: the hottest node's edges are strictly sequential
+                         "critical_path": {"hottest_node_edges": hub_edges, "us_per_step": 1e3 * (ms / args.steps) / max(hub_edges, 1),
+                                           "what": "time per pass / edges of the hottest node: an upper bound on the latency of one "
+                                                   "step of its dependency chain (every update needs the previous one)"}},
         }
+        if stable_ms is not None:
+            line["tie_modes"] = {"exact": {"value": value / world, "ms_per_step": ms / args.steps},
+                                 "stable": {"value": E / (stable_ms * 1e-3), "ms_per_step": stable_ms,
+                                            "what": "equal scores keep insertion order (oracle tie_mode 1, tests/test_gpu_ties.py)"}}
         if world == 1 and not args.no_flat:
             # the same kernel on a hub-free stream of the same size class (uniform endpoints): no long
             # dependency chain, i.e. the kernel's throughput regime, where HBM is the relevant roofline
@@ -510,8 +679,10 @@ def run_ours(args):
                 "edges_per_sec": nf / (best * 1e-3), "achieved": fa, "frac": fa / peak}
         if not args.no_cpu and world == 1:
             v, n, dt = cpu_port_throughput(st, neg, args.cpu_sample_edges, 1)
-            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
-                                    "sample": f"first {n} edges of the workload, bs={BS}, with negatives ({dt:.1f} s)"}
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": 1, "of_cores": os.cpu_count(), "kind": "port",
+                                    "sample": f"first {n} edges of the workload, bs={BS}, with negatives ({dt:.1f} s)",
+                                    "reference_numba": (numba_reference_throughput(args.numba_sample_edges) if not args.no_numba
+                                                        else {"unavailable": "--no-numba"})}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -524,10 +695,15 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--edges", type=int, default=None, help="truncate the stream (debug only)")
-    ap.add_argument("--batches-per-launch", type=int, default=64)
+    ap.add_argument("--workload", default="wikitalk", choices=WORKLOADS, help="shape of a BASELINE.json config (default: configs[4])")
+    ap.add_argument("--batches-per-launch", type=int, default=256)
+    ap.add_argument("--numba-sample-edges", type=int, default=50_000, help="prefix streamed through the reference's own numba finder")
+    ap.add_argument("--no-numba", action="store_true")
+    ap.add_argument("--no-stable", action="store_true", help="skip the tie_mode=stable leg")
     ap.add_argument("--shard-batches-per-launch", type=int, default=256, help="N>1: batches per launch PER GPU")
+    ap.add_argument("--parity-batches", type=int, default=250, help="N>1: batches checked against the oracle before timing")
     ap.add_argument("--e2e-batches", type=int, default=2000)
-    ap.add_argument("--e2e-window", type=int, default=128)
+    ap.add_argument("--e2e-window", type=int, default=256)
     ap.add_argument("--cpu-sample-edges", type=int, default=1_000_000)
     ap.add_argument("--ref-sample-edges", type=int, default=1_000_000)
     ap.add_argument("--traffic", type=float, default=None, help="ncu dram bytes per launch, if captured")
@@ -537,6 +713,8 @@ def main():
                     help="N>1: node-sharded state with in-kernel NVLink exchange (default), or independent replicas")
     ap.add_argument("--no-strong", action="store_true", help="N>1: skip the strong-scaling leg (same stream as N=1, sharded)")
     args = ap.parse_args()
+    global WORKLOAD
+    WORKLOAD = args.workload
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -190,6 +190,12 @@ int zebra_tppr_shard_reset(zebra_tppr_t *h, void *stream);
  * of batch b go to rank b & (world-1) only (same slot offset), the other ranks' slots of that batch
  * stay untouched.  Same setting on every rank. */
 int zebra_tppr_shard_row_mode(zebra_tppr_t *h, int32_t mode);
+/* How a prune orders candidates whose fp64 scores are exactly equal (utils/util.py:555, np.argsort):
+ * 0 (default) = the order numba's quicksort gives, replayed exactly, so results are bit-identical to
+ * the reference; 1 = insertion order (a stable sort).  Mode 1 differs from the reference only in which
+ * of several exactly tied candidates is kept / in their slot order ("ties within tolerance" of the
+ * acceptance criteria) and skips the replay, the most expensive part of a tie-heavy update. */
+int zebra_tppr_set_tie_mode(zebra_tppr_t *h, int32_t mode);
 /* Caps the persistent grid (blocks of 8 warps); lets two ranks share one GPU in tests. */
 int zebra_tppr_set_max_blocks(zebra_tppr_t *h, int32_t blocks);
 

@@ -11,7 +11,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def test_reference_arm_prints_the_contract_line():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "1",
-                        "--edges", "60000", "--ref-sample-edges", "20000"], capture_output=True, text=True, timeout=600, cwd=ROOT)
+                        "--edges", "60000", "--ref-sample-edges", "20000", "--numba-sample-edges", "2000"], capture_output=True, text=True, timeout=600, cwd=ROOT)
     assert r.returncode == 0, r.stderr[-2000:]
     lines = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
     assert len(lines) == 1
@@ -22,6 +22,11 @@ def test_reference_arm_prints_the_contract_line():
     assert d["gpu_launches"] == 0
     cb = d["cpu_baseline"]
     assert cb["kind"] in ("port", "reference") and cb["cores"] >= 1 and cb["value"] == d["value"] and cb["sample"]
+    nb = cb["reference_numba"]          # the reference's own numba finder, timed beside the port
+    assert ("unavailable" in nb) or (nb["value"] > 0 and nb["kind"] == "reference" and "1 of" in nb["cores"])
+    if os.path.exists(os.path.join(ROOT, "baseline", "_ref", "utils", "util.py")):
+        assert "unavailable" not in nb, nb
+        assert nb["value"] < d["value"], "the C port is faster than the numba original it restates"
     e = d["e2e"]
     assert e["value"] == d["value"] and e["unit"] == d["unit"] and e["h2d_bytes_per_step"] == 0 and e["d2h_bytes_per_step"] == 0
     assert "workload" in d["config"] and "model" not in d["config"]

@@ -59,3 +59,29 @@ def test_tie_order_matches_numba_argsort():
         if not np.array_equal(got[c, :n], want):
             bad.append((c, n, vals[c, :n].tolist(), got[c, :n].tolist(), want.tolist()))
     assert not bad, f"{len(bad)} of {len(ns)} cases differ; first: {bad[0]}"
+
+
+@pytest.mark.parametrize("name,n_edges", [("wikitalk", 60_000), ("reddit", 30_000)])
+def test_stable_tie_mode_matches_oracle_stable_mode(name, n_edges):
+    """tie_mode='stable' (zebra_tppr_set_tie_mode 1): equal scores keep insertion order — the oracle's
+    tie_mode 1, bit for bit; and it differs from the exact mode only through exactly tied scores."""
+    from zebra_b200 import synth
+    from zebra_b200.finder import tppr_finder
+    st = synth.make_stream(name, n_edges=n_edges)
+    neg = synth.make_negatives(st, 200)
+    N = st.shape.table_nodes
+    al, be = [0.1, 0.1], [0.5, 0.95]
+    f = tppr_finder(N, 20, 2, al, be, tie_mode="stable")
+    o = oracle.OracleFinder(N, 20, 2, al, be, tie_mode=1)
+    plan = f.make_plan(st.src, st.dst, neg, st.ts, st.eidx, 200)
+    out = plan.run(0, plan.n_batches, 32, out_slots=plan.n_batches)
+    f.sync_check()
+    for b in range(plan.n_batches):
+        lo, hi = b * 200, min(n_edges, (b + 1) * 200)
+        nodes = np.concatenate([st.src[lo:hi], st.dst[lo:hi], neg[lo:hi]]).astype(np.int32)
+        ref = o.streaming_topk(nodes, np.concatenate([st.ts[lo:hi]] * 3), st.eidx[lo:hi])
+        got = plan.views(out, b, 0, plan.n_batches)
+        for q in range(4):
+            for j in range(2):
+                assert np.array_equal(got[q][j].cpu().numpy(), ref[q][j]), (b, q, j)
+    assert f.counters()["tie_prunes"] > 0

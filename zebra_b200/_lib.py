@@ -41,6 +41,7 @@ SIGNATURES = {
     "zebra_tppr_shard_out_bytes": (C.c_size_t, [_VP]),
     "zebra_tppr_shard_reset": (C.c_int, [_VP, _VP]),
     "zebra_tppr_shard_row_mode": (C.c_int, [_VP, _I32]),
+    "zebra_tppr_set_tie_mode": (C.c_int, [_VP, _I32]),
     "zebra_tppr_set_max_blocks": (C.c_int, [_VP, _I32]),
     "zebra_tppr_read_state": (C.c_int, [_VP, _I32, _VP, _I64, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "zebra_tppr_sync_check": (C.c_int, [_VP, _VP]),

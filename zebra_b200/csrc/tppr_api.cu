@@ -152,6 +152,7 @@ struct zebra_tppr {
     int32_t max_chains = zebra::kMaxChains;
     std::vector<int32_t> chain_cnt;            // [num_nodes] scratch of the detection pass (zero between passes)
     int32_t *smflag = nullptr;                 // device [2 * kSmSlots]: chain warps running per SM, ticket warps standing aside
+    int32_t tie_mode = 0;                      // 0 exact (numba's argsort), 1 stable (insertion order among equal scores)
     bool sm_yield = true;                      // ZEBRA_SM_YIELD=0 switches the standing aside off
     uint32_t *dbg_owner = nullptr;             // debug (ZEBRA_DEBUG_ITEMS=1): who processed each item of the launch
     size_t dbg_cap = 0;
@@ -636,6 +637,7 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
     }
     p.out = out; p.ticket = h->ticket; p.status = h->status; p.prof = h->prof;
     p.wait_ns = h->wait_ns;
+    p.tie_mode = h->tie_mode;
     if (h->dbg_items && h->world == 1) {
         const size_t need = static_cast<size_t>(m) * h->n_tppr * sizeof(uint32_t);
         if (h->dbg_cap < need) {
@@ -1603,6 +1605,13 @@ int zebra_tppr_set_max_blocks(zebra_tppr_t *h, int32_t blocks)
     if (!h || blocks < 1) return fail("bad argument");
     h->max_blocks = std::min(h->max_blocks, static_cast<int>(blocks));
     if (h->shard_max_blocks) h->shard_max_blocks = std::min(h->shard_max_blocks, static_cast<int>(blocks));
+    return 0;
+}
+
+int zebra_tppr_set_tie_mode(zebra_tppr_t *h, int32_t mode)
+{
+    if (!h || (mode != 0 && mode != 1)) return fail("tie mode must be 0 (exact: numba's argsort order) or 1 (stable: insertion order)");
+    h->tie_mode = mode;
     return 0;
 }
 

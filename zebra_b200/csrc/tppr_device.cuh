@@ -141,6 +141,7 @@ struct SpanParams {
     const ChainStep *csteps;
     char *cmbox;                                    // [(cidx - cidx_base) * n_tppr + j][2 sides] records
     int32_t cidx_base, n_chains;
+    int32_t tie_mode;                               // 0: numba's argsort order inside groups of equal scores (exact); 1: insertion order
     int32_t *smflag;                                // [kSmSlots] running chain warps per SM, [kSmSlots] ticket warps yielding
     int32_t max_yield;                              // ticket warps that may yield at the same time
     uint32_t *dbg_owner;                            // debug (ZEBRA_DEBUG_ITEMS=1): [edge][instance] who processed the item
@@ -494,19 +495,26 @@ __device__ __forceinline__ void qs_partition_phase(WarpScratch &s, int n, int la
 // smaller scores), with numba's order inside groups of equal ranks; groups whose final ranks all lie
 // below `cut` keep their common rank (they are pruned anyway).  `occ` = bitmap of the occupied ranks.
 // slot 0 = candidate `lane` (valid0), slot 1 = candidate `c1` (valid1).
+// `stable` (tie_mode 1, "ties within tolerance" of the north star): equal scores keep their insertion
+// order instead — no replay; the oracle's tie_mode 1 is the matching restatement.
 __device__ __forceinline__ void tie_order(WarpScratch &s, int n, int cut, unsigned long long occ, bool valid0, int &r0,
-                                          bool valid1, int c1, int &r1, int lane)
+                                          bool valid1, int c1, int &r1, int lane, bool stable = false)
 {
     (void)cut; (void)occ;
     __syncwarp();
     s.Mlo[lane] = 0; s.Mlo[lane + 32] = 0; s.Mhi[lane] = 0; s.Mhi[lane + 32] = 0;
-    if (valid0) s.Q[lane] = static_cast<unsigned short>((r0 << 8) | lane);
-    if (valid1) s.Q[c1] = static_cast<unsigned short>((r1 << 8) | c1);
-    __syncwarp();
-    qs_partition_phase(s, n, lane);
+    int P0 = lane, P1 = c1;
+    if (!stable) {
+        if (valid0) s.Q[lane] = static_cast<unsigned short>((r0 << 8) | lane);
+        if (valid1) s.Q[c1] = static_cast<unsigned short>((r1 << 8) | c1);
+        __syncwarp();
+        qs_partition_phase(s, n, lane);
+        P0 = valid0 ? s.P[lane] : 0; P1 = valid1 ? s.P[c1] : 0;
+    } else {
+        __syncwarp();
+    }
     // order inside a group of equal ranks = order of the positions after the partition phase: per rank a
     // bitmap of the positions holding it, a candidate's offset = the set bits below its own position
-    const int P0 = valid0 ? s.P[lane] : 0, P1 = valid1 ? s.P[c1] : 0;
     if (valid0) atomicOr(P0 < 32 ? &s.Mlo[r0] : &s.Mhi[r0], 1u << (P0 & 31));
     if (valid1) atomicOr(P1 < 32 ? &s.Mlo[r1] : &s.Mhi[r1], 1u << (P1 & 31));
     __syncwarp();
@@ -739,7 +747,7 @@ __device__ __forceinline__ bool update_endpoint(const SpanParams &p, WarpScratch
         const unsigned long long surv = ((1ull << k) - 1) << cut;
         if ((occ & surv) != surv && !(ZEBRA_ABLATE & 4)) {
             // numba's (unstable) argsort decides the order inside a group of equal scores
-            tie_order(s, n, cut, occ, valid0, r0, valid1, pos1, r1, lane);
+            tie_order(s, n, cut, occ, valid0, r0, valid1, pos1, r1, lane, p.tie_mode != 0);
             stats += 0x10000u;
         }
         ZP_MARK(11);

@@ -32,7 +32,7 @@ def _ptr(a):
 
 
 class tppr_finder:  # noqa: N801  (name kept from the reference)
-    def __init__(self, num_nodes, k, n_tppr, alpha_list, beta_list, device=None, strict_snapshots=None):
+    def __init__(self, num_nodes, k, n_tppr, alpha_list, beta_list, device=None, strict_snapshots=None, tie_mode=None):
         if not torch.cuda.is_available():
             raise RuntimeError("zebra_b200.tppr_finder needs a CUDA device (B200, sm_100a); there is no CPU fallback")
         self.num_nodes = int(num_nodes)
@@ -52,6 +52,11 @@ class tppr_finder:  # noqa: N801  (name kept from the reference)
         b = (C.c_double * self.n_tppr)(*self.beta_list)
         check(self._L.zebra_tppr_create(C.byref(h), self.num_nodes, self.k, self.n_tppr, a, b, self.device.index or 0))
         self._h = h
+        if tie_mode is None:
+            tie_mode = os.environ.get("ZEBRA_TIE_MODE", "exact")
+        self.tie_mode = {"exact": 0, "stable": 1, 0: 0, 1: 1}[tie_mode]   # include/zebra_tppr.h zebra_tppr_set_tie_mode
+        if self.tie_mode:
+            check(self._L.zebra_tppr_set_tie_mode(h, self.tie_mode))
         if os.environ.get("ZEBRA_MAX_BLOCKS"):            # developer knob: cap the persistent grid (blocks of 8 warps)
             check(self._L.zebra_tppr_set_max_blocks(h, int(os.environ["ZEBRA_MAX_BLOCKS"])))
         self._table_bytes = self._L.zebra_tppr_table_bytes(h)
