@@ -173,7 +173,11 @@ int64_t zebra_tppr_epoch_slot_bytes(const zebra_epoch_t *epoch);
  * are written by the owner of the node they describe into the output region of EVERY rank at the
  * plan-run slot offsets; after all ranks have synchronised their streams and met at a barrier, each
  * rank's zebra_tppr_shard_out() holds the complete result, byte-identical to the single-GPU one.
- * The caller places a barrier between shard_reset and the first launch and before reusing slots.
+ * Records are touched by their owner only and the mailboxes carry their own cross-rank hand-shake (a rank
+ * pushes into a peer's mailbox half only after that peer has finished the launch that used it before), so no
+ * barrier is needed around shard_reset or between launches; the caller places a barrier only before READING
+ * rows other ranks store (and before letting them overwrite slots it has not read yet).  shard_reset also
+ * clears a recorded wait time-out.  Waits are bounded by wall time (ZEBRA_WAIT_TIMEOUT_MS, default 20 s).
  * backup/restore aliasing is a single-GPU feature; zebra_tppr_read_state reads owned nodes only.
  */
 int zebra_tppr_shard_init(zebra_tppr_t *h, int32_t rank, int32_t world, int64_t max_window_edges,

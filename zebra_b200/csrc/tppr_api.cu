@@ -141,7 +141,7 @@ struct zebra_tppr {
     int64_t max_window_edges = 0;
     char *peer_arena[zebra::kMaxRanks] = {};
     bool peer_opened[zebra::kMaxRanks] = {};   // mapped with cudaIpcOpenMemHandle (to be closed)
-    int32_t launch_parity = 0;
+    int64_t shard_launches = 0;               // sharded launches so far on this handle (the same on every rank)
     uint32_t shard_seq = 1;                    // handle-local tag sequence: identical on every rank
     int shard_max_blocks = 0;
     int32_t row_mode = 0;
@@ -235,6 +235,7 @@ size_t record_bytes(int k) { return zebra::record_stride(k); }
 constexpr size_t kEdgeBytes = 10 * 4 + 8 + 4;
 constexpr size_t kCidxOffset = 10 * 4 + 8;          // byte offset of the cidx array, per unit of `cap`
 constexpr size_t kStepBytesPerEdge = 2 * sizeof(zebra::ChainStep);   // worst case: both endpoints are chain nodes
+constexpr size_t kArenaHeader = 256;                // sharded arena: [header: launches finished per rank][mailbox halves][rows]
 constexpr int64_t kChainMinEdges = 4096;            // shorter spans are streamed without chain warps
 
 // Tags are edge sequence numbers drawn from one process-wide counter, so a table written through one
@@ -698,15 +699,24 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
                                                   : zebra_tppr_out_bytes(h, n_total, rows_per_edge);
             if (need + out_off > h->out_region) return fail("output of %zu bytes at offset %zu exceeds the shared output region (%zu)", need, out_off, h->out_region);
         }
-        p.world_log2 = h->world_log2; p.rank = h->rank; p.mbox_parity = h->launch_parity; p.row_mode = h->row_mode;
+        p.world_log2 = h->world_log2; p.rank = h->rank; p.mbox_parity = static_cast<int32_t>(h->shard_launches & 1);
+        p.row_mode = h->row_mode;
+        p.shard_launch = static_cast<int32_t>(h->shard_launches);
+        p.shard_done = reinterpret_cast<const int32_t *>(h->arena);     // header of the own arena: launches every rank has finished
         p.mbox_half_bytes = static_cast<int64_t>(h->mbox_half);
         for (int r = 0; r < h->world; ++r) {
-            p.mbox_peer[r] = h->peer_arena[r];
-            p.out_peer[r] = h->peer_arena[r] + 2 * h->mbox_half + out_off;
+            p.mbox_peer[r] = h->peer_arena[r] + kArenaHeader;
+            p.out_peer[r] = h->peer_arena[r] + kArenaHeader + 2 * h->mbox_half + out_off;
         }
         p.out = nullptr;
-        h->launch_parity ^= 1;
         zebra::tppr_span_shard_kernel<<<blocks, zebra::kWarpsPerBlock * 32, 0, st>>>(p);
+        // stream-ordered behind the kernel: tell every rank that this rank has finished (and stopped reading
+        // the mailbox half of) this launch; a peer pushes into that half again only after seeing it
+        zebra::ShardDoneParams dp;
+        for (int r = 0; r < zebra::kMaxRanks; ++r) dp.hdr[r] = r < h->world ? reinterpret_cast<int32_t *>(h->peer_arena[r]) : nullptr;
+        dp.world = h->world; dp.rank = h->rank; dp.value = static_cast<int32_t>(h->shard_launches + 1);
+        zebra::shard_done_kernel<<<1, 32, 0, st>>>(dp);
+        h->shard_launches++;
     } else {
         zebra::tppr_span_kernel<<<blocks, zebra::kWarpsPerBlock * 32, 0, st>>>(p);
     }
@@ -1506,8 +1516,8 @@ int zebra_tppr_shard_init(zebra_tppr_t *h, int32_t rank, int32_t world, int64_t 
     h->max_window_edges = max_window_edges;
     h->mbox_half = static_cast<size_t>(max_window_edges) * h->n_tppr * h->stride;
     h->out_region = (out_bytes + 255) & ~static_cast<size_t>(255);
-    CU(cudaMalloc(&h->arena, 2 * h->mbox_half + h->out_region));
-    CU(cudaMemset(h->arena, 0, 2 * h->mbox_half + h->out_region));
+    CU(cudaMalloc(&h->arena, kArenaHeader + 2 * h->mbox_half + h->out_region));
+    CU(cudaMemset(h->arena, 0, kArenaHeader + 2 * h->mbox_half + h->out_region));
     CU(cudaDeviceSynchronize());
     h->peer_arena[rank] = h->arena;
     int per_sm = 0, sms = 0;
@@ -1577,7 +1587,7 @@ int zebra_tppr_shard_disconnect(zebra_tppr_t *h)
     return 0;
 }
 
-void *zebra_tppr_shard_out(zebra_tppr_t *h) { return (h && h->arena) ? h->arena + 2 * h->mbox_half : nullptr; }
+void *zebra_tppr_shard_out(zebra_tppr_t *h) { return (h && h->arena) ? h->arena + kArenaHeader + 2 * h->mbox_half : nullptr; }
 size_t zebra_tppr_shard_out_bytes(const zebra_tppr_t *h) { return h ? h->out_region : 0; }
 
 int zebra_tppr_shard_reset(zebra_tppr_t *h, void *stream)
@@ -1588,7 +1598,9 @@ int zebra_tppr_shard_reset(zebra_tppr_t *h, void *stream)
     for (int j = 0; j < h->n_tppr; ++j)
         CU(cudaMemsetAsync(h->tables[j], 0, static_cast<size_t>(h->table_rows) * h->stride, st));
     CU(cudaMemsetAsync(h->rcnt, 0, sizeof(int32_t) * h->num_nodes * h->n_tppr, st));
+    CU(cudaMemsetAsync(h->status, 0, kStatusWords * sizeof(int32_t), st));   // also clears a recorded wait time-out
     h->plan_active = nullptr;
+    h->rcnt_dirty = false;
     return 0;
 }
 

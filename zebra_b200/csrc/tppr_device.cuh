@@ -130,6 +130,8 @@ struct SpanParams {
     unsigned long long *prof;   // [8] cycle sums per phase (ZEBRA_PROFILE builds)
     // node-sharded mode (tppr_shard_device.cuh): node v lives on rank v & (world-1), local row v >> world_log2
     int32_t world_log2, rank, mbox_parity;
+    int32_t shard_launch;                           // index of this sharded launch on the handle (same on every rank)
+    const int32_t *shard_done;                      // own arena header: [r] = launches rank r has finished
     int32_t row_mode;                               // 0: rows to every rank; 1: rows of batch b to rank b & (world-1) only
     const int32_t *list;                            // sharded: span indices of the edges this rank takes part in (this launch's range)
     int64_t n_list;

@@ -18,9 +18,13 @@
 // dst or a distinct negative — and the tickets run over that list only.  The staging records are
 // compact as well: entry q of the arrays (src, dst, ..., ts) describes edge list[q].
 //
-// Mailboxes are indexed by launch-local item and double-buffered by launch parity: a rank can run
-// at most one launch ahead of a peer that still has to read a slot (a rank finishing launch n needs
-// every peer's pushes of launch n, hence every peer has at least started launch n and finished n-1).
+// Mailboxes are indexed by launch-local item and double-buffered by launch parity.  A rank may push into
+// a peer's half of launch n only after that peer has FINISHED launch n-2 (the previous user of the half):
+// every rank publishes, stream-ordered behind each of its launches, the number of launches it has finished
+// into the arena header of every rank (shard_done_kernel), and a pushing warp checks the partner's count in
+// its own header first (once per warp and partner).  Without it two ranks that share no edge for a launch
+// or two could drift apart by more than one launch and overwrite a slot a third rank's push is still
+// waited for in.
 //
 // Output rows (utils/util.py:447-469) are written by the owner of the node they describe, straight
 // into the output region of the consuming rank(s) (peer stores): row_mode 0 replicates every row on
@@ -30,6 +34,26 @@
 #include "tppr_device.cuh"
 
 namespace zebra {
+
+__device__ __forceinline__ int32_t ld_relaxed_sys_s32(const int32_t *p)
+{
+    int32_t v;
+    asm volatile("ld.relaxed.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+struct ShardDoneParams { int32_t *hdr[kMaxRanks]; int32_t world, rank, value; };
+
+// One warp, launched behind every sharded span kernel on the same stream: lane r stores this rank's count of
+// finished launches into rank r's arena header (release at system scope: the kernel's reads are done).
+__global__ void shard_done_kernel(const ShardDoneParams d)
+{
+    const int r = threadIdx.x;
+    if (r < d.world) {
+        __threadfence_system();
+        asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(d.hdr[r] + d.rank), "r"(d.value) : "memory");
+    }
+}
 
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
@@ -45,6 +69,7 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
     const uint32_t tag_base = p.seq0 + static_cast<uint32_t>(p.tag_offset);
     const int lg = p.world_log2, me = p.rank, pmask = (1 << lg) - 1, world = 1 << lg;
     unsigned stats = 0;
+    unsigned peers_ok = 0;                  // partners known to have left the mailbox half of this launch's parity
     char *const my_mbox = p.mbox_peer[me] + static_cast<size_t>(p.mbox_parity) * p.mbox_half_bytes;
 
     for (;;) {
@@ -107,10 +132,17 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
                                : try_load<true>(mslot, k, lane, false, my_tag, D, curD);
             if (!okG) okG = try_load<false>(recG, k, lane, pG < 0, p.seq0 + static_cast<uint32_t>(pG), G, curG);
             if (!pushed && (oS ? okS : okD)) {      // our endpoint's OLD vector is here: send it before computing
-                push_vector<true>(pslot, k, oS ? S : D, my_tag, lane);
-                pushed = true;
+                const int partner = (oS ? dN : sN) & pmask;
+                if (!((peers_ok >> partner) & 1u)) {
+                    // the partner must have finished the launch that used this half before (launch - 2)
+                    if (ld_relaxed_sys_s32(p.shard_done + partner) >= p.shard_launch - 1) peers_ok |= 1u << partner;
+                }
+                if ((peers_ok >> partner) & 1u) {
+                    push_vector<true>(pslot, k, oS ? S : D, my_tag, lane);
+                    pushed = true;
+                }
             }
-            if (okS && okD) break;
+            if (okS && okD && pushed) break;
             // back off while the local producer is far away (same estimate as the single-GPU kernel)
             uint32_t dist = 0;
             if (!okS && oS) {
@@ -123,7 +155,7 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
                 dist = dd > dist ? dd : dist;
             }
             if (dist > kNear) __nanosleep(backoff_ns(dist));
-            else if ((!okS && !oS) || (!okD && !oD)) __nanosleep(100);   // waiting for a peer's push
+            else if ((!okS && !oS) || (!okD && !oD) || !pushed) __nanosleep(100);   // waiting for a peer's push, or for the peer to leave the mailbox half
             if (wt.expired(p.status, p.wait_ns, (!okS && !oS) || (!okD && !oD) ? 8 : 1, my_tag, 0)) { alive = false; break; }
         }
         if (!alive) continue;
