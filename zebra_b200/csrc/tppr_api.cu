@@ -16,7 +16,9 @@
 #include <climits>
 #include <cstring>
 #include <memory>
+#include <condition_variable>
 #include <mutex>
+#include <thread>
 #include <string>
 #include <vector>
 
@@ -91,6 +93,13 @@ struct HugeArray {
     const T *end() const { return p + n; }
 };
 
+// Scratch of one host dependency pass (fill_soa): per-node state and the chains of negative readers.
+// The handle owns one; every worker thread of a pipelined epoch owns another.
+struct HostScratch {
+    HugeArray<NodeDep> dep;
+    std::vector<int32_t> rnext;
+};
+
 struct zebra_tppr {
     int64_t num_nodes = 0;
     int32_t k = 0, n_tppr = 0, stride = 0, device = 0;
@@ -131,6 +140,11 @@ struct zebra_tppr {
         bool copy_pending = false;
     } eslot[3];
     cudaStream_t copy_stream = nullptr;
+    // staging ring of the pipelined epoch: the dependency pass of window w runs (on a worker thread when the
+    // epoch has any) into slot w % kPrepSlots while earlier windows are on the GPU
+    static constexpr int kPrepSlots = 6;
+    Staging prep[kPrepSlots];
+    int host_threads = -1;                     // worker threads of an epoch (ZEBRA_HOST_THREADS; -1 = default)
     // node-sharded mode (zebra_tppr_shard_*): tables are library-owned local slices, the arena
     // (mailboxes + output region) is peer-mapped on every rank
     int32_t world = 1, rank = 0, world_log2 = 0;
@@ -223,7 +237,15 @@ struct zebra_epoch {
     int64_t issued = 0, consumed = 0;
     cudaStream_t st = nullptr;
     ChainSet cs;                    // chain nodes of the span, chosen at epoch_begin
-    ChainBuild cb;
+    // per staging slot: what the dependency pass of the window staged there produced
+    struct Prep { ChainBuild cb; ChainLaunch cl; size_t img_bytes = 0, cap = 0; int64_t window = -1; bool ready = false, failed = false; std::string err; };
+    Prep prep[zebra_tppr::kPrepSlots];
+    // worker threads: window w is prepared by worker w % n_workers, as soon as its slot is free
+    std::vector<std::thread> workers;
+    std::vector<std::unique_ptr<HostScratch>> scratch;
+    std::mutex mu;
+    std::condition_variable cv;
+    bool stop = false;
 };
 
 namespace {
@@ -315,7 +337,8 @@ void detect_chains(zebra_tppr *h, const NodeT *src, const NodeT *dst, int64_t n,
 // resident warp walks.
 template <typename NodeT>
 int fill_soa(zebra_tppr *h, char *host, size_t cap, const NodeT *src, const NodeT *dst, const NodeT *neg,
-             const double *ts, const int64_t *eidx, int64_t m, const ChainSet *cs = nullptr, ChainBuild *cb = nullptr)
+             const double *ts, const int64_t *eidx, int64_t m, const ChainSet *cs = nullptr, ChainBuild *cb = nullptr,
+             HostScratch *scratch = nullptr)
 {
     const int64_t N = h->num_nodes;
     int32_t *o_src = reinterpret_cast<int32_t *>(host);
@@ -341,9 +364,10 @@ int fill_soa(zebra_tppr *h, char *host, size_t cap, const NodeT *src, const Node
             return fail("node id out of range at edge %lld (num_nodes=%lld)", (long long)i, (long long)N);
         if (e < 0 || e > 0x7fffffffLL) return fail("edge id %lld does not fit int32", (long long)e);
     }
-    NodeDep *dep = h->dep.data();
-    if (h->rnext.size() < static_cast<size_t>(m)) h->rnext.resize(static_cast<size_t>(m));
-    int32_t *rnext = h->rnext.data();
+    NodeDep *dep = scratch ? scratch->dep.data() : h->dep.data();
+    std::vector<int32_t> &rn = scratch ? scratch->rnext : h->rnext;
+    if (rn.size() < static_cast<size_t>(m)) rn.resize(static_cast<size_t>(m));
+    int32_t *rnext = rn.data();
     // kFlagDstFirst without a backward pass: NodeDep::pad remembers, per node, the latest edge (index + 1)
     // that wrote it and does not know yet which of its endpoints is rewritten first; the first later
     // write of either endpoint settles it (one edge rewriting both: no preference)
@@ -914,6 +938,7 @@ int zebra_tppr_create(zebra_tppr_t **out, int64_t num_nodes, int32_t k, int32_t 
         h->max_chains = std::max(0, std::min(atoi(e), zebra::kMaxChains));
         h->chains_enabled = h->max_chains > 0;
     }
+    if (const char *e = getenv("ZEBRA_HOST_THREADS")) h->host_threads = std::max(0, atoi(e));
     if (const char *e = getenv("ZEBRA_SM_YIELD")) h->sm_yield = atoi(e) != 0;
     if (const char *e = getenv("ZEBRA_DEBUG_ITEMS")) h->dbg_items = atoi(e) != 0;
     if (const char *e = getenv("ZEBRA_WAIT_TIMEOUT_MS")) h->wait_ns = static_cast<unsigned long long>(std::max(1, atoi(e))) * 1000000ull;
@@ -939,6 +964,11 @@ int zebra_tppr_destroy(zebra_tppr_t *h)
         if (sl.out_host) cudaFreeHost(sl.out_host);
         if (sl.ev_kernel) cudaEventDestroy(sl.ev_kernel);
         if (sl.ev_copy) cudaEventDestroy(sl.ev_copy);
+    }
+    for (auto &ps : h->prep) {
+        if (ps.host) cudaFreeHost(ps.host);
+        if (ps.dev) cudaFree(ps.dev);
+        if (ps.free_ev) cudaEventDestroy(ps.free_ev);
     }
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     for (int r = 0; r < zebra::kMaxRanks; ++r)
@@ -1347,17 +1377,57 @@ int zebra_tppr_plan_run(zebra_tppr_t *h, zebra_plan_t *pl, int64_t first_batch, 
 
 /* ---- pipelined epoch ---- */
 
+// Host dependency pass of window w into its staging slot (pinned memory): the edge records, the chain step
+// records behind them and the launch geometry.  Runs on the caller's thread (scratch = the handle's) or on a
+// worker thread of the epoch (scratch = the worker's own); touches no CUDA state.
+static void epoch_prepare(zebra_epoch *ep, int64_t w, HostScratch *scratch)
+{
+    zebra_tppr *h = ep->h;
+    zebra_epoch::Prep &pr = ep->prep[w % zebra_tppr::kPrepSlots];
+    Staging &stg = h->prep[w % zebra_tppr::kPrepSlots];
+    const int64_t b0 = w * ep->window, b1 = std::min(ep->n_batches, b0 + ep->window);
+    const int64_t lo = b0 * ep->batch_size, hi = std::min(ep->n, b1 * ep->batch_size);
+    const int64_t m = hi - lo;
+    pr.cap = (static_cast<size_t>(m) + 7) & ~static_cast<size_t>(7);
+    pr.failed = fill_soa<int32_t>(h, stg.host, pr.cap, ep->src + lo, ep->dst + lo, ep->neg ? ep->neg + lo : nullptr, ep->ts + lo,
+                                  ep->eidx + lo, m, &ep->cs, &pr.cb, scratch) != 0;
+    if (pr.failed) pr.err = zebra_last_error();
+    else pr.img_bytes = place_chain_steps(ep->cs, stg.host, stg.dev, pr.cap, pr.cb, pr.cl);
+    pr.window = w;
+}
+
+// Worker `tid` of `n_workers`: prepares windows tid, tid + n_workers, ... each as soon as its staging slot is
+// free, i.e. once the window that used the slot before has been handed to the caller (its kernel is done).
+static void epoch_worker(zebra_epoch *ep, int tid, int n_workers)
+{
+    HostScratch *sc = ep->scratch[static_cast<size_t>(tid)].get();
+    for (int64_t w = tid; w < ep->n_windows; w += n_workers) {
+        {
+            std::unique_lock<std::mutex> lk(ep->mu);
+            ep->cv.wait(lk, [&] { return ep->stop || w < ep->consumed + zebra_tppr::kPrepSlots; });
+            if (ep->stop) return;
+        }
+        epoch_prepare(ep, w, sc);
+        {
+            std::lock_guard<std::mutex> lk(ep->mu);
+            ep->prep[w % zebra_tppr::kPrepSlots].ready = true;
+        }
+        ep->cv.notify_all();
+    }
+}
+
 static int epoch_issue(zebra_epoch *ep)
 {
     zebra_tppr *h = ep->h;
     const int64_t w = ep->issued;
     zebra_tppr::EpochSlot &sl = h->eslot[w % 3];
+    zebra_epoch::Prep &pr = ep->prep[w % zebra_tppr::kPrepSlots];
+    Staging &stg = h->prep[w % zebra_tppr::kPrepSlots];
     const int64_t b0 = w * ep->window, b1 = std::min(ep->n_batches, b0 + ep->window);
     const int64_t lo = b0 * ep->batch_size, hi = std::min(ep->n, b1 * ep->batch_size);
     const int64_t m = hi - lo;
     // the slot's previous window (w-3) has been handed to the caller and released, so its copy is done
     if (sl.copy_pending) { CU(cudaEventSynchronize(sl.ev_copy)); sl.copy_pending = false; }
-    if (ensure_staging(h, sl.stg, static_cast<size_t>(ep->window * ep->batch_size) + 8)) return 1;
     const size_t ob = static_cast<size_t>(ep->window) * ep->slot_bytes;
     if (sl.out_cap < ob) {
         if (sl.out_dev) CU(cudaFree(sl.out_dev));
@@ -1373,19 +1443,25 @@ static int epoch_issue(zebra_epoch *ep)
         CU(cudaEventCreateWithFlags(&sl.ev_kernel, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&sl.ev_copy, cudaEventDisableTiming));
     }
-    const size_t cap = (static_cast<size_t>(m) + 7) & ~static_cast<size_t>(7);
-    if (fill_soa<int32_t>(h, sl.stg.host, cap, ep->src + lo, ep->dst + lo, ep->neg ? ep->neg + lo : nullptr, ep->ts + lo,
-                          ep->eidx + lo, m, &ep->cs, &ep->cb)) return 1;
+    // the staging image of the window: prepared by a worker thread, or right here
+    if (ep->workers.empty()) {
+        epoch_prepare(ep, w, nullptr);
+    } else {
+        std::unique_lock<std::mutex> lk(ep->mu);
+        ep->cv.wait(lk, [&] { return pr.ready && pr.window == w; });
+        pr.ready = false;
+    }
+    if (pr.failed) return fail("%s", pr.err.c_str());
+    const size_t cap = pr.cap;
+    const ChainLaunch &cl = pr.cl;
     uint32_t seq0 = 0;
     if (alloc_seq(h, m, ep->st, &seq0)) return 1;
-    ChainLaunch cl;
-    const size_t img_bytes = place_chain_steps(ep->cs, sl.stg.host, sl.stg.dev, cap, ep->cb, cl);
-    CU(cudaMemcpyAsync(sl.stg.dev, sl.stg.host, img_bytes, cudaMemcpyHostToDevice, ep->st));
+    CU(cudaMemcpyAsync(stg.dev, stg.host, pr.img_bytes, cudaMemcpyHostToDevice, ep->st));
     if (w == 0) CU(cudaEventRecord(h->ev0, ep->st));
     BatchOut bo;
     bo.batch_size = ep->batch_size; bo.first_batch = b0; bo.out_slots = ep->window;
     bo.slot_bytes = static_cast<int64_t>(ep->slot_bytes);
-    if (launch_kernel(h, sl.stg.dev, cap, 0, m, ep->n, lo, ep->rows_per_edge, (1 << h->n_tppr) - 1, sl.out_dev, bo, seq0, 0,
+    if (launch_kernel(h, stg.dev, cap, 0, m, ep->n, lo, ep->rows_per_edge, (1 << h->n_tppr) - 1, sl.out_dev, bo, seq0, 0,
                       ep->st, nullptr, 0, &cl)) return 1;
     CU(cudaEventRecord(sl.ev_kernel, ep->st));
     if (ep->rows_per_edge) {
@@ -1435,9 +1511,22 @@ int zebra_tppr_epoch_begin(zebra_tppr_t *h, const int32_t *host_src, const int32
     h->last_items = 0;
     if (begin_span(h, ep->st)) { delete ep; return 1; }
     h->epoch_active = ep;
+    for (auto &ps : h->prep)
+        if (ensure_staging(h, ps, static_cast<size_t>(ep->window * ep->batch_size) + 8)) { h->epoch_active = nullptr; delete ep; return 1; }
+    // worker threads for the host dependency pass (the GPU needs ~45 ns per edge of a hub-bound stream, one
+    // host thread ~55 ns): windows are independent of each other, so they are prepared in parallel, ahead
+    int n_workers = h->host_threads;
+    if (n_workers < 0) n_workers = static_cast<int>(std::min<unsigned>(3, std::max(1u, std::thread::hardware_concurrency()) - 1));
+    if (ep->n_windows < 4) n_workers = 0;
+    n_workers = std::min<int>(n_workers, zebra_tppr::kPrepSlots - 2);
+    for (int t = 0; t < n_workers; ++t) {
+        ep->scratch.emplace_back(new HostScratch());
+        ep->scratch.back()->dep.assign(static_cast<size_t>(h->num_nodes), NodeDep{-1, -1, 0u, 0u});
+    }
+    for (int t = 0; t < n_workers; ++t) ep->workers.emplace_back(epoch_worker, ep, t, n_workers);
     // two windows in flight before the caller asks for the first
     for (int q = 0; q < 2 && ep->issued < ep->n_windows; ++q)
-        if (epoch_issue(ep)) { h->epoch_active = nullptr; delete ep; return 1; }
+        if (epoch_issue(ep)) { zebra_tppr_epoch_end(ep); return 1; }
     *out = ep;
     return 0;
 }
@@ -1462,7 +1551,11 @@ int zebra_tppr_epoch_next(zebra_epoch_t *ep, void **host_rows, int64_t *first_ba
     *first_batch = b0;
     *n_batches = std::min(ep->n_batches, b0 + ep->window) - b0;
     *host_rows = ep->rows_per_edge ? sl.out_host : nullptr;
-    ep->consumed = w + 1;
+    {
+        std::lock_guard<std::mutex> lk(ep->mu);
+        ep->consumed = w + 1;
+    }
+    ep->cv.notify_all();
     if (ep->consumed == ep->n_windows) {
         CU(cudaMemcpyAsync(h->status_host, h->status, kStatusWords * sizeof(int32_t), cudaMemcpyDeviceToHost, ep->st));
         CU(cudaStreamSynchronize(ep->st));
@@ -1481,6 +1574,12 @@ int zebra_tppr_epoch_end(zebra_epoch_t *ep)
 {
     if (!ep) return 0;
     zebra_tppr *h = ep->h;
+    {
+        std::lock_guard<std::mutex> lk(ep->mu);
+        ep->stop = true;
+    }
+    ep->cv.notify_all();
+    for (auto &t : ep->workers) t.join();
     cudaSetDevice(h->device);
     cudaStreamSynchronize(ep->st);
     if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
@@ -1524,6 +1623,12 @@ int zebra_tppr_shard_init(zebra_tppr_t *h, int32_t rank, int32_t world, int64_t 
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, zebra::tppr_span_shard_kernel, zebra::kWarpsPerBlock * 32, 0));
     CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
     h->shard_max_blocks = std::max(1, per_sm * sms);
+    {
+        // load the small kernel now: a first launch would load it lazily, and that load can wait for running
+        // kernels — e.g. this rank's span kernel, which itself waits for a peer the host has not launched yet
+        cudaFuncAttributes fa;
+        CU(cudaFuncGetAttributes(&fa, zebra::shard_done_kernel));
+    }
     if (ipc_handle_out) {
         cudaIpcMemHandle_t mh;
         CU(cudaIpcGetMemHandle(&mh, h->arena));

@@ -498,7 +498,7 @@ __device__ __forceinline__ void qs_partition_phase(WarpScratch &s, int n, int la
 // below `cut` keep their common rank (they are pruned anyway).  `occ` = bitmap of the occupied ranks.
 // slot 0 = candidate `lane` (valid0), slot 1 = candidate `c1` (valid1).
 // `stable` (tie_mode 1, "ties within tolerance" of the north star): equal scores keep their insertion
-// order instead — no replay; the oracle's tie_mode 1 is the matching restatement.
+// order instead — no replay; the CPU checker's tie_mode 1 is the matching restatement.
 __device__ __forceinline__ void tie_order(WarpScratch &s, int n, int cut, unsigned long long occ, bool valid0, int &r0,
                                           bool valid1, int c1, int &r1, int lane, bool stable = false)
 {
