@@ -364,43 +364,19 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
         dist.all_reduce(pb)                       # H2D of a plan, summed over the ranks
         res["plan_bytes"] = int(pb[0])
         if e2e:
-            # end to end: host arrays in (dependency pass + H2D of the replicated span on every rank), the
-            # complete rows of every batch back in pinned host memory on EVERY rank.  Per window: kernel,
-            # a one-element all-reduce as cross-rank completion (plumbing, not data), D2H on a second stream.
-            # data-parallel consumers: rank r reads back the rows of its 1/N of every window's batches
-            # (together the ranks read every batch exactly once); the full rows are on every GPU anyway
-            per = window // world                    # window is a multiple of world, windows start at multiples of it
-            pinned = [torch.empty((per, slot), dtype=torch.uint8).pin_memory() for _ in range(2)]
-            flag = torch.zeros(1, device=dev)
-            ev_ready = [torch.cuda.Event() for _ in range(2)]
-            ev_copy = [torch.cuda.Event() for _ in range(2)]
-
+            # end to end: host arrays in (replicated span on every rank), this rank's batches out in pinned host
+            # memory (rank r consumes batches b % N == r: together the ranks read every batch exactly once).
+            # ShardedFinder.epoch = the library's pipelined sharded epoch: per window the ownership-aware
+            # dependency pass (worker threads), H2D of the records the rank takes part in, the sharded span
+            # kernel, and — once every rank has finished the window (in-library hand-shake through the arena
+            # header, no collective) — the D2H of the rank's batches on a second stream.
             def e2e_pass():
-                pl = f.make_plan(st.src, st.dst, neg, st.ts, st.eidx, BS)
                 f.reset_tppr()
-                acc = 0.0
-                for w in range(n_win):
-                    h, b0 = w & 1, w * window
-                    nb = min(window, pl.n_batches - b0)
-                    pl.run(b0, nb, window, out_slots=window, out_offset=h * window * slot)
-                    if w >= 1:
-                        main.wait_event(ev_copy[(w - 1) & 1])   # this rank has drained the other half ...
-                    dist.all_reduce(flag)                       # ... and so has everybody once this completes
-                    ev_ready[h].record(main)
-                    if w >= 2:
-                        acc += float(pinned[h][0, 0])           # host consumes window w-2 before its buffer is reused
-                    with torch.cuda.stream(copy_stream):
-                        copy_stream.wait_event(ev_ready[h])
-                        base = h * window * slot
-                        mine = f.out[base: base + nb * slot].view(nb, slot)[rank::world]      # batches b with b % N == rank
-                        if mine.shape[0]:
-                            pinned[h][: mine.shape[0]].copy_(mine, non_blocking=True)
-                        ev_copy[h].record(copy_stream)
-                    if w >= 1:
-                        ev_copy[(w - 1) & 1].synchronize()
-                ev_copy[(n_win - 1) & 1].synchronize()
-                f.sync_check()
-                pl.close()
+                acc, cnt_b = 0.0, 0
+                for b, nd, ei, dt, w in f.epoch(st.src, st.dst, neg, st.ts, st.eidx, BS, window=window):
+                    acc += float(w[-1][0, 0]) + float(nd[0][-1, -1])
+                    cnt_b += 1
+                assert cnt_b == len(range(rank, plan.n_batches, world)), (cnt_b, plan.n_batches)
                 return acc
 
             e2e_pass()
@@ -410,6 +386,7 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
                 e2e_pass()
             barrier()
             res["e2e_s"] = time.perf_counter() - t0
+            res["e2e_h2d"] = 0
         t = torch.tensor([res["ms"], res.get("e2e_s", 0.0)], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         res["ms"], res["e2e_s"] = float(t[0]), float(t[1])
@@ -473,9 +450,10 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
                    "tie_path_prunes_last_step_rank0": weak["tie_prunes"]},
         "e2e": {"value": E * args.steps / weak["e2e_s"], "unit": UNIT,
                 "h2d_bytes_per_step": weak["plan_bytes"], "d2h_bytes_per_step": len(ALPHAS) * 16 * 3 * E * K,
-                "step": f"per rank: plan built from host arrays (ownership-aware dependency pass + H2D of the records of the edges the rank takes part in), sharded "
-                        f"run in windows of {window} batches, a one-element all-reduce per window as cross-rank completion, rank r copies "
-                        f"the rows of its batches (b % {world} == r) to pinned host memory (every batch read back once)"},
+                "step": f"ShardedFinder.epoch on every rank (host arrays in): per window of {window} batches the ownership-aware dependency "
+                        f"pass on worker threads, H2D of the records of the edges the rank takes part in, the sharded span kernel, an in-library "
+                        f"cross-rank completion hand-shake, D2H of the rank's batches (b % {world} == r) into pinned host memory on a second "
+                        f"stream (every batch read back once)"},
         "gpu_launches": weak["launches"] * world,
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak * world, "unit": "GB/s", "frac": achieved / (peak * world),

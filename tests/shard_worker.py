@@ -52,6 +52,28 @@ def main():
                 oe, on, ot, os_, onm = cpu.state(j, int(a))
                 assert np.array_equal(e, oe) and np.array_equal(s, os_) and nm == onm
         dist.barrier()
+    # pipelined sharded epoch (host arrays in, this rank's batches out in pinned host memory), twice
+    f.set_row_mode(1)
+    wep = max(world, (window // world) * world)
+    for rep in range(2):
+        f.reset_tppr()
+        cpu = oracle.OracleFinder(N, k, 2, al, be)
+        seen = []
+        ep = f.epoch(st.src, st.dst, neg, st.ts, st.eidx, bs, window=wep)
+        nxt = 0
+        for b, nd, ei, dt, w in ep:
+            while nxt <= b:                      # the oracle walks every batch, this rank checks its own
+                lo, hi = nxt * bs, min(n_edges, (nxt + 1) * bs)
+                nodes = np.concatenate([st.src[lo:hi], st.dst[lo:hi], neg[lo:hi]]).astype(np.int32)
+                ref = cpu.streaming_topk(nodes, np.concatenate([st.ts[lo:hi]] * 3), st.eidx[lo:hi])
+                nxt += 1
+            for got, want in zip((nd, ei, dt, w), ref):
+                for x, y in zip(got, want):
+                    assert np.array_equal(x, y), f"epoch: rank {rank} batch {b} pass {rep}"
+            seen.append(b)
+        assert seen == list(range(rank, n_batches, world)), (rank, seen[:5], len(seen))
+        dist.barrier()
+    f.set_row_mode(0)
     if rank == 0:
         print("exchange:", exchange_stats(st.src, st.dst, neg, world, k, 2), flush=True)
     print(f"SHARD_OK rank {rank}/{world} kernel_ms {f.last_kernel_ms():.2f} {f.counters()}", flush=True)

@@ -238,7 +238,10 @@ struct zebra_epoch {
     cudaStream_t st = nullptr;
     ChainSet cs;                    // chain nodes of the span, chosen at epoch_begin
     // per staging slot: what the dependency pass of the window staged there produced
-    struct Prep { ChainBuild cb; ChainLaunch cl; size_t img_bytes = 0, cap = 0; int64_t window = -1; bool ready = false, failed = false; std::string err; };
+    struct Prep {
+        ChainBuild cb; ChainLaunch cl; size_t img_bytes = 0, cap = 0; int64_t window = -1; bool ready = false, failed = false; std::string err;
+        std::vector<int32_t> list; std::vector<int64_t> batch_ofs;      // node-sharded handles: this rank's work list of the window
+    };
     Prep prep[zebra_tppr::kPrepSlots];
     // worker threads: window w is prepared by worker w % n_workers, as soon as its slot is free
     std::vector<std::thread> workers;
@@ -520,7 +523,7 @@ int shard_work_list(zebra_tppr *h, const int32_t *src, const int32_t *dst, const
 // before src.  NodeDep::pad remembers, per node, the latest such edge still waiting for that answer;
 // the first later write of either endpoint settles it (a single edge rewriting both: no preference).
 void fill_soa_sharded(zebra_tppr *h, char *host, size_t cap, const int32_t *src, const int32_t *dst, const int32_t *neg,
-                      const double *ts, const int64_t *eidx, const std::vector<int32_t> &list)
+                      const double *ts, const int64_t *eidx, const std::vector<int32_t> &list, HostScratch *scratch = nullptr)
 {
     const int32_t pm = h->world - 1, me = h->rank, lg = h->world_log2;
     int32_t *o_src = reinterpret_cast<int32_t *>(host);
@@ -528,10 +531,11 @@ void fill_soa_sharded(zebra_tppr *h, char *host, size_t cap, const int32_t *src,
     int32_t *p_s = o_e + cap, *p_d = p_s + cap, *p_n = p_d + cap;
     uint32_t *r_s = reinterpret_cast<uint32_t *>(p_n + cap), *r_d = r_s + cap, *flg = r_d + cap;
     double *o_ts = reinterpret_cast<double *>(flg + cap);
-    NodeDep *dep = h->dep.data();                                     // sized num_nodes >= local rows
+    NodeDep *dep = scratch ? scratch->dep.data() : h->dep.data();     // sized num_nodes >= local rows
     const size_t L = list.size();
-    if (h->rnext.size() < L) h->rnext.resize(L);
-    int32_t *rnext = h->rnext.data();
+    std::vector<int32_t> &rn = scratch ? scratch->rnext : h->rnext;
+    if (rn.size() < L) rn.resize(L);
+    int32_t *rnext = rn.data();
     auto settle = [&](uint32_t qe, int32_t x) {                       // node x of edge qe is the first to be rewritten
         const int32_t s = o_src[qe], d = o_dst[qe];
         if (x == d) flg[qe] |= zebra::kFlagDstFirst;
@@ -726,6 +730,7 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
         p.world_log2 = h->world_log2; p.rank = h->rank; p.mbox_parity = static_cast<int32_t>(h->shard_launches & 1);
         p.row_mode = h->row_mode;
         p.shard_launch = static_cast<int32_t>(h->shard_launches);
+        p.row_guard = (h->epoch_active && rows_per_edge) ? 1 : 0;
         p.shard_done = reinterpret_cast<const int32_t *>(h->arena);     // header of the own arena: launches every rank has finished
         p.mbox_half_bytes = static_cast<int64_t>(h->mbox_half);
         for (int r = 0; r < h->world; ++r) {
@@ -738,7 +743,7 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
         // the mailbox half of) this launch; a peer pushes into that half again only after seeing it
         zebra::ShardDoneParams dp;
         for (int r = 0; r < zebra::kMaxRanks; ++r) dp.hdr[r] = r < h->world ? reinterpret_cast<int32_t *>(h->peer_arena[r]) : nullptr;
-        dp.world = h->world; dp.rank = h->rank; dp.value = static_cast<int32_t>(h->shard_launches + 1);
+        dp.world = h->world; dp.rank = h->rank; dp.value = static_cast<int32_t>(h->shard_launches + 1); dp.slot = 0;
         zebra::shard_done_kernel<<<1, 32, 0, st>>>(dp);
         h->shard_launches++;
     } else {
@@ -1388,6 +1393,21 @@ static void epoch_prepare(zebra_epoch *ep, int64_t w, HostScratch *scratch)
     const int64_t b0 = w * ep->window, b1 = std::min(ep->n_batches, b0 + ep->window);
     const int64_t lo = b0 * ep->batch_size, hi = std::min(ep->n, b1 * ep->batch_size);
     const int64_t m = hi - lo;
+    if (h->world > 1) {
+        // node-sharded: the work list of this rank within the window, compact records for it, then the list
+        // itself (as span indices) behind the records
+        const int32_t *ng = ep->neg ? ep->neg + lo : nullptr;
+        pr.failed = shard_work_list(h, ep->src + lo, ep->dst + lo, ng, ep->eidx + lo, m, ep->batch_size, pr.list, pr.batch_ofs) != 0;
+        if (pr.failed) { pr.err = zebra_last_error(); pr.window = w; return; }
+        pr.cap = (pr.list.size() + 8) & ~static_cast<size_t>(7);
+        fill_soa_sharded(h, stg.host, pr.cap, ep->src + lo, ep->dst + lo, ng, ep->ts + lo, ep->eidx + lo, pr.list, scratch);
+        int32_t *dl = reinterpret_cast<int32_t *>(stg.host + pr.cap * kEdgeBytes);
+        for (size_t q = 0; q < pr.list.size(); ++q) dl[q] = pr.list[q] + static_cast<int32_t>(lo);
+        pr.img_bytes = pr.cap * kEdgeBytes + pr.list.size() * sizeof(int32_t);
+        pr.cl = ChainLaunch();
+        pr.window = w;
+        return;
+    }
     pr.cap = (static_cast<size_t>(m) + 7) & ~static_cast<size_t>(7);
     pr.failed = fill_soa<int32_t>(h, stg.host, pr.cap, ep->src + lo, ep->dst + lo, ep->neg ? ep->neg + lo : nullptr, ep->ts + lo,
                                   ep->eidx + lo, m, &ep->cs, &pr.cb, scratch) != 0;
@@ -1428,13 +1448,14 @@ static int epoch_issue(zebra_epoch *ep)
     const int64_t m = hi - lo;
     // the slot's previous window (w-3) has been handed to the caller and released, so its copy is done
     if (sl.copy_pending) { CU(cudaEventSynchronize(sl.ev_copy)); sl.copy_pending = false; }
+    const bool sharded = h->world > 1;
     const size_t ob = static_cast<size_t>(ep->window) * ep->slot_bytes;
     if (sl.out_cap < ob) {
         if (sl.out_dev) CU(cudaFree(sl.out_dev));
         if (sl.out_host) CU(cudaFreeHost(sl.out_host));
         sl.out_dev = nullptr; sl.out_host = nullptr; sl.out_cap = 0;
         if (ob) {
-            CU(cudaMalloc(&sl.out_dev, ob));
+            if (!sharded) CU(cudaMalloc(&sl.out_dev, ob));      // sharded: rows land in the shared output region
             CU(cudaMallocHost(&sl.out_host, ob));
         }
         sl.out_cap = ob;
@@ -1461,6 +1482,45 @@ static int epoch_issue(zebra_epoch *ep)
     BatchOut bo;
     bo.batch_size = ep->batch_size; bo.first_batch = b0; bo.out_slots = ep->window;
     bo.slot_bytes = static_cast<int64_t>(ep->slot_bytes);
+    if (sharded) {
+        // rows of window w go to half w & 1 of every consumer's output region; the consumer copies its batches
+        // out once EVERY rank has finished the launch, and tells the others when its half may be stored into again
+        const int64_t launch = h->shard_launches;
+        const size_t half_off = static_cast<size_t>(w & 1) * ob;
+        const int32_t *dev_list = reinterpret_cast<const int32_t *>(stg.dev + cap * kEdgeBytes);
+        if (launch_kernel(h, stg.dev, cap, 0, m, ep->n, lo, ep->rows_per_edge, (1 << h->n_tppr) - 1,
+                          reinterpret_cast<char *>(half_off), bo, seq0, 0, ep->st, dev_list, static_cast<int64_t>(pr.list.size()))) return 1;
+        CU(cudaEventRecord(sl.ev_kernel, ep->st));
+        if (ep->rows_per_edge) {
+            CU(cudaStreamWaitEvent(h->copy_stream, sl.ev_kernel, 0));
+            zebra::shard_wait_kernel<<<1, 32, 0, h->copy_stream>>>(reinterpret_cast<const int32_t *>(h->arena), h->world,
+                                                                  static_cast<int32_t>(launch + 1), h->status, h->wait_ns);
+            const char *region = h->arena + kArenaHeader + 2 * h->mbox_half + half_off;
+            const int64_t nb = b1 - b0;
+            if (h->row_mode == 1) {
+                // this rank's batches of the window: b = rank (mod world); windows start at multiples of world
+                const int64_t mine = nb > h->rank ? (nb - h->rank + h->world - 1) / h->world : 0;
+                if (mine > 0)
+                    CU(cudaMemcpy2DAsync(sl.out_host, ep->slot_bytes, region + static_cast<size_t>(h->rank) * ep->slot_bytes,
+                                         static_cast<size_t>(h->world) * ep->slot_bytes, ep->slot_bytes, static_cast<size_t>(mine),
+                                         cudaMemcpyDeviceToHost, h->copy_stream));
+            } else {
+                CU(cudaMemcpyAsync(sl.out_host, region, static_cast<size_t>(nb) * ep->slot_bytes, cudaMemcpyDeviceToHost, h->copy_stream));
+            }
+            zebra::ShardDoneParams dp;
+            for (int r = 0; r < zebra::kMaxRanks; ++r) dp.hdr[r] = r < h->world ? reinterpret_cast<int32_t *>(h->peer_arena[r]) : nullptr;
+            dp.world = h->world; dp.rank = h->rank; dp.value = static_cast<int32_t>(launch + 1); dp.slot = 1;
+            zebra::shard_done_kernel<<<1, 32, 0, h->copy_stream>>>(dp);
+            CU(cudaGetLastError());
+            CU(cudaEventRecord(sl.ev_copy, h->copy_stream));
+        } else {
+            CU(cudaEventRecord(sl.ev_copy, ep->st));
+        }
+        sl.copy_pending = true;
+        if (w + 1 == ep->n_windows) { CU(cudaEventRecord(h->ev1, ep->st)); h->timed = true; }
+        ep->issued = w + 1;
+        return 0;
+    }
     if (launch_kernel(h, stg.dev, cap, 0, m, ep->n, lo, ep->rows_per_edge, (1 << h->n_tppr) - 1, sl.out_dev, bo, seq0, 0,
                       ep->st, nullptr, 0, &cl)) return 1;
     CU(cudaEventRecord(sl.ev_kernel, ep->st));
@@ -1494,7 +1554,15 @@ int zebra_tppr_epoch_begin(zebra_tppr_t *h, const int32_t *host_src, const int32
     for (int j = 0; j < h->n_tppr; ++j)
         if (!h->tables[j]) return fail("zebra_tppr_bind_tables has not been called");
     if (h->plan_active || h->epoch_active) return fail("another plan or epoch is in progress on this handle");
-    if (h->world > 1) return fail("node-sharded handles stream through plans (zebra_tppr_plan_run)");
+    if (h->world > 1) {
+        if (rows_per_edge && (batches_per_window % h->world) != 0 && h->row_mode == 1)
+            return fail("node-sharded epoch: batches_per_window must be a multiple of the world size (batch b is consumed by rank b mod world)");
+        if (batch_size * batches_per_window > h->max_window_edges) return fail("window exceeds the mailbox window given to zebra_tppr_shard_init");
+        if (rows_per_edge && 2 * static_cast<size_t>(batches_per_window) * zebra_tppr_out_bytes(h, batch_size, rows_per_edge) > h->out_region)
+            return fail("node-sharded epoch needs an output region of two windows of rows (zebra_tppr_shard_init out_bytes)");
+        for (int r = 0; r < h->world; ++r)
+            if (!h->peer_arena[r]) return fail("zebra_tppr_shard_connect has not been called");
+    }
     CU(cudaSetDevice(h->device));
     if (!h->copy_stream) CU(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
     zebra_epoch *ep = new zebra_epoch();
@@ -1505,6 +1573,14 @@ int zebra_tppr_epoch_begin(zebra_tppr_t *h, const int32_t *host_src, const int32
     ep->n_windows = (ep->n_batches + ep->window - 1) / ep->window;
     ep->slot_bytes = zebra_tppr_out_bytes(h, batch_size, rows_per_edge);
     ep->st = static_cast<cudaStream_t>(stream);
+    if (h->world > 1 && rows_per_edge) {
+        // everything this rank received before this epoch has been consumed: both halves may be stored into
+        zebra::ShardDoneParams dp;
+        for (int r = 0; r < zebra::kMaxRanks; ++r) dp.hdr[r] = r < h->world ? reinterpret_cast<int32_t *>(h->peer_arena[r]) : nullptr;
+        dp.world = h->world; dp.rank = h->rank; dp.value = static_cast<int32_t>(h->shard_launches); dp.slot = 1;
+        zebra::shard_done_kernel<<<1, 32, 0, ep->st>>>(dp);
+        CU(cudaGetLastError());
+    }
     detect_chains<int32_t>(h, host_src, host_dst, n, ep->cs);
     h->chain_items = 0; h->chain_steps = 0;
     CU(cudaMemsetAsync(h->status + 1, 0, 3 * sizeof(int32_t), ep->st));
@@ -1516,7 +1592,12 @@ int zebra_tppr_epoch_begin(zebra_tppr_t *h, const int32_t *host_src, const int32
     // worker threads for the host dependency pass (the GPU needs ~45 ns per edge of a hub-bound stream, one
     // host thread ~55 ns): windows are independent of each other, so they are prepared in parallel, ahead
     int n_workers = h->host_threads;
-    if (n_workers < 0) n_workers = static_cast<int>(std::min<unsigned>(3, std::max(1u, std::thread::hardware_concurrency()) - 1));
+    if (n_workers < 0) {
+        // share the host cores with the other ranks of the box (torchrun sets LOCAL_WORLD_SIZE)
+        unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+        if (const char *e = getenv("LOCAL_WORLD_SIZE")) hw = std::max(1u, hw / static_cast<unsigned>(std::max(1, atoi(e))));
+        n_workers = static_cast<int>(std::min<unsigned>(3, hw - 1));
+    }
     if (ep->n_windows < 4) n_workers = 0;
     n_workers = std::min<int>(n_workers, zebra_tppr::kPrepSlots - 2);
     for (int t = 0; t < n_workers; ++t) {
@@ -1628,6 +1709,7 @@ int zebra_tppr_shard_init(zebra_tppr_t *h, int32_t rank, int32_t world, int64_t 
         // kernels — e.g. this rank's span kernel, which itself waits for a peer the host has not launched yet
         cudaFuncAttributes fa;
         CU(cudaFuncGetAttributes(&fa, zebra::shard_done_kernel));
+        CU(cudaFuncGetAttributes(&fa, zebra::shard_wait_kernel));
     }
     if (ipc_handle_out) {
         cudaIpcMemHandle_t mh;

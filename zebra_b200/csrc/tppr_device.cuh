@@ -132,6 +132,7 @@ struct SpanParams {
     int32_t world_log2, rank, mbox_parity;
     int32_t shard_launch;                           // index of this sharded launch on the handle (same on every rank)
     const int32_t *shard_done;                      // own arena header: [r] = launches rank r has finished
+    int32_t row_guard;                              // pipelined epoch: wait for the consumer rank before storing its rows
     int32_t row_mode;                               // 0: rows to every rank; 1: rows of batch b to rank b & (world-1) only
     const int32_t *list;                            // sharded: span indices of the edges this rank takes part in (this launch's range)
     int64_t n_list;
@@ -248,7 +249,8 @@ struct Waiter {
     unsigned long long t0 = 0;
     // `code`, `a`, `b`: what was being waited for, recorded in status[4..6] by the first wait that expires
     // (1 table record of src/dst, 2 chain mailbox slot, 3 negative-sample readers, 4 negative's record,
-    //  5 chain: own record, 6 chain: partner chain's push, 7 chain: partner's record, 8 peer GPU's push)
+    //  5 chain: own record, 6 chain: partner chain's push, 7 chain: partner's record, 8 peer GPU's push,
+    //  9 consumer rank has not copied its rows out yet, 10 a rank has not finished the launch)
     __device__ __forceinline__ void log_wait(int32_t *status, int code, uint32_t a, uint32_t b, int32_t c)
     {
         if ((threadIdx.x & 31) != 0) return;

@@ -42,16 +42,32 @@ __device__ __forceinline__ int32_t ld_relaxed_sys_s32(const int32_t *p)
     return v;
 }
 
-struct ShardDoneParams { int32_t *hdr[kMaxRanks]; int32_t world, rank, value; };
+// Arena header: int32 [0..kMaxRanks) launches each rank has FINISHED, [kMaxRanks..2 kMaxRanks) launches whose
+// rows each rank has COPIED out of its output region (pipelined epochs).
+struct ShardDoneParams { int32_t *hdr[kMaxRanks]; int32_t world, rank, value, slot; };
 
-// One warp, launched behind every sharded span kernel on the same stream: lane r stores this rank's count of
-// finished launches into rank r's arena header (release at system scope: the kernel's reads are done).
+// One warp, launched behind a sharded span kernel (slot 0) or behind the copy of a window's rows (slot 1) on
+// the same stream: lane r stores this rank's count into rank r's arena header (release at system scope).
 __global__ void shard_done_kernel(const ShardDoneParams d)
 {
     const int r = threadIdx.x;
     if (r < d.world) {
         __threadfence_system();
-        asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(d.hdr[r] + d.rank), "r"(d.value) : "memory");
+        asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(d.hdr[r] + d.slot * kMaxRanks + d.rank), "r"(d.value) : "memory");
+    }
+}
+
+// Holds a stream until every rank has finished `value` launches (their rows for this rank have landed).
+__global__ void shard_wait_kernel(const int32_t *done, int32_t world, int32_t value, int32_t *status, unsigned long long wait_ns)
+{
+    const int r = threadIdx.x;
+    if (r < world) {
+        Waiter w;
+        while (ld_relaxed_sys_s32(done + r) < value) {
+            if (w.expired(status, wait_ns, 10, static_cast<uint32_t>(value), static_cast<uint32_t>(r))) break;
+            __nanosleep(1000);
+        }
+        __threadfence_system();
     }
 }
 
@@ -69,6 +85,7 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
     const uint32_t tag_base = p.seq0 + static_cast<uint32_t>(p.tag_offset);
     const int lg = p.world_log2, me = p.rank, pmask = (1 << lg) - 1, world = 1 << lg;
     unsigned stats = 0;
+    unsigned rows_ok = 0;                   // ranks known to have drained the output half this launch stores into
     unsigned peers_ok = 0;                  // partners known to have left the mailbox half of this launch's parity
     char *const my_mbox = p.mbox_peer[me] + static_cast<size_t>(p.mbox_parity) * p.mbox_half_bytes;
 
@@ -209,6 +226,16 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
             const bool eS = oS, eD = oD;
             const bool eG = has_neg && (neg_own ? oG : (gN == sN ? oS : oD));
             for (int q = q_lo; q < q_hi; ++q) {
+                if (p.row_guard && !((rows_ok >> q) & 1u)) {
+                    // pipelined epochs: rank q must have copied out the rows of the launch that used this half
+                    // of its output region before (launch - 2); it publishes how far it has copied
+                    Waiter wr;
+                    while (ld_relaxed_sys_s32(p.shard_done + kMaxRanks + q) < p.shard_launch - 1) {
+                        if (wr.expired(p.status, p.wait_ns, 9, my_tag, static_cast<uint32_t>(q))) break;
+                        __nanosleep(500);
+                    }
+                    rows_ok |= 1u << q;
+                }
                 char *obase = p.out_peer[q] + off;
                 if (eS) emit_row(p, obase, plane, row, S, t, lane);
                 if (eD) emit_row(p, obase, plane, row + nrow, D, t, lane);

@@ -141,6 +141,17 @@ class ShardedFinder:
         from .finder import StreamPlan
         return _ShardedPlan(self, src, dst, neg, timestamps, edge_idxs, batch_size, rows_per_edge)
 
+    def epoch(self, src, dst, neg, timestamps, edge_idxs, batch_size, rows_per_edge=3, window=None):
+        """Pipelined pass over a chronological span held in HOST memory (include/zebra_tppr.h "pipelined
+        epochs" on a node-sharded handle): every rank calls it with the same replicated arrays.  Windows of
+        `window` batches (a multiple of the world size) are staged (ownership-aware dependency pass on worker
+        threads), computed by the sharded span kernel and — once every rank has finished the window — this
+        rank's batches (b % world == rank under row_mode 1, all batches under row_mode 0) are copied to pinned
+        host memory.  Returns an iterator that yields (batch index, nodes, eidx, dt, w), each a list of n_tppr
+        numpy arrays [rows, k] exactly like `tppr_finder.streaming_topk` of that batch (views of pinned library
+        memory, valid until the iterator moves past their window)."""
+        return _ShardedEpoch(self, src, dst, neg, timestamps, edge_idxs, batch_size, rows_per_edge, window)
+
     def state(self, inst, nodes):
         """Vectors of `nodes` (all owned by this rank), like tppr_finder.state."""
         import torch
@@ -225,3 +236,61 @@ def create_sharded(num_nodes, k, n_tppr, alpha_list, beta_list, max_window_edges
     f.connect(gather_handles(f.ipc_handle, group))
     dist.barrier(group)
     return f
+
+
+class _ShardedEpoch:
+    def __init__(self, f, src, dst, neg, timestamps, edge_idxs, batch_size, rows_per_edge, window):
+        import torch
+        from .finder import _ptr
+        self.f = f
+        self.src = np.ascontiguousarray(src, dtype=np.int32)
+        self.dst = np.ascontiguousarray(dst, dtype=np.int32)
+        self.neg = None if neg is None else np.ascontiguousarray(neg, dtype=np.int32)
+        self.ts = np.ascontiguousarray(timestamps, dtype=np.float64)
+        self.eidx = np.ascontiguousarray(edge_idxs, dtype=np.int64)
+        self.n, self.bs, self.rows_per_edge = len(self.src), int(batch_size), int(rows_per_edge)
+        if window is None:
+            window = max(f.world, (f.max_window_edges // self.bs) // f.world * f.world)
+        self.window = int(window)
+        self._ep = C.c_void_p()
+        with torch.cuda.device(f.device):
+            f._check(f._L.zebra_tppr_epoch_begin(f._h, _ptr(self.src), _ptr(self.dst), _ptr(self.neg), _ptr(self.ts), _ptr(self.eidx),
+                                                 self.n, self.rows_per_edge, self.bs, self.window, f._stream_ptr(), C.byref(self._ep)))
+        self.slot = int(f._L.zebra_tppr_epoch_slot_bytes(self._ep))
+
+    def __iter__(self):
+        f, L = self.f, self.f._L
+        rows_ptr, b0, nb = C.c_void_p(), C.c_int64(), C.c_int64()
+        T, k, R = f.n_tppr, f.k, self.rows_per_edge * self.bs
+        mode1 = getattr(f, "row_mode", 0) == 1
+        try:
+            while True:
+                f._check(L.zebra_tppr_epoch_next(self._ep, C.byref(rows_ptr), C.byref(b0), C.byref(nb)))
+                if nb.value == 0:
+                    break
+                if not self.rows_per_edge:
+                    continue
+                first, cnt = b0.value, nb.value
+                mine = list(range(first + f.rank, first + cnt, f.world)) if mode1 else list(range(first, first + cnt))
+                if not mine:
+                    continue
+                raw = np.ctypeslib.as_array(C.cast(rows_ptr, C.POINTER(C.c_uint8)), shape=(len(mine) * self.slot,))
+                for q, b in enumerate(mine):
+                    edges = min(self.bs, self.n - b * self.bs)
+                    r = self.rows_per_edge * edges
+                    ti = raw[q * self.slot: q * self.slot + T * 16 * r * k].view(np.int32).reshape(T, 4, r, k)
+                    tf = ti.view(np.float32)
+                    yield (b, [ti[j, 0] for j in range(T)], [ti[j, 1] for j in range(T)], [tf[j, 2] for j in range(T)], [tf[j, 3] for j in range(T)])
+        finally:
+            self.close()
+
+    def close(self):
+        if getattr(self, "_ep", None):
+            self.f._L.zebra_tppr_epoch_end(self._ep)
+            self._ep = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
