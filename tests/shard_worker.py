@@ -26,7 +26,8 @@ def main():
     neg = synth.make_negatives(st, bs)
     N = st.shape.table_nodes
     n_batches = (n_edges + bs - 1) // bs
-    f = create_sharded(N, k, 2, al, be, window * bs, n_batches * 2 * 16 * 3 * bs * k)
+    wep = max(world, (min(window, n_batches) // world) * world)      # window of the pipelined epoch: a multiple of world
+    f = create_sharded(N, k, 2, al, be, window * bs, max(n_batches, 2 * wep) * 2 * 16 * 3 * bs * k)
     plan = f.make_plan(st.src, st.dst, neg, st.ts, st.eidx, bs)
     for rep in range(2):                       # second pass: reset + rerun must give the same bytes
         f.reset_tppr()
@@ -54,7 +55,6 @@ def main():
         dist.barrier()
     # pipelined sharded epoch (host arrays in, this rank's batches out in pinned host memory), twice
     f.set_row_mode(1)
-    wep = max(world, (window // world) * world)
     for rep in range(2):
         f.reset_tppr()
         cpu = oracle.OracleFinder(N, k, 2, al, be)

@@ -103,27 +103,31 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
         const int64_t li = tk / static_cast<uint32_t>(p.n_tppr);    // 32-bit division: items < 2^32
         const int j = tk - li * p.n_tppr;
         if (!((p.inst_mask >> j) & 1)) continue;
-        // the staging records of a sharded plan are compact: entry li describes edge list[li]
+        // the staging records of a sharded plan are compact: entry li describes edge list[li].  The whole
+        // record in one batch of independent loads, before any branch that depends on it.
         const int64_t i = static_cast<int64_t>(p.list[li]) - p.i_offset;     // launch-local edge index
         const int sN = p.src[li], dN = p.dst[li];
+        const int gN_raw = p.neg[li];
+        const uint32_t flags = p.flags[li];
+        const int32_t pS = p.prev_s[li], pD_raw = p.prev_d[li], pG_raw = p.prev_n[li];
+        const double t = p.ts[li];
+        const int e = p.eidx[li];
+        const uint32_t rwS = p.rthr_s[li], rwD_raw = p.rthr_d[li];
         const bool has_neg = p.rows_per_edge == 3;
-        const int gN = has_neg ? p.neg[li] : sN;
+        const int gN = has_neg ? gN_raw : sN;
         const bool loop = sN == dN;
         const bool neg_own = has_neg && gN != sN && gN != dN;
         const bool oS = (sN & pmask) == me, oD = loop ? oS : (dN & pmask) == me;
         const bool oG = neg_own && (gN & pmask) == me;
         if (!(oS || oD || oG)) continue;          // nothing of this edge lives here
-        const uint32_t flags = p.flags[li];
         int32_t *rcnt = p.rcnt[j];
-        const int32_t pS = p.prev_s[li], pD = loop ? -1 : p.prev_d[li], pG = neg_own ? p.prev_n[li] : -1;
+        const int32_t pD = loop ? -1 : pD_raw, pG = neg_own ? pG_raw : -1;
+        const uint32_t rwD = loop ? 0u : rwD_raw;
         char *table = p.tables[j];
         char *recS = table + static_cast<size_t>(sN >> lg) * p.stride;
         char *recD = table + static_cast<size_t>(dN >> lg) * p.stride;
         const char *recG = table + static_cast<size_t>(gN >> lg) * p.stride;
         const uint32_t my_tag = tag_base + static_cast<uint32_t>(i);
-        const double t = p.ts[li];
-        const int e = p.eidx[li];
-        const uint32_t rwS = p.rthr_s[li], rwD = loop ? 0u : p.rthr_d[li];
 
         const bool needSD = oS || oD;
         const bool cross = needSD && !(oS && oD);              // the other endpoint lives on another rank

@@ -195,9 +195,15 @@ def compute_embedding_tppr_ensemble(self, memory, source_nodes, timestamps, edge
     R, k, n_tppr = len(source_nodes), self.k, self.n_tppr
     dev = self.edge_features.device
 
-    t = time.time()
+    # the reference brackets its (synchronous, CPU) query with time.time() (embedding_module.py:220-225); the
+    # query here is enqueued asynchronously, so it is bracketed with CUDA events on the stream instead and the
+    # elapsed device time is added up when t_tppr is read (train.py:230, once per epoch) — see _TpprTimer
+    ev0 = torch.cuda.Event(enable_timing=True)
+    ev1 = torch.cuda.Event(enable_timing=True)
+    ev0.record()
     topk = _query_raw(self, source_nodes, timestamps, edge_idxs)
-    self.t_tppr += time.time() - t
+    ev1.record()
+    _timer(self).pending.append((ev0, ev1))
     plane = R * k
 
     lazy = None
@@ -248,9 +254,42 @@ def compute_embedding_tppr_ensemble(self, memory, source_nodes, timestamps, edge
     return embeddings
 
 
+class _TpprTimer:
+    """Seconds spent in the T-PPR query: CUDA-event time of every query since the last reset, summed when
+    read.  An event pair spans from the moment the stream reaches the query (or the host starts enqueuing it,
+    whichever is later) to the end of its last kernel — host dependency pass, H2D and kernel included."""
+
+    def __init__(self):
+        self.base, self.pending = 0.0, []
+
+    def read(self):
+        if self.pending:
+            self.pending[-1][1].synchronize()
+            self.base += sum(a.elapsed_time(b) for a, b in self.pending) * 1e-3
+            self.pending = []
+        return self.base
+
+
+def _timer(self):
+    t = self.__dict__.get("_zebra_tppr_timer")
+    if t is None:
+        t = self.__dict__["_zebra_tppr_timer"] = _TpprTimer()
+    return t
+
+
+def _get_t_tppr(self):
+    return _timer(self).read()
+
+
+def _set_t_tppr(self, value):
+    t = _timer(self)
+    t.base, t.pending = float(value), []
+
+
 def patch(module_cls):
     """Install the device-resident path on the reference's GraphDiffusionEmbedding class."""
     module_cls.compute_embedding_tppr_ensemble = compute_embedding_tppr_ensemble
+    module_cls.t_tppr = property(_get_t_tppr, _set_t_tppr)      # read by train.py:230, reset by model/tgn_model.py:121
     return module_cls
 
 
@@ -276,6 +315,8 @@ class GraphDiffusionEmbedding(torch.nn.Module):
     """Host-side mirror of the reference's GraphDiffusionEmbedding (modules/embedding_module.py:76-136,
     217-331) for users who do not run the reference's train.py: same parameter names (its state_dict
     loads here and vice versa), same T-PPR protocol methods, device-resident query + fused gather."""
+
+    t_tppr = property(_get_t_tppr, _set_t_tppr)       # CUDA-event time of the queries (see _TpprTimer)
 
     def __init__(self, edge_features, neighbor_finder, n_edge_features, n_time_features, embedding_dimension, device,
                  args, num_nodes):
