@@ -489,10 +489,16 @@ def run_ours(args):
             dist.destroy_process_group()
             return
 
-    # every rank streams its own replica of the workload (different seed): weak scaling, no exchange
-    st, neg = load_workload(n_edges=args.edges, seed=None if rank == 0 else 1005 + 100 * rank)
+    split = world > 1 and args.mode == "instances"
+    if split and world != len(ALPHAS):
+        raise SystemExit("--mode instances places one (alpha,beta) instance per GPU: run it with --gpus %d" % len(ALPHAS))
+    # replicas: every rank streams its own replica of the workload (different seed): weak scaling, no exchange.
+    # instances: every rank streams the SAME workload for ONE of the (alpha,beta) instances (utils/util.py:489-492:
+    # the instances never interact) — strong scaling over the instances, no exchange either.
+    st, neg = load_workload(n_edges=args.edges, seed=None if (rank == 0 or split) else 1005 + 100 * rank)
     E, N = st.n_edges, st.shape.table_nodes
-    f = tppr_finder(N, K, len(ALPHAS), ALPHAS, BETAS, device=dev)
+    al, be = ([ALPHAS[rank]], [BETAS[rank]]) if split else (ALPHAS, BETAS)
+    f = tppr_finder(N, K, len(al), al, be, device=dev)
     plan = f.make_plan(st.src, st.dst, neg, st.ts, st.eidx, BS)
     window = args.batches_per_launch
     out = plan.alloc_out(window)
@@ -535,7 +541,7 @@ def run_ours(args):
     # numba's argsort; reported beside the exact default
     stable_ms = None
     if not args.no_stable:
-        f2 = tppr_finder(N, K, len(ALPHAS), ALPHAS, BETAS, device=dev, tie_mode="stable")
+        f2 = tppr_finder(N, K, len(al), al, be, device=dev, tie_mode="stable")
         p2 = f2.make_plan(st.src, st.dst, neg, st.ts, st.eidx, BS)
         best = 1e30
         for _ in range(2):
@@ -571,7 +577,7 @@ def run_ours(args):
     e2e_s = time.perf_counter() - t0
     e2e_edges = E
     h2d = ((E + 7) // 8 * 8) * 48
-    d2h = len(ALPHAS) * 16 * 3 * E * K
+    d2h = len(al) * 16 * 3 * E * K
     launches_e2e = -(-plan.n_batches // args.e2e_window)
 
     # informational: the strict per-call drop-in (one synchronous streaming_topk per batch)
@@ -598,7 +604,7 @@ def run_ours(args):
     ms, e2e_s = float(t[0]), float(t[1])
     if rank == 0:
         peak, peak_src = peaks()
-        value = world * E * args.steps / (ms * 1e-3)
+        value = (1 if split else world) * E * args.steps / (ms * 1e-3)
         per_launch_ms = ms / max(launches, 1)
         alg_per_launch = E * bytes_per_edge() / n_launch
         achieved = alg_per_launch / (per_launch_ms * 1e-3) / 1e9
@@ -610,12 +616,13 @@ def run_ours(args):
             "config": {"workload": workload_text(st),
                        "edges_per_gpu": E,
                        "step": "reset tables + stream the whole span once",
-                       "batches_per_launch": window, "parallelism": f"replicas x{world}" if world > 1 else "single GPU",
-                       "l2": f"tables {len(ALPHAS) * N * f._record_bytes / 1e6:.0f} MB + outputs exceed the 126 MB L2 (inputs larger than L2)",
+                       "batches_per_launch": window, "parallelism": (f"one (alpha,beta) instance per GPU x{world}, same stream, no exchange" if split else
+                                                                       f"replicas x{world}") if world > 1 else "single GPU",
+                       "l2": f"tables {len(al) * N * f._record_bytes / 1e6:.0f} MB + outputs exceed the 126 MB L2 (inputs larger than L2)",
                        "tie_mode": "exact (numba argsort order replayed inside groups of equal scores; bit-identical to the reference)",
                        "tie_path_prunes_last_step": tie_prunes,
                        "chain_nodes": chain_info},
-            "e2e": {"value": world * e2e_edges * args.steps / e2e_s, "unit": UNIT,
+            "e2e": {"value": (1 if split else world) * e2e_edges * args.steps / e2e_s, "unit": UNIT,
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "step": f"all {plan.n_batches} batches through tppr_finder.stream_epoch (host numpy in, host numpy out per "
                             f"batch; windows of {args.e2e_window} batches pipelined: host dependency pass, H2D, kernel, D2H)",
@@ -689,8 +696,9 @@ def main():
     ap.add_argument("--traffic", type=float, default=None, help="ncu dram bytes per launch, if captured")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-flat", action="store_true", help="skip the hub-free throughput leg")
-    ap.add_argument("--mode", default="sharded", choices=["sharded", "replicas"],
-                    help="N>1: node-sharded state with in-kernel NVLink exchange (default), or independent replicas")
+    ap.add_argument("--mode", default="sharded", choices=["sharded", "replicas", "instances"],
+                    help="N>1: node-sharded state with in-kernel NVLink exchange (default), independent replicas, or one "
+                         "(alpha,beta) instance per GPU (needs --gpus = number of instances)")
     ap.add_argument("--no-strong", action="store_true", help="N>1: skip the strong-scaling leg (same stream as N=1, sharded)")
     args = ap.parse_args()
     global WORKLOAD

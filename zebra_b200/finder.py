@@ -108,12 +108,15 @@ class tppr_finder:  # noqa: N801  (name kept from the reference)
         if len(nodes) != max(rows_per_edge, 2) * n or len(ts) < n:
             raise ValueError("source_nodes/timestamps do not match edge_idxs")
         nbytes = self._L.zebra_tppr_out_bytes(self._h, n, rows_per_edge)
-        dev_out = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=self.device)
         host = None
         if to_host and nbytes:
+            # numpy-returning calls: the device copy of the rows is scratch, kept across calls (no allocation per batch)
             if self._host_out is None or self._host_out.numel() < nbytes:
                 self._host_out = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
-            host = self._host_out
+                self._dev_scratch = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+            host, dev_out = self._host_out, self._dev_scratch
+        else:
+            dev_out = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=self.device)
         with torch.cuda.device(self.device):
             check(self._L.zebra_tppr_stream(self._h, _ptr(nodes), _ptr(ts), _ptr(eidx), n, rows_per_edge, inst,
                                             _ptr(dev_out) if nbytes else None, _ptr(host), self._stream_ptr()))
@@ -129,13 +132,13 @@ class tppr_finder:  # noqa: N801  (name kept from the reference)
         dev_out, host, rows, nbytes = self._launch(source_nodes, timestamps, edge_idxs, rows_per_edge, inst, to_host)
         plane = rows * self.k
         if to_host:
-            buf = host.numpy()[:nbytes] if nbytes else np.zeros(0, np.uint8)
+            # one copy out of the pinned buffer (it is overwritten by the next call), then views of it
+            buf = host.numpy()[:nbytes].copy() if nbytes else np.zeros(0, np.uint8)
             outs = ([], [], [], [])
             for j in range(self.n_tppr):
                 base = j * plane * 16
                 for q, dt in enumerate((np.int32, np.int32, np.float32, np.float32)):
-                    a = buf[base + q * plane * 4: base + (q + 1) * plane * 4].view(dt).reshape(rows, self.k).copy()
-                    outs[q].append(a)
+                    outs[q].append(buf[base + q * plane * 4: base + (q + 1) * plane * 4].view(dt).reshape(rows, self.k))
             return outs
         outs = ([], [], [], [])
         for j in range(self.n_tppr):
