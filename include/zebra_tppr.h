@@ -116,6 +116,15 @@ int64_t zebra_tppr_plan_batches(const zebra_plan_t *plan);
  * (on a node-sharded handle only the edges this rank takes part in are staged, plus 4 per entry of its
  * work list). */
 size_t zebra_tppr_plan_bytes(const zebra_plan_t *plan);
+/* ---- link-prediction metrics of a batch on the device (replaces the per-batch D2H + three scikit-learn
+ *      calls of evaluation/evaluation.py:34-45 and train.py:218-227) -------------------------------------
+ * dev_pos / dev_neg: float32[n_total] probabilities of the positive / negative edges, cut into batches of
+ * batch_size (the last one may be shorter; batch_size <= 4096).  dev_out: float64[ceil(n_total/batch_size)][3]
+ * = average precision, ROC AUC, accuracy of every batch, as scikit-learn defines them for binary labels
+ * (distinct-threshold step integral / trapezoid; accuracy = mean(pos >= neg)).  Asynchronous. */
+int zebra_edge_metrics(const float *dev_pos, const float *dev_neg, int64_t n_total, int64_t batch_size,
+                       double *dev_out, void *stream);
+
 /* Test / debug hook: copies the raw record of `node` in instance `inst` (zebra_tppr_record_bytes bytes:
  * header chunk and 2k entry chunks, each ending in its 32-bit tag) to host memory.  Synchronous. */
 int zebra_debug_read_record(zebra_tppr_t *h, int32_t inst, int64_t node, void *host_out);

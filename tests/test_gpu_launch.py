@@ -1,5 +1,5 @@
 """Row A12: the reference's own, unmodified train.py (a copy under baseline/_ref, made by
-__graft_entry__.build()) driven through `python -m zebra_b200.launch` at levels 0, 1 and 2, one
+__graft_entry__.build()) driven through `python -m zebra_b200.launch` at levels 0, 1, 2 and 3, one
 epoch on a tiny Wikipedia-shaped stream, against `--level ref` (the reference's numba finder).
 Same seed, same flags: validation / new-node validation / test AP must agree within 0.2 points
 (north_star), and level 0 — which only swaps the finder classes — to the last printed digit.
@@ -42,12 +42,12 @@ def test_train_py_through_launcher_matches_reference(tmp_path, strategy):
     st = synth.make_stream(name, n_edges=4000)
     synth.write_ml_format(st, str(tmp_path / "data"), name)
     res = {}
-    for level in ("ref", "0", "1", "2"):
+    for level in ("ref", "0", "1", "2", "3"):
         work = tmp_path / f"run_{level}"
         work.mkdir()
         res[level] = _run(level, str(work), name, strategy)
     ref_v, ref_s = res["ref"]
     assert res["0"][1] == ref_s, f"level 0 must print the reference's AP digits: {res['0'][1]} vs {ref_s}"
-    for level in ("1", "2"):
+    for level in ("1", "2", "3"):
         for a, b in zip(res[level][0], ref_v):
             assert abs(a - b) <= 0.002, (level, res[level][1], ref_s)       # 0.2 AP points

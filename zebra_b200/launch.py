@@ -1,6 +1,6 @@
 """Run the reference's own `train.py`, untouched, with the B200 hot path dropped in.
 
-    python -m zebra_b200.launch --ref /path/to/Zebra [--level 0|1|2|ref] [--workdir DIR] -- <train.py flags>
+    python -m zebra_b200.launch --ref /path/to/Zebra [--level 0|1|2|3|ref] [--workdir DIR] -- <train.py flags>
 
 `--ref`     checkout of LuckyLYM/Zebra (its train.py, model/, modules/, utils/ are imported as they are).
 `--level`   1 (default): `utils.util.tppr_finder`, `utils.util.NeighborFinder`/`get_neighbor_finder` are
@@ -8,6 +8,9 @@
                by the device-resident version (fused gather);
             2: level 1 plus the lazy memory update on the device (zebra_pending_select + zebra_gather_*_lazy:
                no per-batch D2H of the neighbour ids, no host-side unique, no clone of the whole memory);
+            3: level 2 plus the link-prediction metrics off scikit-learn (zebra_b200/metrics.py): validation and
+               test passes score their batches on the device with one D2H per pass, the training loop's per-batch
+               metrics use cheap host restatements of the same definitions;
             0: only the finder classes are replaced (numpy in / numpy out, the strict drop-in);
             ref: nothing is replaced (the reference's numba CPU path; used for the side-by-side runs).
 `--workdir` directory to run in; the reference reads `../data/{name}/ml_{name}.csv|.npy` relative to it
@@ -54,16 +57,19 @@ def install(level: str):
     ref_util.get_neighbor_finder = neighbor_finder.get_neighbor_finder
     import modules.embedding_module as em          # binds `from utils.util import tppr_finder` -> ours
     em.tppr_finder = finder.tppr_finder
-    if level in ("1", "2"):
+    if level in ("1", "2", "3"):
         from . import embedding
-        embedding.LAZY_MEMORY = level == "2"
+        embedding.LAZY_MEMORY = level in ("2", "3")
         embedding.patch(em.GraphDiffusionEmbedding)
+    if level == "3":
+        from . import metrics
+        metrics.install()
 
 
 def main(argv=None):
     ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
     ap.add_argument("--ref", required=True)
-    ap.add_argument("--level", default="1", choices=["0", "1", "2", "ref"])
+    ap.add_argument("--level", default="1", choices=["0", "1", "2", "3", "ref"])
     ap.add_argument("--workdir", default=None)
     ap.add_argument("rest", nargs=argparse.REMAINDER)
     a = ap.parse_args(argv)
