@@ -116,6 +116,18 @@ int64_t zebra_tppr_plan_batches(const zebra_plan_t *plan);
  * (on a node-sharded handle only the edges this rank takes part in are staged, plus 4 per entry of its
  * work list). */
 size_t zebra_tppr_plan_bytes(const zebra_plan_t *plan);
+/* ---- raw messages of a batch in one kernel (model/tgn_model.py:204-226: four index operations, a time
+ *      encoding and a torch.cat per batch, each behind its own small host-to-device copy) -----------------
+ * For row r: dev_messages[r] = [ memory[u_r] | memory[v_r] | edge_feat[e_r] | cos((t_r - last_update[u_r]) * w + b) ],
+ * float32, 2*dim_mem + dim_edge + dim_time columns.  dev_u: the distinct nodes of [src ; dst] whose last
+ * interaction of the batch is (partner dev_v, edge dev_e, float32 time dev_t).  The time encoding is the
+ * gather's (libdevice cosf, separate multiply and add).  An out-of-range id sets the sticky flag that
+ * zebra_gather_check reports.  Asynchronous. */
+int zebra_raw_messages(const int32_t *dev_u, const int32_t *dev_v, const int32_t *dev_e, const float *dev_t, int64_t n_rows,
+                       const float *dev_memory, int64_t num_nodes, int32_t dim_mem, const float *dev_last_update,
+                       const float *dev_edge_feat, int64_t n_edge_rows, int32_t dim_edge, const float *dev_time_w,
+                       const float *dev_time_b, int32_t dim_time, float *dev_messages, void *stream);
+
 /* ---- link-prediction metrics of a batch on the device (replaces the per-batch D2H + three scikit-learn
  *      calls of evaluation/evaluation.py:34-45 and train.py:218-227) -------------------------------------
  * dev_pos / dev_neg: float32[n_total] probabilities of the positive / negative edges, cut into batches of

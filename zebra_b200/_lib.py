@@ -61,6 +61,7 @@ SIGNATURES = {
     "zebra_gather_fwd_lazy": (C.c_int, [_VP, _I32, _I64, _I32, _VP, _I64, _I32, _VP, _I64, _I32, _VP, _VP, _I32, _VP, _VP, _VP, _VP,
                                         _VP, _VP, _VP, _VP]),
     "zebra_gather_bwd_lazy": (C.c_int, [_I32, _I64, _I32, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _I64, _I32, _I32, _VP]),
+    "zebra_raw_messages": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _VP, _I64, _I32, _VP, _VP, _I64, _I32, _VP, _VP, _I32, _VP, _VP]),
     "zebra_edge_metrics": (C.c_int, [_VP, _VP, _I64, _I64, _VP, _VP]),
     "zebra_last_error": (C.c_char_p, []),
     "zebra_build_info": (C.c_char_p, []),

@@ -97,6 +97,32 @@ int zebra_gather_fwd(const void *dev_topk, int32_t n_tppr, int64_t rows, int32_t
                            nullptr, stream);
 }
 
+int zebra_raw_messages(const int32_t *dev_u, const int32_t *dev_v, const int32_t *dev_e, const float *dev_t, int64_t n_rows,
+                       const float *dev_memory, int64_t num_nodes, int32_t dim_mem, const float *dev_last_update,
+                       const float *dev_edge_feat, int64_t n_edge_rows, int32_t dim_edge, const float *dev_time_w,
+                       const float *dev_time_b, int32_t dim_time, float *dev_messages, void *stream)
+{
+    if (n_rows <= 0) return 0;
+    if (!dev_u || !dev_v || !dev_e || !dev_t || !dev_memory || !dev_last_update || !dev_edge_feat || !dev_time_w || !dev_time_b ||
+        !dev_messages)
+        return fail("null device pointer");
+    if (ensure_status()) return 1;
+    zebra::RawMsgParams p;
+    memset(&p, 0, sizeof p);
+    p.u = dev_u; p.v = dev_v; p.e = dev_e; p.t = dev_t; p.U = n_rows; p.num_nodes = num_nodes; p.n_edge_rows = n_edge_rows;
+    p.memory = dev_memory; p.last_update = dev_last_update; p.edge_feat = dev_edge_feat; p.time_w = dev_time_w; p.time_b = dev_time_b;
+    p.Dm = dim_mem; p.De = dim_edge; p.Dt = dim_time; p.msg = dev_messages; p.status = g_status;
+    const int D = 2 * dim_mem + dim_edge + dim_time;
+    const bool vec = dim_mem % 4 == 0 && dim_edge % 4 == 0 && D % 4 == 0 && aligned16(dev_memory) && aligned16(dev_edge_feat) &&
+                     aligned16(dev_messages);
+    const unsigned blocks = static_cast<unsigned>((n_rows + 7) / 8);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (vec) zebra::raw_message_kernel<true><<<blocks, 256, 0, st>>>(p);
+    else zebra::raw_message_kernel<false><<<blocks, 256, 0, st>>>(p);
+    CU(cudaGetLastError());
+    return 0;
+}
+
 int zebra_gather_bwd(const void *dev_topk, int32_t n_tppr, int64_t rows, int32_t k, const float *dev_gx,
                      const float *dev_wn, const float *dev_gsrc, const int32_t *dev_src_nodes, float *dev_gmemory,
                      int64_t num_nodes, int32_t dim_mem, int32_t dim_total, void *stream)

@@ -308,4 +308,42 @@ pending_compact_kernel(const uint32_t *bitmap, int64_t n_words, int32_t *wordpre
     }
 }
 
+// ---- raw messages (model/tgn_model.py:204-226) --------------------------------
+// After a batch the reference builds, for every distinct node u of [src ; dst] (its LAST interaction of the
+// batch, partner v, edge e, time t):  message[u] = [ memory[u] | memory[v] | edge_features[e] |
+// cos((float(t) - last_update[u]) * w + b) ], with four separate index operations, a time encoding and a
+// torch.cat, each after its own small host-to-device copy.  One warp per node does all of it here.
+struct RawMsgParams {
+    const int32_t *u, *v, *e;      // [U] distinct nodes (ascending), their partners, edge ids
+    const float *t;                // [U] float32 edge times
+    int64_t U, num_nodes, n_edge_rows;
+    const float *memory, *last_update, *edge_feat, *time_w, *time_b;
+    int32_t Dm, De, Dt;
+    float *msg;                    // [U, 2*Dm + De + Dt]
+    int32_t *status;
+};
+
+template <bool VEC>
+__global__ void __launch_bounds__(256)
+raw_message_kernel(const RawMsgParams p)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t r = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    if (r >= p.U) return;
+    const int u = p.u[r], v = p.v[r], e = p.e[r];
+    if (u < 0 || u >= p.num_nodes || v < 0 || v >= p.num_nodes || e < 0 || e >= p.n_edge_rows) {
+        if (lane == 0) atomicExch(p.status, 1);
+        return;
+    }
+    const int D = 2 * p.Dm + p.De + p.Dt;
+    float *x = p.msg + static_cast<size_t>(r) * D;
+    copy_row<VEC>(x, p.memory + static_cast<size_t>(u) * p.Dm, p.Dm, lane);
+    copy_row<VEC>(x + p.Dm, p.memory + static_cast<size_t>(v) * p.Dm, p.Dm, lane);
+    copy_row<VEC>(x + 2 * p.Dm, p.edge_feat + static_cast<size_t>(e) * p.De, p.De, lane);
+    const float dt = __fsub_rn(p.t[r], __ldg(p.last_update + u));
+    float *xt = x + 2 * p.Dm + p.De;
+    for (int c = lane; c < p.Dt; c += 32)
+        xt[c] = cos_arg(__fadd_rn(__fmul_rn(dt, __ldg(p.time_w + c)), __ldg(p.time_b + c)));
+}
+
 }  // namespace zebra

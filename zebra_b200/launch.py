@@ -8,7 +8,8 @@
                by the device-resident version (fused gather);
             2: level 1 plus the lazy memory update on the device (zebra_pending_select + zebra_gather_*_lazy:
                no per-batch D2H of the neighbour ids, no host-side unique, no clone of the whole memory);
-            3: level 2 plus the link-prediction metrics off scikit-learn (zebra_b200/metrics.py): validation and
+            3: level 2 plus the raw messages of a batch built by one kernel (zebra_b200/messages.py) and the
+               link-prediction metrics off scikit-learn (zebra_b200/metrics.py): validation and
                test passes score their batches on the device with one D2H per pass, the training loop's per-batch
                metrics use cheap host restatements of the same definitions;
             0: only the finder classes are replaced (numpy in / numpy out, the strict drop-in);
@@ -62,8 +63,9 @@ def install(level: str):
         embedding.LAZY_MEMORY = level in ("2", "3")
         embedding.patch(em.GraphDiffusionEmbedding)
     if level == "3":
-        from . import metrics
+        from . import messages, metrics
         metrics.install()
+        messages.install()
 
 
 def main(argv=None):
