@@ -354,6 +354,9 @@ typedef struct { int64_t node; double ts; double w; } zo_query;
  * int_power_impl), not libm pow: verified against numba 0.65.0 for beta=0.95, n=1..399. */
 static double pow_int(double a, int64_t n)
 {
+    /* beyond 0x10000 numba's int_power_impl hands over to libm: math.pow(a, float(n)) (checked against
+     * numba 0.65.0: beta = 0.999 / 0.9999, n = 65536 squaring, n = 65537, 70000, 200000 libm) */
+    if (n > 0x10000) return pow(a, (double)n);
     double r = 1.0;
     while (n != 0) {
         if (n & 1) r *= a;

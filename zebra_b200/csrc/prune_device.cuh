@@ -43,7 +43,10 @@ __host__ __device__ inline size_t prune_scratch_bytes(int64_t t_max)
 }
 
 __device__ __forceinline__ double pow_int(double a, int64_t n)
-{   // numba lowers float ** int to exponentiation by squaring
+{   // numba lowers float ** int to exponentiation by squaring; beyond 0x10000 it calls libm's pow(a, float(n)).
+    // CUDA's pow is within 1 ulp of libm's, not guaranteed bit-identical: a node with more than 65,536 earlier
+    // neighbours (and beta so close to 1 that beta^65537 has not underflowed) may differ in the last bit there.
+    if (n > 0x10000) return pow(a, static_cast<double>(n));
     double r = 1.0;
     while (n != 0) {
         if (n & 1) r = __dmul_rn(r, a);

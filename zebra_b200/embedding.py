@@ -32,6 +32,10 @@ REPRODUCIBLE_BACKWARD = os.environ.get("ZEBRA_GATHER_BACKWARD", "sorted").lower(
 # weight normalisation of the neighbour sum: the reference's torch ops (default, bit-identical) or the fused
 # kernel's output (ZEBRA_WEIGHT_NORM=fused: saves four small launches per instance, last-bit differences)
 EXACT_WEIGHT_NORM = os.environ.get("ZEBRA_WEIGHT_NORM", "torch").lower() != "fused"
+# ZEBRA_VALIDATE_IDS=1: every fused gather is followed by zebra_gather_check (one synchronisation per batch), so
+# an out-of-range node / edge id raises at once like the reference's torch indexing; off by default, where
+# such a row is skipped and the sticky flag is reported by the next zebra_gather_check
+VALIDATE_IDS = os.environ.get("ZEBRA_VALIDATE_IDS", "0") == "1"
 
 
 # lazy memory update on the device (level 2): the pending set is selected by a kernel,
@@ -73,6 +77,8 @@ class FusedGather(torch.autograd.Function):
             st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
             check(L.zebra_gather_fwd(_p(topk), n_tppr, rows, k, _p(memory), N, Dm, _p(edge_features), Ee, De,
                                      _p(time_w), _p(time_b), Dt, _p(src_nodes), _p(X), _p(wn), _p(src_rows), st))
+            if VALIDATE_IDS:
+                check(L.zebra_gather_check(st))        # synchronises; raises on an out-of-range id, as the reference's indexing would
         ctx.save_for_backward(topk, src_nodes, wn)
         ctx.shape = (n_tppr, rows, k, N, Dm, D)
         ctx.mark_non_differentiable(wn)
@@ -125,6 +131,8 @@ class FusedGatherLazy(torch.autograd.Function):
             check(L.zebra_gather_fwd_lazy(_p(topk), n_tppr, rows, k, _p(memory), N, Dm, _p(edge_features), Ee, De,
                                           _p(time_w), _p(time_b), Dt, _p(src_nodes), _p(X), _p(wn), _p(src_rows),
                                           _p(upd_rows), _p(bitmap), _p(wordprefix), st))
+            if VALIDATE_IDS:
+                check(L.zebra_gather_check(st))
         ctx.save_for_backward(topk, src_nodes, wn, bitmap, wordprefix)
         ctx.shape = (n_tppr, rows, k, N, Dm, D, upd_rows.shape[0])
         ctx.mark_non_differentiable(wn)
