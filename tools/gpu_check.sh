@@ -17,12 +17,16 @@ bench)
   timeout 900 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"; cat gpurun_out/bench.json; tail -3 gpurun_out/bench.err
   timeout 600 python bench.py --impl reference --steps 1 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"; cat gpurun_out/bench_ref.json ;;
 ncu)
-  CMD="python bench.py --edges 400000 --steps 1 --warmup 1 --no-cpu --e2e-batches 10"
+  # launch list of the bench command, then one full capture each of a hub-bound and a hub-free launch of the span kernel
+  CMD="python bench.py --edges 400000 --steps 1 --warmup 3 --no-cpu --e2e-batches 10 --no-stable --no-numba"
   timeout 600 $CMD > gpurun_out/ncu_plain.log 2>&1 &&
-  timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launches.log 2>&1
+  timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launches.log 2>&1
   echo "ncu launches rc=$?"
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:tppr_span -s 40 -c 2 -f -o gpurun_out/prof $CMD > gpurun_out/ncu_full.log 2>&1
-  echo "ncu full rc=$?"; tail -3 gpurun_out/ncu_full.log ;;
+  for m in hub flat; do
+    timeout 300 python tools/ncu_targets.py $m > gpurun_out/ncu_target_$m.log 2>&1 &&
+    timeout 900 ncu --set full --clock-control none --import-source on -k regex:tppr_span_kernel -s 3 -c 2 -f -o gpurun_out/prof_$m python tools/ncu_targets.py $m > gpurun_out/ncu_full_$m.log 2>&1
+    echo "ncu full $m rc=$?"; tail -2 gpurun_out/ncu_full_$m.log
+  done ;;
 kernels)
   timeout 600 python tools/perf_kernels.py > gpurun_out/kernels.log 2>&1; echo "kernels rc=$?"; cat gpurun_out/kernels.log
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:"gather_fwd|prune_topk" -c 6 -f -o gpurun_out/prof_kernels python tools/perf_kernels.py > gpurun_out/ncu_kernels.log 2>&1

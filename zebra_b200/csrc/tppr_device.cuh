@@ -976,6 +976,7 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
         int64_t i;
         int j;
         bool from_ticket = false;
+        uint32_t my_tk = 0;
         if (hx < hx_end) {
             // helper: the next edge of the chain that is this warp's turn
             const ChainStep *st = p.csteps + hx;
@@ -1012,6 +1013,7 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
             i = tk / static_cast<uint32_t>(p.n_tppr);     // 32-bit division: items < 2^32
             j = static_cast<int>(tk - i * p.n_tppr);
             from_ticket = true;
+            my_tk = tk;
         }
         ZP_DECL;
         if (p.dbg_owner && lane == 0) {
@@ -1034,6 +1036,14 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
         const int e = p.eidx[i];
         const uint32_t rwS = p.rthr_s[i], rwD_raw = p.rthr_d[i];
         const int32_t ci = p.cidx[i];
+        // look-ahead (see below): the node whose record this lane will pull into L2, requested with the batch above
+        const unsigned long long tk2 = static_cast<unsigned long long>(my_tk) + gridDim.x * kWarpsPerBlock;
+        const int pf_lines = p.stride >> 7;
+        const bool pf = from_ticket && tk2 < total && lane < 3 * pf_lines;
+        const uint32_t pf_i = static_cast<uint32_t>(tk2) / static_cast<uint32_t>(p.n_tppr);
+        const int pf_r = lane / pf_lines;
+        int32_t pf_node = 0;
+        if (pf) pf_node = (pf_r == 0 ? p.src : (pf_r == 1 ? p.dst : p.neg))[pf_i];
         const bool has_neg = p.rows_per_edge == 3;
         const int gN = has_neg ? gN_raw : sN;
         const bool loop = sN == dN;
@@ -1071,6 +1081,16 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
         bool okG = neg_own ? try_load(recG, k, lane, pG < 0, p.seq0 + static_cast<uint32_t>(pG), G, curG) : true;
         bool alive = true;
         Waiter wt;
+        if (pf) {
+            // The item a whole front of ticket warps ahead will be claimed about one item-time from now: pull its
+            // three records into L2 (no registers held beyond one id per lane, nothing waited for — the id was
+            // requested together with this item's edge record and has arrived by now).  Without it a ticket warp
+            // spends most of an item waiting for DRAM (ncu: long-scoreboard stalls on the three record loads dominate
+            // the hub-free stream at 16 warps per SM).
+            const int j2 = static_cast<int>(static_cast<uint32_t>(tk2) - pf_i * p.n_tppr);
+            const char *a2 = p.tables[j2] + static_cast<size_t>(pf_node) * p.stride + 128 * (lane - pf_r * pf_lines);
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(a2));
+        }
         ZP_MARK(0);
         while (!(okS && okD)) {
             // distance (in edges) of the farther unsatisfied table producer from the version visible now
