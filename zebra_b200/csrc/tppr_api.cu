@@ -738,6 +738,10 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
             p.out_peer[r] = h->peer_arena[r] + kArenaHeader + 2 * h->mbox_half + out_off;
         }
         p.out = nullptr;
+        // pipelined epoch: the copy stream runs two one-warp kernels per window (wait for every rank, publish the
+        // copy) while the span kernel of a later window may be spinning for exactly that publication — the
+        // persistent grid must not fill the GPU to the last block slot, or those kernels could never start
+        if (p.row_guard) blocks = std::max(1, std::min(blocks, h->shard_max_blocks - 8));
         zebra::tppr_span_shard_kernel<<<blocks, zebra::kWarpsPerBlock * 32, 0, st>>>(p);
         // stream-ordered behind the kernel: tell every rank that this rank has finished (and stopped reading
         // the mailbox half of) this launch; a peer pushes into that half again only after seeing it
