@@ -373,9 +373,9 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
             def e2e_pass():
                 f.reset_tppr()
                 acc, cnt_b = 0.0, 0
-                for b, nd, ei, dt, w in f.epoch(st.src, st.dst, neg, st.ts, st.eidx, BS, window=window):
-                    acc += float(w[-1][0, 0]) + float(nd[0][-1, -1])
-                    cnt_b += 1
+                for bs_idx, nd, ei, dt, w in f.epoch(st.src, st.dst, neg, st.ts, st.eidx, BS, window=window, windows=True):
+                    acc += float(w[-1][:, 0, 0].sum()) + float(nd[0][:, -1, -1].sum())      # every batch's arrays are touched
+                    cnt_b += len(bs_idx)
                 assert cnt_b == len(range(rank, plan.n_batches, world)), (cnt_b, plan.n_batches)
                 return acc
 

@@ -201,5 +201,28 @@ def test_sharded_pipelined_epoch_matches_oracle(world, name, n_edges, bs, window
         for r in range(world):
             want = list(range(r, n_batches, world)) if row_mode == 1 else list(range(n_batches))
             assert seen[r] == want, (r, seen[r][:6])
+    # the same pass consumed window by window
+    for f in fs:
+        f.reset_tppr()
+    eps = []
+    for f, s_ in zip(fs, streams):
+        with torch.cuda.stream(s_):
+            eps.append(iter(f.epoch(st.src, st.dst, neg, st.ts, st.eidx, bs, window=window, windows=True)))
+    live = list(range(world))
+    got_batches = [[] for _ in fs]
+    while live:
+        for r in list(live):
+            item = next(eps[r], None)
+            if item is None:
+                live.remove(r)
+                continue
+            idxs, nd, ei, dt, w = item
+            for q, b in enumerate(idxs):
+                for got, want in zip((nd, ei, dt, w), refs[b]):
+                    for x, y in zip(got, want):
+                        assert np.array_equal(x[q], y), ("windows", r, b)
+                got_batches[r].append(b)
+    for r in range(world):
+        assert got_batches[r] == (list(range(r, n_batches, world)) if row_mode == 1 else list(range(n_batches)))
     for f in fs:
         assert f.counters()["timeouts"] == 0

@@ -141,7 +141,7 @@ class ShardedFinder:
         from .finder import StreamPlan
         return _ShardedPlan(self, src, dst, neg, timestamps, edge_idxs, batch_size, rows_per_edge)
 
-    def epoch(self, src, dst, neg, timestamps, edge_idxs, batch_size, rows_per_edge=3, window=None):
+    def epoch(self, src, dst, neg, timestamps, edge_idxs, batch_size, rows_per_edge=3, window=None, windows=False):
         """Pipelined pass over a chronological span held in HOST memory (include/zebra_tppr.h "pipelined
         epochs" on a node-sharded handle): every rank calls it with the same replicated arrays.  Windows of
         `window` batches (a multiple of the world size) are staged (ownership-aware dependency pass on worker
@@ -149,8 +149,10 @@ class ShardedFinder:
         rank's batches (b % world == rank under row_mode 1, all batches under row_mode 0) are copied to pinned
         host memory.  Returns an iterator that yields (batch index, nodes, eidx, dt, w), each a list of n_tppr
         numpy arrays [rows, k] exactly like `tppr_finder.streaming_topk` of that batch (views of pinned library
-        memory, valid until the iterator moves past their window)."""
-        return _ShardedEpoch(self, src, dst, neg, timestamps, edge_idxs, batch_size, rows_per_edge, window)
+        memory, valid until the iterator moves past their window).  `windows=True` yields one
+        (batch indices, nodes, eidx, dt, w) tuple per window instead, each array [n_own_batches, rows, k] (full
+        batches; a ragged last batch of the span comes as its own tuple)."""
+        return _ShardedEpoch(self, src, dst, neg, timestamps, edge_idxs, batch_size, rows_per_edge, window, windows)
 
     def state(self, inst, nodes):
         """Vectors of `nodes` (all owned by this rank), like tppr_finder.state."""
@@ -239,7 +241,7 @@ def create_sharded(num_nodes, k, n_tppr, alpha_list, beta_list, max_window_edges
 
 
 class _ShardedEpoch:
-    def __init__(self, f, src, dst, neg, timestamps, edge_idxs, batch_size, rows_per_edge, window):
+    def __init__(self, f, src, dst, neg, timestamps, edge_idxs, batch_size, rows_per_edge, window, windows=False):
         import torch
         from .finder import _ptr
         self.f = f
@@ -252,6 +254,7 @@ class _ShardedEpoch:
         if window is None:
             window = max(f.world, (f.max_window_edges // self.bs) // f.world * f.world)
         self.window = int(window)
+        self.by_window = bool(windows)
         self._ep = C.c_void_p()
         with torch.cuda.device(f.device):
             f._check(f._L.zebra_tppr_epoch_begin(f._h, _ptr(self.src), _ptr(self.dst), _ptr(self.neg), _ptr(self.ts), _ptr(self.eidx),
@@ -275,6 +278,21 @@ class _ShardedEpoch:
                 if not mine:
                     continue
                 raw = np.ctypeslib.as_array(C.cast(rows_ptr, C.POINTER(C.c_uint8)), shape=(len(mine) * self.slot,))
+                if self.by_window:
+                    ragged = (self.n - mine[-1] * self.bs) < self.bs
+                    full = len(mine) - (1 if ragged else 0)
+                    if full:
+                        wi = raw[:full * self.slot].view(np.int32).reshape(full, T, 4, R, k)
+                        wf = wi.view(np.float32)
+                        yield (mine[:full], [wi[:, j, 0] for j in range(T)], [wi[:, j, 1] for j in range(T)],
+                               [wf[:, j, 2] for j in range(T)], [wf[:, j, 3] for j in range(T)])
+                    if ragged:
+                        r = self.rows_per_edge * (self.n - mine[-1] * self.bs)
+                        ti = raw[full * self.slot: full * self.slot + T * 16 * r * k].view(np.int32).reshape(T, 4, r, k)
+                        tf = ti.view(np.float32)
+                        yield (mine[full:], [ti[None, j, 0] for j in range(T)], [ti[None, j, 1] for j in range(T)],
+                               [tf[None, j, 2] for j in range(T)], [tf[None, j, 3] for j in range(T)])
+                    continue
                 for q, b in enumerate(mine):
                     edges = min(self.bs, self.n - b * self.bs)
                     r = self.rows_per_edge * edges
