@@ -89,3 +89,14 @@ def test_csr_builder_matches_reference_order():
     assert indptr[-1] == 2 * st.n_edges
     v = int(st.src[5])
     assert np.all(np.diff(ts[indptr[v]:indptr[v + 1]]) >= 0)
+
+
+def test_loaded_library_matches_the_committed_sources():
+    """The .so the tests load is built from the csrc/ and include/ of this checkout: lib() rebuilds when the
+    content stamp written at build time does not match (zebra_b200/build.py), so a stale shipped binary
+    cannot be what runs."""
+    from zebra_b200 import _lib, build
+    L = _lib.lib()
+    assert not build.stale()
+    assert open(build.SO + ".stamp").read().strip() == build.source_digest()
+    assert b"sm_100a" in L.zebra_build_info()
