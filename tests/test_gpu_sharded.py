@@ -226,3 +226,77 @@ def test_sharded_pipelined_epoch_matches_oracle(world, name, n_edges, bs, window
         assert got_batches[r] == (list(range(r, n_batches, world)) if row_mode == 1 else list(range(n_batches)))
     for f in fs:
         assert f.counters()["timeouts"] == 0
+
+
+@pytest.mark.parametrize("world,seed,n_nodes,hot", [(2, 11, 60, 6), (4, 12, 500, 20), (2, 13, 30, 3)])
+def test_sharded_chain_warps_match_oracle(world, seed, n_nodes, hot):
+    """Hub chains in the node-sharded kernel: the owner rank of a hot node walks its edges with a resident chain
+    warp; partners on other ranks exchange vectors with it through the NVLink mailboxes.  Adversarial stream
+    (most edges between hot nodes, self-loops, negatives on hot nodes) through plans and the pipelined epoch."""
+    import torch
+    from tests.test_gpu_chains import _stream
+    from zebra_b200.sharded import ShardedFinder
+    E, bs, k, window = 16_000, 200, 20, 16
+    src, dst, neg, ts, eidx = _stream(seed, n_nodes, E, hot)
+    N = n_nodes + 1
+    n_batches = E // bs
+    slot = 2 * 16 * 3 * bs * k
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    cpu = oracle.OracleFinder(N, k, 2, AL, BE)
+    refs = []
+    for b in range(n_batches):
+        lo, hi = b * bs, (b + 1) * bs
+        nodes = np.concatenate([src[lo:hi], dst[lo:hi], neg[lo:hi]]).astype(np.int32)
+        refs.append(cpu.streaming_topk(nodes, np.concatenate([ts[lo:hi]] * 3), eidx[lo:hi]))
+    fs = [ShardedFinder(N, k, 2, AL, BE, r, world, window * bs, n_batches * slot) for r in range(world)]
+    for f in fs:
+        f.set_max_blocks(max(1, (2 * sms) // world))
+    ShardedFinder.connect_local(fs)
+    streams = [torch.cuda.Stream() for _ in fs]
+    plans = [f.make_plan(src, dst, neg, ts, eidx, bs) for f in fs]
+    torch.cuda.synchronize()
+    for f, p, s_ in zip(fs, plans, streams):
+        with torch.cuda.stream(s_):
+            p.run(0, n_batches, window, out_slots=n_batches)
+    for f, s_ in zip(fs, streams):
+        with torch.cuda.stream(s_):
+            f.sync_check()
+    torch.cuda.synchronize()
+    assert sum(f.counters()["chain_steps"] for f in fs) > 0
+    for b in range(n_batches):
+        for f, p in zip(fs, plans):
+            got = p.views(f.out, b, 0, n_batches)
+            for la, lb in zip(got, refs[b]):
+                for x, y in zip(la, lb):
+                    assert np.array_equal(x.cpu().numpy(), y), f"plan: rank {f.rank} batch {b}"
+    ids = np.arange(1, N)
+    for f in fs:
+        mine = ids[(ids & (world - 1)) == f.rank]
+        for j in range(2):
+            for a, (e, n, t, s, nm) in zip(mine, f.state(j, mine)):
+                oe, on, ot, os_, onm = cpu.state(j, int(a))
+                assert np.array_equal(e, oe) and np.array_equal(s, os_) and nm == onm, (f.rank, j, a)
+    # the pipelined epoch over the same stream (row mode 1)
+    for f in fs:
+        f.set_row_mode(1)
+        f.reset_tppr()
+    eps = []
+    for f, s_ in zip(fs, streams):
+        with torch.cuda.stream(s_):
+            eps.append(iter(f.epoch(src, dst, neg, ts, eidx, bs, window=window)))
+    live = list(range(world))
+    count = [0] * world
+    while live:
+        for r in list(live):
+            item = next(eps[r], None)
+            if item is None:
+                live.remove(r)
+                continue
+            b, nd, ei, dt, w = item
+            for got, want in zip((nd, ei, dt, w), refs[b]):
+                for x, y in zip(got, want):
+                    assert np.array_equal(x, y), ("epoch", r, b)
+            count[r] += 1
+    assert sum(count) == n_batches
+    for f in fs:
+        assert f.counters()["timeouts"] == 0

@@ -275,8 +275,9 @@ int ensure_staging(zebra_tppr *h, Staging &s, size_t edges)
     if (s.host) CU(cudaFreeHost(s.host));
     if (s.dev) CU(cudaFree(s.dev));
     size_t cap = std::max<size_t>(edges, 1024);
-    CU(cudaMallocHost(&s.host, cap * (kEdgeBytes + kStepBytesPerEdge)));
-    CU(cudaMalloc(&s.dev, cap * (kEdgeBytes + kStepBytesPerEdge)));
+    // arrays + (sharded epochs) the work list + the chain step records, worst case
+    CU(cudaMallocHost(&s.host, cap * (kEdgeBytes + kStepBytesPerEdge + 8) + 64));
+    CU(cudaMalloc(&s.dev, cap * (kEdgeBytes + kStepBytesPerEdge + 8) + 64));
     if (!s.free_ev) CU(cudaEventCreateWithFlags(&s.free_ev, cudaEventDisableTiming));
     s.cap = cap;
     return 0;
@@ -289,7 +290,7 @@ template <typename NodeT>
 void detect_chains(zebra_tppr *h, const NodeT *src, const NodeT *dst, int64_t n, ChainSet &cs)
 {
     cs.n = 0;
-    if (!h->chains_enabled || h->world > 1 || n < kChainMinEdges || h->max_chains <= 0) return;
+    if (!h->chains_enabled || n < kChainMinEdges || h->max_chains <= 0) return;
     const uint64_t N = static_cast<uint64_t>(h->num_nodes);
     if (h->chain_cnt.size() != N) h->chain_cnt.assign(N, 0);
     int32_t *cnt = h->chain_cnt.data();
@@ -318,14 +319,19 @@ void detect_chains(zebra_tppr *h, const NodeT *src, const NodeT *dst, int64_t n,
         return x.first != y.first ? x.first > y.first : x.second < y.second;
     });
     // every (chain, instance) gets a block of its own, resident next to the ticket blocks
-    const int room = std::max(0, h->max_blocks / 2 / std::max(1, h->n_tppr));
+    const int room = std::max(0, (h->world > 1 ? h->shard_max_blocks : h->max_blocks) / 2 / std::max(1, h->n_tppr));
     const int keep = std::min<int>({static_cast<int>(found.size()), h->max_chains, zebra::kMaxChains, room});
-    if (keep > 0) cs.map.assign(N, 0);
+    // node-sharded: every rank picks the same nodes from the same replicated span and keeps the ones it owns
+    int kept = 0;
     for (int q = 0; q < keep; ++q) {
-        cs.node[q] = found[static_cast<size_t>(q)].second;
-        cs.map[static_cast<size_t>(cs.node[q])] = static_cast<uint8_t>(q + 1);
+        const int32_t v = found[static_cast<size_t>(q)].second;
+        if (h->world > 1 && (v & (h->world - 1)) != h->rank) continue;
+        if (kept == 0) cs.map.assign(N, 0);
+        cs.node[kept] = v;
+        cs.map[static_cast<size_t>(v)] = static_cast<uint8_t>(kept + 1);
+        ++kept;
     }
-    cs.n = keep;
+    cs.n = kept;
 }
 
 // Fills one staging slot for m edges and derives their dependencies (one forward pass and a clean-up
@@ -523,7 +529,8 @@ int shard_work_list(zebra_tppr *h, const int32_t *src, const int32_t *dst, const
 // before src.  NodeDep::pad remembers, per node, the latest such edge still waiting for that answer;
 // the first later write of either endpoint settles it (a single edge rewriting both: no preference).
 void fill_soa_sharded(zebra_tppr *h, char *host, size_t cap, const int32_t *src, const int32_t *dst, const int32_t *neg,
-                      const double *ts, const int64_t *eidx, const std::vector<int32_t> &list, HostScratch *scratch = nullptr)
+                      const double *ts, const int64_t *eidx, const std::vector<int32_t> &list, HostScratch *scratch = nullptr,
+                      const ChainSet *cs = nullptr, ChainBuild *cb = nullptr)
 {
     const int32_t pm = h->world - 1, me = h->rank, lg = h->world_log2;
     int32_t *o_src = reinterpret_cast<int32_t *>(host);
@@ -531,6 +538,9 @@ void fill_soa_sharded(zebra_tppr *h, char *host, size_t cap, const int32_t *src,
     int32_t *p_s = o_e + cap, *p_d = p_s + cap, *p_n = p_d + cap;
     uint32_t *r_s = reinterpret_cast<uint32_t *>(p_n + cap), *r_d = r_s + cap, *flg = r_d + cap;
     double *o_ts = reinterpret_cast<double *>(flg + cap);
+    int32_t *o_cidx = reinterpret_cast<int32_t *>(o_ts + cap);
+    const uint8_t *cmap = (cb && cs && cs->n > 0) ? cs->map.data() : nullptr;
+    if (cb) cb->clear();
     NodeDep *dep = scratch ? scratch->dep.data() : h->dep.data();     // sized num_nodes >= local rows
     const size_t L = list.size();
     std::vector<int32_t> &rn = scratch ? scratch->rnext : h->rnext;
@@ -582,6 +592,31 @@ void fill_soa_sharded(zebra_tppr *h, char *host, size_t cap, const int32_t *src,
         if (oa) overwrite(*da, i, p_s[q], r_s[q]);
         if (wb) overwrite(*db, i, p_d[q], r_d[q]);
         if (oa && wb) { da->pad = static_cast<uint32_t>(q) + 1; db->pad = static_cast<uint32_t>(q) + 1; }
+        o_cidx[q] = -1;
+        if (cmap) {
+            // chain nodes this rank owns: their side of the edge goes to the resident chain warp
+            const uint8_t ca = oa ? cmap[a] : 0, cbq = wb ? cmap[b] : 0;
+            if (ca | cbq) {
+                const int32_t ci = cb->n_items++;
+                o_cidx[q] = ci;
+                const int32_t ee = static_cast<int32_t>(eidx[i]);
+                const bool loop = b == a, b_here = (b & pm) == me, a_here = oa;
+                if (ca) {
+                    flg[q] |= zebra::kFlagSrcChain | (static_cast<uint32_t>(ca - 1) << zebra::kFlagSrcChainShift);
+                    cb->steps[ca - 1].push_back(zebra::ChainStep{i, b, ee, (wb ? p_d[q] : -1), r_s[q],
+                                                                 (loop ? zebra::kStepLoop : 0u) | (cbq ? zebra::kStepPeerChain : 0u) |
+                                                                     ((!loop && !b_here) ? zebra::kStepPeerRemote : 0u),
+                                                                 ci, p_s[q], ts[i], static_cast<int64_t>(q)});
+                }
+                if (cbq) {
+                    flg[q] |= zebra::kFlagDstChain | (static_cast<uint32_t>(cbq - 1) << zebra::kFlagDstChainShift);
+                    cb->steps[cbq - 1].push_back(zebra::ChainStep{i, a, ee, (oa ? p_s[q] : -1), r_d[q],
+                                                                  zebra::kStepDst | (ca ? zebra::kStepPeerChain : 0u) |
+                                                                      (!a_here ? zebra::kStepPeerRemote : 0u),
+                                                                  ci, p_d[q], ts[i], static_cast<int64_t>(q)});
+                }
+            }
+        }
     }
     // the scratch goes back to "no writer, no reader": the local rows are few enough to refill wholesale
     const size_t local_rows = static_cast<size_t>((h->num_nodes - 1) >> lg) + 1;
@@ -667,12 +702,11 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
     p.out = out; p.ticket = h->ticket; p.status = h->status; p.prof = h->prof;
     p.wait_ns = h->wait_ns;
     p.tie_mode = h->tie_mode;
-    if (h->dbg_items && h->world == 1) {
-        const size_t need = static_cast<size_t>(m) * h->n_tppr * sizeof(uint32_t);
+    if (h->dbg_items) {
+        const size_t need = static_cast<size_t>(std::max<int64_t>(h->world > 1 ? n_list : m, 1)) * h->n_tppr * sizeof(uint32_t);
         if (h->dbg_cap < need) {
-            CU(cudaStreamSynchronize(st));
-            if (h->dbg_owner) CU(cudaFree(h->dbg_owner));
-            CU(cudaMalloc(&h->dbg_owner, need));
+            if (h->dbg_owner) CU(cudaFreeAsync(h->dbg_owner, st));
+            CU(cudaMallocAsync(reinterpret_cast<void **>(&h->dbg_owner), need, st));
             h->dbg_cap = need;
         }
         CU(cudaMemsetAsync(h->dbg_owner, 0, need, st));
@@ -684,11 +718,12 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
         // the mailbox of this launch: one slot per (chain item, instance, side)
         const size_t need = static_cast<size_t>(std::max(cl->n_items, 1)) * h->n_tppr * 2 * h->stride;
         if (h->cmbox_cap < need) {
-            CU(cudaStreamSynchronize(st));
-            if (h->cmbox) CU(cudaFree(h->cmbox));
+            // stream-ordered (cudaFree / cudaMalloc would wait for every kernel on the device — also for another
+            // rank's span kernel in the same process, which may be waiting for THIS launch)
+            if (h->cmbox) CU(cudaFreeAsync(h->cmbox, st));
             h->cmbox = nullptr; h->cmbox_cap = 0;
             const size_t grow = need + need / 4;
-            CU(cudaMalloc(&h->cmbox, grow));
+            CU(cudaMallocAsync(reinterpret_cast<void **>(&h->cmbox), grow, st));
             CU(cudaMemsetAsync(h->cmbox, 0, grow, st));
             h->cmbox_cap = grow;
         }
@@ -710,11 +745,12 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
     if (chain_warps) {
         // one block per (chain, instance): its warp 0 walks the chain, the others help; all resident, and
         // always some blocks of ticket warps next to them (the chains wait for what those produce)
-        blocks = std::max(blocks, std::min(h->max_blocks, chain_warps + std::max(16, chain_warps)));
-        if (chain_warps + 8 > blocks) return fail("%d chain blocks do not fit a resident grid of %d blocks", chain_warps, h->max_blocks);
+        const int cap_blocks = sharded ? h->shard_max_blocks : h->max_blocks;
+        blocks = std::max(blocks, std::min(cap_blocks, chain_warps + std::max(16, chain_warps)));
+        if (chain_warps + 8 > blocks) return fail("%d chain blocks do not fit a resident grid of %d blocks", chain_warps, cap_blocks);
         CU(cudaMemsetAsync(h->smflag, 0, 2 * zebra::kSmSlots * sizeof(int32_t), st));
         p.smflag = h->smflag;
-        p.max_yield = h->sm_yield ? std::max(0, (blocks - chain_warps) * zebra::kWarpsPerBlock - 256) : 0;
+        p.max_yield = (h->sm_yield && !sharded) ? std::max(0, (blocks - chain_warps) * zebra::kWarpsPerBlock - 256) : 0;
     }
     if (sharded) {
         if (m > h->max_window_edges) return fail("sharded launch of %lld edges exceeds the mailbox window (%lld)", (long long)m, (long long)h->max_window_edges);
@@ -730,6 +766,7 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
         p.world_log2 = h->world_log2; p.rank = h->rank; p.mbox_parity = static_cast<int32_t>(h->shard_launches & 1);
         p.row_mode = h->row_mode;
         p.shard_launch = static_cast<int32_t>(h->shard_launches);
+        p.rec_offset = lo;                              // chain steps name their staging record by its index in the image
         p.row_guard = (h->epoch_active && rows_per_edge) ? 1 : 0;
         p.shard_done = reinterpret_cast<const int32_t *>(h->arena);     // header of the own arena: launches every rank has finished
         p.mbox_half_bytes = static_cast<int64_t>(h->mbox_half);
@@ -763,9 +800,10 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
 
 // Appends the chain step records of a single-launch staging image right behind its arrays (chain after
 // chain) and describes them for the launch.  Returns the bytes of the image to upload.
-size_t place_chain_steps(const ChainSet &cs, char *host, char *dev, size_t cap, const ChainBuild &cb, ChainLaunch &cl)
+size_t place_chain_steps(const ChainSet &cs, char *host, char *dev, size_t cap, const ChainBuild &cb, ChainLaunch &cl,
+                         size_t extra = 0)
 {
-    size_t bytes = cap * kEdgeBytes;
+    size_t bytes = cap * kEdgeBytes + extra;          // `extra`: bytes between the arrays and the step records (sharded: the work list)
     cl.n = 0;
     if (cs.n == 0 || cb.n_items == 0) return bytes;
     zebra::ChainStep *dst = reinterpret_cast<zebra::ChainStep *>(host + bytes);
@@ -1163,9 +1201,32 @@ int zebra_tppr_plan_create(zebra_tppr_t *h, const int32_t *host_src, const int32
             if (e != cudaSuccess) { delete pl; return fail("pinned staging of %zu bytes: %s", bytes, cudaGetErrorString(e)); }
             h->plan_stage_cap = bytes + bytes / 8;
         }
-        fill_soa_sharded(h, h->plan_stage, pl->cap, host_src, host_dst, rows_per_edge == 3 ? host_neg : nullptr, host_ts, host_eidx, list);
-        e = cudaMalloc(&pl->dev, bytes);
+        ChainSet cs;
+        ChainBuild cb;
+        detect_chains<int32_t>(h, host_src, host_dst, n, cs);
+        fill_soa_sharded(h, h->plan_stage, pl->cap, host_src, host_dst, rows_per_edge == 3 ? host_neg : nullptr, host_ts, host_eidx, list,
+                         nullptr, &cs, &cb);
+        std::vector<zebra::ChainStep> all;
+        if (cs.n > 0 && cb.n_items > 0) {
+            pl->chain_n = cs.n;
+            all.reserve(cb.total());
+            pl->item_edge.assign(static_cast<size_t>(cb.n_items), 0);
+            for (int q = 0; q < cs.n; ++q) {
+                pl->chain_node[q] = cs.node[q];
+                pl->chain_off[q] = static_cast<int32_t>(all.size());
+                pl->chain_edges[q].reserve(cb.steps[q].size());
+                for (const zebra::ChainStep &st : cb.steps[q]) {
+                    pl->chain_edges[q].push_back(st.edge);
+                    pl->item_edge[static_cast<size_t>(st.cidx)] = st.edge;
+                    all.push_back(st);
+                }
+            }
+            pl->chain_off[cs.n] = static_cast<int32_t>(all.size());
+        }
+        pl->steps_bytes = all.size() * sizeof(zebra::ChainStep);
+        e = cudaMalloc(&pl->dev, bytes + std::max<size_t>(pl->steps_bytes, 16));
         if (e == cudaSuccess) e = cudaMemcpy(pl->dev, h->plan_stage, bytes, cudaMemcpyHostToDevice);
+        if (e == cudaSuccess && pl->steps_bytes) e = cudaMemcpy(pl->dev + bytes, all.data(), pl->steps_bytes, cudaMemcpyHostToDevice);
         if (e == cudaSuccess) e = cudaMalloc(&pl->dev_list, std::max<size_t>(list.size(), 1) * sizeof(int32_t));
         if (e == cudaSuccess) e = cudaMemcpy(pl->dev_list, list.data(), list.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
     } else {
@@ -1404,11 +1465,13 @@ static void epoch_prepare(zebra_epoch *ep, int64_t w, HostScratch *scratch)
         pr.failed = shard_work_list(h, ep->src + lo, ep->dst + lo, ng, ep->eidx + lo, m, ep->batch_size, pr.list, pr.batch_ofs) != 0;
         if (pr.failed) { pr.err = zebra_last_error(); pr.window = w; return; }
         pr.cap = (pr.list.size() + 8) & ~static_cast<size_t>(7);
-        fill_soa_sharded(h, stg.host, pr.cap, ep->src + lo, ep->dst + lo, ng, ep->ts + lo, ep->eidx + lo, pr.list, scratch);
+        fill_soa_sharded(h, stg.host, pr.cap, ep->src + lo, ep->dst + lo, ng, ep->ts + lo, ep->eidx + lo, pr.list, scratch,
+                         &ep->cs, &pr.cb);
         int32_t *dl = reinterpret_cast<int32_t *>(stg.host + pr.cap * kEdgeBytes);
         for (size_t q = 0; q < pr.list.size(); ++q) dl[q] = pr.list[q] + static_cast<int32_t>(lo);
-        pr.img_bytes = pr.cap * kEdgeBytes + pr.list.size() * sizeof(int32_t);
-        pr.cl = ChainLaunch();
+        // [compact records][work list][chain steps]
+        const size_t list_bytes = ((pr.list.size() * sizeof(int32_t)) + 15) & ~static_cast<size_t>(15);
+        pr.img_bytes = place_chain_steps(ep->cs, stg.host, stg.dev, pr.cap, pr.cb, pr.cl, list_bytes);
         pr.window = w;
         return;
     }
@@ -1493,7 +1556,7 @@ static int epoch_issue(zebra_epoch *ep)
         const size_t half_off = static_cast<size_t>(w & 1) * ob;
         const int32_t *dev_list = reinterpret_cast<const int32_t *>(stg.dev + cap * kEdgeBytes);
         if (launch_kernel(h, stg.dev, cap, 0, m, ep->n, lo, ep->rows_per_edge, (1 << h->n_tppr) - 1,
-                          reinterpret_cast<char *>(half_off), bo, seq0, 0, ep->st, dev_list, static_cast<int64_t>(pr.list.size()))) return 1;
+                          reinterpret_cast<char *>(half_off), bo, seq0, 0, ep->st, dev_list, static_cast<int64_t>(pr.list.size()), &cl)) return 1;
         CU(cudaEventRecord(sl.ev_kernel, ep->st));
         if (ep->rows_per_edge) {
             CU(cudaStreamWaitEvent(h->copy_stream, sl.ev_kernel, 0));

@@ -71,9 +71,10 @@ struct alignas(16) ChainStep {
     int32_t cidx;        // chain item index of the edge (mailbox slot = cidx - cidx_base)
     int32_t prev_self;   // previous writer of the chain node itself (used by the first step of a launch)
     double ts;
-    int64_t pad;
+    int64_t rec;         // index of the edge's staging record in the image (node-sharded plans hold compact records)
 };
-enum : uint32_t { kStepDst = 1u, kStepLoop = 2u, kStepPeerChain = 4u };
+enum : uint32_t { kStepDst = 1u, kStepLoop = 2u, kStepPeerChain = 4u,
+                  kStepPeerRemote = 8u };     // node-sharded: the partner lives on another rank (its vector arrives by NVLink push)
 struct ChainDesc { int32_t node, begin, end, pad; };   // steps [begin, end) of SpanParams::csteps
 
 // The norm of a node depends only on how many updates it has seen (norm <- norm*beta + beta,
@@ -130,6 +131,7 @@ struct SpanParams {
     unsigned long long *prof;   // [8] cycle sums per phase (ZEBRA_PROFILE builds)
     // node-sharded mode (tppr_shard_device.cuh): node v lives on rank v & (world-1), local row v >> world_log2
     int32_t world_log2, rank, mbox_parity;
+    int64_t rec_offset;                             // node-sharded: staging record of a chain step = ChainStep::rec - rec_offset
     int32_t shard_launch;                           // index of this sharded launch on the handle (same on every rank)
     const int32_t *shard_done;                      // own arena header: [r] = launches rank r has finished
     int32_t row_guard;                              // pipelined epoch: wait for the consumer rank before storing its rows
@@ -224,6 +226,13 @@ __device__ __forceinline__ void st_chunk(char *p, double d, int i, uint32_t tag)
 __device__ __forceinline__ double chunk_f64(const uint4 &c)
 {
     return __longlong_as_double(static_cast<long long>((static_cast<unsigned long long>(c.y) << 32) | c.x));
+}
+
+__device__ __forceinline__ int32_t ld_relaxed_sys_s32(const int32_t *p)
+{
+    int32_t v;
+    asm volatile("ld.relaxed.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
 }
 
 __device__ __forceinline__ int32_t ld_relaxed_s32(const int32_t *p)
@@ -832,13 +841,20 @@ __device__ __forceinline__ uint32_t load_step_word(const ChainStep *st, int lane
 // chain warp pushes), push the own OLD vector into the item's mailbox slot for the ticket warp that does
 // the rest of the edge, update, publish the new version to the table record.  The next partner's record
 // is loaded into registers before the update, so that its latency overlaps the update.
+// kShard (node-sharded kernel): records are addressed by local row (node >> log2 world); a partner owned by
+// another rank sends its old vector into this rank's mailbox slot of the item and receives ours in its own
+// (pushed straight from the chain warp's registers over NVLink, after the launch hand-shake with that rank).
+template <bool kShard>
 __device__ __noinline__ void run_chain(const SpanParams &p, WarpScratch &s, int q, int j, int lane, unsigned &stats)
 {
     const ChainDesc c = p.chains[q];
     if (c.begin >= c.end) return;
     const int k = p.k;
+    const int lg = kShard ? p.world_log2 : 0;
     char *table = p.tables[j];
-    char *recH = table + static_cast<size_t>(c.node) * p.stride;
+    char *recH = table + static_cast<size_t>(c.node >> lg) * p.stride;
+    unsigned peers_ok = 0;
+    char *const my_mbox = kShard ? p.mbox_peer[p.rank] + static_cast<size_t>(p.mbox_parity) * p.mbox_half_bytes : nullptr;
     int32_t *rcntH = p.rcnt[j] + c.node;
     const ChainStep *steps = p.csteps;
     uint32_t w0 = load_step_word(steps + c.begin, lane);
@@ -858,7 +874,7 @@ __device__ __noinline__ void run_chain(const SpanParams &p, WarpScratch &s, int 
     {
         const uint32_t fl = __shfl_sync(kFull, w0, 5);
         const int peer = static_cast<int>(__shfl_sync(kFull, w0, 1));
-        raw = load_raw(table + static_cast<size_t>((fl & (kStepLoop | kStepPeerChain)) ? c.node : peer) * p.stride, k, lane);
+        raw = load_raw(table + static_cast<size_t>(((fl & (kStepLoop | kStepPeerChain | kStepPeerRemote)) ? c.node : peer) >> lg) * p.stride, k, lane);
     }
     for (int x = c.begin; x < c.end; ++x) {
         ZP_DECL;
@@ -880,6 +896,29 @@ __device__ __noinline__ void run_chain(const SpanParams &p, WarpScratch &s, int 
         if (fl & kStepLoop) {
             B = vsel(true, H, H);
             push_vector<false>(my_slot, k, H, tag, lane);
+        } else if (kShard && (fl & kStepPeerRemote)) {
+            // the partner lives on another rank: our old vector goes to the helper here (rows) and over NVLink to
+            // the partner's owner; the partner's old vector arrives in this rank's mailbox slot of the item
+            push_vector<false>(my_slot, k, H, tag, lane);
+            const int partner = peer & ((1 << lg) - 1);
+            const size_t slot_off = (static_cast<size_t>(edge - p.tag_offset) * p.n_tppr + j) * p.stride;   // launch-local edge
+            if (!((peers_ok >> partner) & 1u)) {
+                Waiter wh;
+                while (ld_relaxed_sys_s32(p.shard_done + partner) < p.shard_launch - 1) {
+                    if (wh.expired(p.status, p.wait_ns, 8, tag, static_cast<uint32_t>(partner))) { alive = false; break; }
+                    __nanosleep(200);
+                }
+                peers_ok |= 1u << partner;
+            }
+            if (alive) {
+                push_vector<true>(p.mbox_peer[partner] + static_cast<size_t>(p.mbox_parity) * p.mbox_half_bytes + slot_off, k, H, tag, lane);
+                uint32_t cur;
+                Waiter wt;
+                while (!try_load<true>(my_mbox + slot_off, k, lane, false, tag, B, cur)) {
+                    if (wt.expired(p.status, p.wait_ns, 8, tag, static_cast<uint32_t>(peer))) { alive = false; break; }
+                    __nanosleep(40);
+                }
+            }
         } else if (fl & kStepPeerChain) {
             // both endpoints are chain nodes: each chain warp pushes first, then takes the other's push
             push_vector<false>(my_slot, k, H, tag, lane);
@@ -891,7 +930,7 @@ __device__ __noinline__ void run_chain(const SpanParams &p, WarpScratch &s, int 
                 __nanosleep(40);
             }
         } else {
-            const char *recP = table + static_cast<size_t>(peer) * p.stride;
+            const char *recP = table + static_cast<size_t>(peer >> lg) * p.stride;
             const uint32_t expect = p.seq0 + static_cast<uint32_t>(prev_peer);
             uint32_t cur;
             bool ok = check_raw(raw, lane, prev_peer < 0, expect, B, cur);
@@ -916,7 +955,7 @@ __device__ __noinline__ void run_chain(const SpanParams &p, WarpScratch &s, int 
         if (x + 1 < c.end) {
             const uint32_t nfl = __shfl_sync(kFull, w1, 5);
             const int npeer = static_cast<int>(__shfl_sync(kFull, w1, 1));
-            raw = load_raw(table + static_cast<size_t>((nfl & (kStepLoop | kStepPeerChain)) ? c.node : npeer) * p.stride, k, lane);
+            raw = load_raw(table + static_cast<size_t>(((nfl & (kStepLoop | kStepPeerChain | kStepPeerRemote)) ? c.node : npeer) >> lg) * p.stride, k, lane);
         }
         ZP_MARK_IF(q == 0, 6);
         VecR Hn;
@@ -966,7 +1005,7 @@ tppr_span_kernel(const __grid_constant__ SpanParams p)
         if ((p.inst_mask >> hj) & 1) {
             if ((threadIdx.x >> 5) == 0) {
                 if (lane == 0) atomicAdd(p.smflag + smid, 1);
-                run_chain(p, s, q, hj, lane, stats);
+                run_chain<false>(p, s, q, hj, lane, stats);
                 if (lane == 0) atomicSub(p.smflag + smid, 1);
             } else { hx = p.chains[q].begin + (threadIdx.x >> 5) - 1; hx_end = p.chains[q].end; }
         }

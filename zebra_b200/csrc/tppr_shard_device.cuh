@@ -35,13 +35,6 @@
 
 namespace zebra {
 
-__device__ __forceinline__ int32_t ld_relaxed_sys_s32(const int32_t *p)
-{
-    int32_t v;
-    asm volatile("ld.relaxed.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-
 // Arena header: int32 [0..kMaxRanks) launches each rank has FINISHED, [kMaxRanks..2 kMaxRanks) launches whose
 // rows each rank has COPIED out of its output region (pipelined epochs).
 struct ShardDoneParams { int32_t *hdr[kMaxRanks]; int32_t world, rank, value, slot; };
@@ -89,19 +82,45 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
     unsigned peers_ok = 0;                  // partners known to have left the mailbox half of this launch's parity
     char *const my_mbox = p.mbox_peer[me] + static_cast<size_t>(p.mbox_parity) * p.mbox_half_bytes;
 
-    for (;;) {
-        uint32_t tk = 0;
-        if (lane == 0) tk = atomicAdd(p.ticket, 1u) - p.ticket_base;
-        tk = __shfl_sync(kFull, tk, 0);
-        if (tk >= total) {
-            if (lane == 0 && stats) {
-                if (stats & 0xffffu) atomicAdd(p.status + 2, static_cast<int>(stats & 0xffffu));
-                if (stats >> 16) atomicAdd(p.status + 1, static_cast<int>(stats >> 16));
-            }
-            break;
+    // hub chains of the nodes THIS rank owns (tppr_device.cuh "hub chains"): the first n_chains * n_tppr blocks
+    // serve one (chain node, instance) each — warp 0 walks the chain, the others take the chain's edges in turn
+    int hx = 0, hx_end = 0, hj = 0;
+    if (p.n_chains > 0 && blockIdx.x < static_cast<unsigned>(p.n_chains * p.n_tppr)) {
+        const int q = blockIdx.x / p.n_tppr;
+        hj = blockIdx.x - q * p.n_tppr;
+        if ((p.inst_mask >> hj) & 1) {
+            if ((threadIdx.x >> 5) == 0) run_chain<true>(p, s, q, hj, lane, stats);
+            else { hx = p.chains[q].begin + (threadIdx.x >> 5) - 1; hx_end = p.chains[q].end; }
         }
-        const int64_t li = tk / static_cast<uint32_t>(p.n_tppr);    // 32-bit division: items < 2^32
-        const int j = tk - li * p.n_tppr;
+    }
+
+    for (;;) {
+        int64_t li;
+        int j;
+        bool from_ticket = false;
+        if (hx < hx_end) {
+            const ChainStep *st = p.csteps + hx;
+            hx += kWarpsPerBlock - 1;
+            const uint32_t fl = __ldg(&st->flags);
+            // an edge between two chain nodes of this rank is in both chains: the helpers of its src side take it
+            if ((fl & kStepPeerChain) && (fl & kStepDst)) continue;
+            li = __ldg(&st->rec) - p.rec_offset;
+            j = hj;
+        } else {
+            uint32_t tk = 0;
+            if (lane == 0) tk = atomicAdd(p.ticket, 1u) - p.ticket_base;
+            tk = __shfl_sync(kFull, tk, 0);
+            if (tk >= total) {
+                if (lane == 0 && stats) {
+                    if (stats & 0xffffu) atomicAdd(p.status + 2, static_cast<int>(stats & 0xffffu));
+                    if (stats >> 16) atomicAdd(p.status + 1, static_cast<int>(stats >> 16));
+                }
+                break;
+            }
+            li = tk / static_cast<uint32_t>(p.n_tppr);    // 32-bit division: items < 2^32
+            j = static_cast<int>(tk - li * p.n_tppr);
+            from_ticket = true;
+        }
         if (!((p.inst_mask >> j) & 1)) continue;
         // the staging records of a sharded plan are compact: entry li describes edge list[li].  The whole
         // record in one batch of independent loads, before any branch that depends on it.
@@ -113,6 +132,18 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
         const double t = p.ts[li];
         const int e = p.eidx[li];
         const uint32_t rwS = p.rthr_s[li], rwD_raw = p.rthr_d[li];
+        const int32_t ci = p.cidx[li];
+        if (from_ticket && (flags & (kFlagSrcChain | kFlagDstChain))) continue;   // a chain block's helpers take it
+        if (p.dbg_owner && lane == 0) {
+            // debug: every (list entry, instance) must be processed exactly once
+            const uint32_t me_id = 1u + blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5) + (from_ticket ? 0u : 0x40000000u);
+            const uint32_t old = atomicExch(p.dbg_owner + li * p.n_tppr + j, me_id);
+            if (old != 0) {
+                atomicExch(p.status, 1);
+                Waiter w;
+                w.log_wait(p.status, 99, tag_base + static_cast<uint32_t>(p.list[li] - p.i_offset), old, static_cast<int32_t>(me_id));
+            }
+        }
         const bool has_neg = p.rows_per_edge == 3;
         const int gN = has_neg ? gN_raw : sN;
         const bool loop = sN == dN;
@@ -129,6 +160,16 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
         const char *recG = table + static_cast<size_t>(gN >> lg) * p.stride;
         const uint32_t my_tag = tag_base + static_cast<uint32_t>(i);
 
+        // an OWNED endpoint that is a chain node: its old vector comes from the item's chain mailbox slot, its update
+        // and the push to a remote partner are the chain warp's business
+        const bool cS = oS && (flags & kFlagSrcChain) != 0, cD = !loop && oD && (flags & kFlagDstChain) != 0;
+        const char *srcS = recS, *srcD = recD;
+        uint32_t expS = p.seq0 + static_cast<uint32_t>(pS), expD = p.seq0 + static_cast<uint32_t>(pD);
+        bool anyS = pS < 0, anyD = pD < 0;
+        if (cS) { srcS = chain_slot(p, ci, j, 0); expS = my_tag; anyS = false; }
+        if (cD) { srcD = chain_slot(p, ci, j, 1); expD = my_tag; anyD = false; }
+        if (p.rows_per_edge == 0 && !oG && (!oS || cS) && (loop || !oD || cD)) continue;   // update-only: nothing left to do here
+
         const bool needSD = oS || oD;
         const bool cross = needSD && !(oS && oD);              // the other endpoint lives on another rank
         const size_t slot_off = (static_cast<size_t>(i) * p.n_tppr + j) * p.stride;
@@ -144,12 +185,16 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
         D = S; G = S;
         uint32_t curS = 0, curD = 0, curG = 0;
         bool okS = !needSD, okD = !needSD || loop, okG = !oG;
-        bool pushed = !cross, alive = true;
+        // the only owned endpoint is a chain node: nothing here needs the remote partner's vector (its row and its
+        // update belong to its owner, our update to the chain warp)
+        if (cross && cS) okD = true;
+        if (cross && cD) okS = true;
+        bool pushed = !cross || (oS ? cS : cD), alive = true;      // a chain warp pushes its node's vector itself
         Waiter wt;
         for (;;) {
-            if (!okS) okS = oS ? try_load<false>(recS, k, lane, pS < 0, p.seq0 + static_cast<uint32_t>(pS), S, curS)
+            if (!okS) okS = oS ? try_load<false>(srcS, k, lane, anyS, expS, S, curS)
                                : try_load<true>(mslot, k, lane, false, my_tag, S, curS);
-            if (!okD) okD = oD ? try_load<false>(recD, k, lane, pD < 0, p.seq0 + static_cast<uint32_t>(pD), D, curD)
+            if (!okD) okD = oD ? try_load<false>(srcD, k, lane, anyD, expD, D, curD)
                                : try_load<true>(mslot, k, lane, false, my_tag, D, curD);
             if (!okG) okG = try_load<false>(recG, k, lane, pG < 0, p.seq0 + static_cast<uint32_t>(pG), G, curG);
             if (!pushed && (oS ? okS : okD)) {      // our endpoint's OLD vector is here: send it before computing
@@ -166,17 +211,17 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
             if (okS && okD && pushed) break;
             // back off while the local producer is far away (same estimate as the single-GPU kernel)
             uint32_t dist = 0;
-            if (!okS && oS) {
+            if (!okS && oS && !cS) {
                 const uint32_t d = curS - tag_base, pe = static_cast<uint32_t>(pS - p.tag_offset);
                 dist = (d < static_cast<uint32_t>(p.n_chunk) && d <= pe) ? pe - d : pe + 1;
             }
-            if (!okD && oD) {
+            if (!okD && oD && !cD) {
                 const uint32_t d = curD - tag_base, pe = static_cast<uint32_t>(pD - p.tag_offset);
                 const uint32_t dd = (d < static_cast<uint32_t>(p.n_chunk) && d <= pe) ? pe - d : pe + 1;
                 dist = dd > dist ? dd : dist;
             }
             if (dist > kNear) __nanosleep(backoff_ns(dist));
-            else if ((!okS && !oS) || (!okD && !oD) || !pushed) __nanosleep(100);   // waiting for a peer's push, or for the peer to leave the mailbox half
+            else if ((!okS && (!oS || cS)) || (!okD && (!oD || cD)) || !pushed) __nanosleep(100);   // waiting for a peer's push, or for the peer to leave the mailbox half
             if (wt.expired(p.status, p.wait_ns, (!okS && !oS) || (!okD && !oD) ? 8 : 1, my_tag, 0)) { alive = false; break; }
         }
         if (!alive) continue;
@@ -192,6 +237,7 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
             for (int h = 0; h < (loop ? 1 : 2); ++h) {
                 const bool isD = (h == 0) ? df : !df;
                 if (!(isD ? oD : oS)) continue;
+                if (isD ? cD : cS) continue;            // a chain node's side is computed by its chain warp
                 const VecR A = vsel(isD, D, S), B = vsel(isD, S, D);
                 ok &= update_endpoint(p, s, A, B, isD ? sN : dN, e, t, j, isD ? recD : recS, my_tag,
                                       rcnt + (isD ? dN : sN), isD ? rwD : rwS, lane, stats);
