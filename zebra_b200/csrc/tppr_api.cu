@@ -182,6 +182,7 @@ struct zebra_tppr {
 struct ChainSet {
     int32_t n = 0;
     int32_t node[zebra::kMaxChains] = {};
+    bool owned[zebra::kMaxChains] = {};        // node-sharded: this rank owns the node (runs its chain warp); else it only helps
     std::vector<uint8_t> map;                  // [num_nodes] 0 = ordinary node, q + 1 = chain q; empty when n == 0
 };
 
@@ -196,7 +197,7 @@ struct ChainBuild {
 // Chain geometry of one kernel launch.
 struct ChainLaunch {
     int32_t n = 0;
-    int32_t node[zebra::kMaxChains], begin[zebra::kMaxChains], end[zebra::kMaxChains];
+    int32_t node[zebra::kMaxChains], begin[zebra::kMaxChains], end[zebra::kMaxChains], owned[zebra::kMaxChains];
     const zebra::ChainStep *dev_steps = nullptr;
     int32_t cidx_base = 0, n_items = 0;
 };
@@ -217,6 +218,7 @@ struct zebra_plan {
     // start inside the device image; per chain item the span index of its edge
     int32_t chain_n = 0;
     int32_t chain_node[zebra::kMaxChains] = {};
+    bool chain_owned[zebra::kMaxChains] = {};
     std::vector<int32_t> chain_edges[zebra::kMaxChains];
     int32_t chain_off[zebra::kMaxChains + 1] = {};
     std::vector<int32_t> item_edge;
@@ -321,17 +323,16 @@ void detect_chains(zebra_tppr *h, const NodeT *src, const NodeT *dst, int64_t n,
     // every (chain, instance) gets a block of its own, resident next to the ticket blocks
     const int room = std::max(0, (h->world > 1 ? h->shard_max_blocks : h->max_blocks) / 2 / std::max(1, h->n_tppr));
     const int keep = std::min<int>({static_cast<int>(found.size()), h->max_chains, zebra::kMaxChains, room});
-    // node-sharded: every rank picks the same nodes from the same replicated span and keeps the ones it owns
-    int kept = 0;
+    // node-sharded: every rank picks the same nodes from the same replicated span; the owner of a chain node runs
+    // its chain warp, the other ranks run helpers for the edges that join it to one of THEIR nodes
+    if (keep > 0) cs.map.assign(N, 0);
     for (int q = 0; q < keep; ++q) {
         const int32_t v = found[static_cast<size_t>(q)].second;
-        if (h->world > 1 && (v & (h->world - 1)) != h->rank) continue;
-        if (kept == 0) cs.map.assign(N, 0);
-        cs.node[kept] = v;
-        cs.map[static_cast<size_t>(v)] = static_cast<uint8_t>(kept + 1);
-        ++kept;
+        cs.node[q] = v;
+        cs.owned[q] = h->world == 1 || (v & (h->world - 1)) == h->rank;
+        cs.map[static_cast<size_t>(v)] = static_cast<uint8_t>(q + 1);
     }
-    cs.n = kept;
+    cs.n = keep;
 }
 
 // Fills one staging slot for m edges and derives their dependencies (one forward pass and a clean-up
@@ -594,8 +595,11 @@ void fill_soa_sharded(zebra_tppr *h, char *host, size_t cap, const int32_t *src,
         if (oa && wb) { da->pad = static_cast<uint32_t>(q) + 1; db->pad = static_cast<uint32_t>(q) + 1; }
         o_cidx[q] = -1;
         if (cmap) {
-            // chain nodes this rank owns: their side of the edge goes to the resident chain warp
-            const uint8_t ca = oa ? cmap[a] : 0, cbq = wb ? cmap[b] : 0;
+            // chain nodes this rank owns: their side of the edge goes to the resident chain warp.  A chain node of
+            // ANOTHER rank joined to one of this rank's nodes: the edge goes to this rank's helpers of that chain (a
+            // ticket warp would sit on it until the remote chain warp gets there, and with it the ticket front)
+            const uint8_t ga = cmap[a], gb = (b != a) ? cmap[b] : 0;
+            const uint8_t ca = (ga && oa) ? ga : 0, cbq = (gb && wb) ? gb : 0;
             if (ca | cbq) {
                 const int32_t ci = cb->n_items++;
                 o_cidx[q] = ci;
@@ -615,6 +619,12 @@ void fill_soa_sharded(zebra_tppr *h, char *host, size_t cap, const int32_t *src,
                                                                       (!a_here ? zebra::kStepPeerRemote : 0u),
                                                                   ci, p_d[q], ts[i], static_cast<int64_t>(q)});
                 }
+            } else if (ga && !oa && wb) {
+                flg[q] |= zebra::kFlagSrcChain | (static_cast<uint32_t>(ga - 1) << zebra::kFlagSrcChainShift);
+                cb->steps[ga - 1].push_back(zebra::ChainStep{i, b, static_cast<int32_t>(eidx[i]), -1, 0u, 0u, -1, -1, ts[i], static_cast<int64_t>(q)});
+            } else if (gb && !wb && (b & pm) != me && oa) {
+                flg[q] |= zebra::kFlagDstChain | (static_cast<uint32_t>(gb - 1) << zebra::kFlagDstChainShift);
+                cb->steps[gb - 1].push_back(zebra::ChainStep{i, a, static_cast<int32_t>(eidx[i]), -1, 0u, 0u, -1, -1, ts[i], static_cast<int64_t>(q)});
             }
         }
     }
@@ -729,7 +739,7 @@ int launch_kernel(zebra_tppr *h, const char *dev, size_t cap, int64_t lo, int64_
         }
         p.cprog = h->cprog;
         p.csteps = cl->dev_steps; p.cmbox = h->cmbox; p.cidx_base = cl->cidx_base; p.n_chains = cl->n;
-        for (int q = 0; q < cl->n; ++q) p.chains[q] = zebra::ChainDesc{cl->node[q], cl->begin[q], cl->end[q], 0};
+        for (int q = 0; q < cl->n; ++q) p.chains[q] = zebra::ChainDesc{cl->node[q], cl->begin[q], cl->end[q], cl->owned[q]};
         chain_warps = cl->n * h->n_tppr;
         h->chain_items += cl->n_items;
         for (int q = 0; q < cl->n; ++q) h->chain_steps += cl->end[q] - cl->begin[q];
@@ -805,12 +815,13 @@ size_t place_chain_steps(const ChainSet &cs, char *host, char *dev, size_t cap, 
 {
     size_t bytes = cap * kEdgeBytes + extra;          // `extra`: bytes between the arrays and the step records (sharded: the work list)
     cl.n = 0;
-    if (cs.n == 0 || cb.n_items == 0) return bytes;
+    if (cs.n == 0 || cb.total() == 0) return bytes;
     zebra::ChainStep *dst = reinterpret_cast<zebra::ChainStep *>(host + bytes);
     int32_t pos = 0;
     cl.n = cs.n;
     for (int q = 0; q < cs.n; ++q) {
         cl.node[q] = cs.node[q];
+        cl.owned[q] = cs.owned[q] ? 1 : 0;
         cl.begin[q] = pos;
         if (!cb.steps[q].empty()) memcpy(dst + pos, cb.steps[q].data(), cb.steps[q].size() * sizeof(zebra::ChainStep));
         pos += static_cast<int32_t>(cb.steps[q].size());
@@ -1207,17 +1218,18 @@ int zebra_tppr_plan_create(zebra_tppr_t *h, const int32_t *host_src, const int32
         fill_soa_sharded(h, h->plan_stage, pl->cap, host_src, host_dst, rows_per_edge == 3 ? host_neg : nullptr, host_ts, host_eidx, list,
                          nullptr, &cs, &cb);
         std::vector<zebra::ChainStep> all;
-        if (cs.n > 0 && cb.n_items > 0) {
+        if (cs.n > 0 && cb.total() > 0) {       // (helper steps of another rank's chain count too)
             pl->chain_n = cs.n;
             all.reserve(cb.total());
             pl->item_edge.assign(static_cast<size_t>(cb.n_items), 0);
             for (int q = 0; q < cs.n; ++q) {
                 pl->chain_node[q] = cs.node[q];
+                pl->chain_owned[q] = cs.owned[q];
                 pl->chain_off[q] = static_cast<int32_t>(all.size());
                 pl->chain_edges[q].reserve(cb.steps[q].size());
                 for (const zebra::ChainStep &st : cb.steps[q]) {
                     pl->chain_edges[q].push_back(st.edge);
-                    pl->item_edge[static_cast<size_t>(st.cidx)] = st.edge;
+                    if (st.cidx >= 0) pl->item_edge[static_cast<size_t>(st.cidx)] = st.edge;
                     all.push_back(st);
                 }
             }
@@ -1241,17 +1253,18 @@ int zebra_tppr_plan_create(zebra_tppr_t *h, const int32_t *host_src, const int32
             return 1;
         }
         std::vector<zebra::ChainStep> all;
-        if (cs.n > 0 && cb.n_items > 0) {
+        if (cs.n > 0 && cb.total() > 0) {       // (helper steps of another rank's chain count too)
             pl->chain_n = cs.n;
             all.reserve(cb.total());
             pl->item_edge.assign(static_cast<size_t>(cb.n_items), 0);
             for (int q = 0; q < cs.n; ++q) {
                 pl->chain_node[q] = cs.node[q];
+                pl->chain_owned[q] = cs.owned[q];
                 pl->chain_off[q] = static_cast<int32_t>(all.size());
                 pl->chain_edges[q].reserve(cb.steps[q].size());
                 for (const zebra::ChainStep &st : cb.steps[q]) {
                     pl->chain_edges[q].push_back(st.edge);
-                    pl->item_edge[static_cast<size_t>(st.cidx)] = st.edge;
+                    if (st.cidx >= 0) pl->item_edge[static_cast<size_t>(st.cidx)] = st.edge;
                     all.push_back(st);
                 }
             }
@@ -1309,7 +1322,27 @@ int zebra_debug_host_pass(int64_t num_nodes, int32_t world, int32_t rank, const 
         count = list.size();
         cap = (count + 8) & ~static_cast<size_t>(7);
         img.reset(new char[cap * kEdgeBytes]);
-        fill_soa_sharded(&h, img.get(), cap, host_src, host_dst, host_neg, host_ts, host_eidx, list);
+        ChainSet cs;
+        ChainBuild cb;
+        h.shard_max_blocks = 296;
+        detect_chains<int32_t>(&h, host_src, host_dst, n, cs);
+        fill_soa_sharded(&h, img.get(), cap, host_src, host_dst, host_neg, host_ts, host_eidx, list, nullptr, &cs, &cb);
+        {
+            // every list entry with a chain flag must be taken by exactly one helper step; no other entry by any
+            const uint32_t *fl = reinterpret_cast<const uint32_t *>(img.get()) + 9 * cap;
+            std::vector<int> taken(count, 0);
+            for (int q = 0; q < cs.n; ++q)
+                for (const zebra::ChainStep &st : cb.steps[q]) {
+                    if ((st.flags & zebra::kStepPeerChain) && (st.flags & zebra::kStepDst)) continue;
+                    if (st.rec < 0 || st.rec >= static_cast<int64_t>(count)) return fail("chain step names record %lld of %zu", (long long)st.rec, count);
+                    taken[static_cast<size_t>(st.rec)]++;
+                }
+            for (size_t q = 0; q < count; ++q) {
+                const bool flagged = (fl[q] & (zebra::kFlagSrcChain | zebra::kFlagDstChain)) != 0;
+                if (taken[q] != (flagged ? 1 : 0))
+                    return fail("list entry %zu (edge %d): chain flags %u but taken by %d helper steps", q, list[q], fl[q] & 12u, taken[q]);
+            }
+        }
     } else {
         count = static_cast<size_t>(n);
         cap = (count + 7) & ~static_cast<size_t>(7);
@@ -1425,6 +1458,7 @@ int zebra_tppr_plan_run(zebra_tppr_t *h, zebra_plan_t *pl, int64_t first_batch, 
             for (int q = 0; q < pl->chain_n; ++q) {
                 const std::vector<int32_t> &ce = pl->chain_edges[q];
                 cl.node[q] = pl->chain_node[q];
+                cl.owned[q] = pl->chain_owned[q] ? 1 : 0;
                 cl.begin[q] = pl->chain_off[q] + static_cast<int32_t>(std::lower_bound(ce.begin(), ce.end(), lo32) - ce.begin());
                 cl.end[q] = pl->chain_off[q] + static_cast<int32_t>(std::lower_bound(ce.begin(), ce.end(), hi32) - ce.begin());
             }

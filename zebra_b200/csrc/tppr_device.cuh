@@ -75,7 +75,7 @@ struct alignas(16) ChainStep {
 };
 enum : uint32_t { kStepDst = 1u, kStepLoop = 2u, kStepPeerChain = 4u,
                   kStepPeerRemote = 8u };     // node-sharded: the partner lives on another rank (its vector arrives by NVLink push)
-struct ChainDesc { int32_t node, begin, end, pad; };   // steps [begin, end) of SpanParams::csteps
+struct ChainDesc { int32_t node, begin, end, owned; };   // steps [begin, end) of SpanParams::csteps; owned: this GPU runs the chain warp
 
 // The norm of a node depends only on how many updates it has seen (norm <- norm*beta + beta,
 // utils/util.py:522,574), so the factors of its next update are tabulated per update count instead

@@ -84,13 +84,17 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
 
     // hub chains of the nodes THIS rank owns (tppr_device.cuh "hub chains"): the first n_chains * n_tppr blocks
     // serve one (chain node, instance) each — warp 0 walks the chain, the others take the chain's edges in turn
-    int hx = 0, hx_end = 0, hj = 0;
+    int hx = 0, hx_end = 0, hj = 0, hstride = kWarpsPerBlock - 1;
     if (p.n_chains > 0 && blockIdx.x < static_cast<unsigned>(p.n_chains * p.n_tppr)) {
         const int q = blockIdx.x / p.n_tppr;
         hj = blockIdx.x - q * p.n_tppr;
         if ((p.inst_mask >> hj) & 1) {
-            if ((threadIdx.x >> 5) == 0) run_chain<true>(p, s, q, hj, lane, stats);
-            else { hx = p.chains[q].begin + (threadIdx.x >> 5) - 1; hx_end = p.chains[q].end; }
+            // a chain node of another rank: no chain warp here, all eight warps help with the edges that join it to
+            // this rank's nodes (their pushes are what the remote chain warp waits for)
+            const bool owned = p.chains[q].owned != 0;
+            const int w = threadIdx.x >> 5;
+            if (owned && w == 0) run_chain<true>(p, s, q, hj, lane, stats);
+            else { hx = p.chains[q].begin + (owned ? w - 1 : w); hx_end = p.chains[q].end; hstride = owned ? kWarpsPerBlock - 1 : kWarpsPerBlock; }
         }
     }
 
@@ -100,7 +104,7 @@ tppr_span_shard_kernel(const __grid_constant__ SpanParams p)
         bool from_ticket = false;
         if (hx < hx_end) {
             const ChainStep *st = p.csteps + hx;
-            hx += kWarpsPerBlock - 1;
+            hx += hstride;
             const uint32_t fl = __ldg(&st->flags);
             // an edge between two chain nodes of this rank is in both chains: the helpers of its src side take it
             if ((fl & kStepPeerChain) && (fl & kStepDst)) continue;
