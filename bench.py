@@ -391,6 +391,7 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         res["ms"], res["e2e_s"] = float(t[0]), float(t[1])
         res["tie_prunes"] = f.counters()["tie_prunes"]
+        res["chain_steps"] = f.counters()["chain_steps"]
         plan.close()
         f.disconnect()
         barrier()
@@ -447,7 +448,8 @@ def run_sharded(args, torch, dist, world, rank, local, dev):
                    "exchange": xs,
                    "l2": f"per-GPU tables {len(ALPHAS) * ((weak['N'] + world - 1) // world) * weak['record_bytes'] / 1e6:.0f} MB + "
                          f"outputs exceed the 126 MB L2 (inputs larger than L2)",
-                   "tie_path_prunes_last_step_rank0": weak["tie_prunes"]},
+                   "tie_path_prunes_last_step_rank0": weak["tie_prunes"],
+                   "chain_and_helper_steps_last_step_rank0": weak["chain_steps"]},
         "e2e": {"value": E * args.steps / weak["e2e_s"], "unit": UNIT,
                 "h2d_bytes_per_step": weak["plan_bytes"], "d2h_bytes_per_step": len(ALPHAS) * 16 * 3 * E * K,
                 "step": f"ShardedFinder.epoch on every rank (host arrays in): per window of {window} batches the ownership-aware dependency "

@@ -153,12 +153,14 @@ def test_sharded_error_behaviour():
                                         None, None, None))
 
 
+@pytest.mark.parametrize("chains", ["0", "1"])
 @pytest.mark.parametrize("world,name,n_edges,bs,window,row_mode", [(2, "reddit", 9000, 200, 4, 1), (4, "superuser", 7000, 100, 8, 1),
                                                                    (2, "wikipedia", 5000, 200, 6, 0)])
-def test_sharded_pipelined_epoch_matches_oracle(world, name, n_edges, bs, window, row_mode):
+def test_sharded_pipelined_epoch_matches_oracle(world, name, n_edges, bs, window, row_mode, chains, monkeypatch):
     """zebra_tppr_epoch_* on node-sharded handles: windows staged by worker threads, rows copied out once every
     rank has finished the window, output halves re-used only after their consumer has drained them."""
     import torch
+    monkeypatch.setenv("ZEBRA_SHARD_CHAINS", chains)
     from zebra_b200.sharded import ShardedFinder
     st = synth.make_stream(name, n_edges=n_edges, seed=78)
     neg = synth.make_negatives(st, bs)
@@ -229,13 +231,14 @@ def test_sharded_pipelined_epoch_matches_oracle(world, name, n_edges, bs, window
 
 
 @pytest.mark.parametrize("world,seed,n_nodes,hot", [(2, 11, 60, 6), (4, 12, 500, 20), (2, 13, 30, 3)])
-def test_sharded_chain_warps_match_oracle(world, seed, n_nodes, hot):
+def test_sharded_chain_warps_match_oracle(world, seed, n_nodes, hot, monkeypatch):
     """Hub chains in the node-sharded kernel: the owner rank of a hot node walks its edges with a resident chain
     warp; partners on other ranks exchange vectors with it through the NVLink mailboxes.  Adversarial stream
     (most edges between hot nodes, self-loops, negatives on hot nodes) through plans and the pipelined epoch."""
     import torch
     from tests.test_gpu_chains import _stream
     from zebra_b200.sharded import ShardedFinder
+    monkeypatch.setenv("ZEBRA_SHARD_CHAINS", "1")          # off by default on sharded handles (DESIGN.md section 7)
     E, bs, k, window = 16_000, 200, 20, 16
     src, dst, neg, ts, eidx = _stream(seed, n_nodes, E, hot)
     N = n_nodes + 1

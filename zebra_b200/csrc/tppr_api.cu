@@ -167,6 +167,7 @@ struct zebra_tppr {
     std::vector<int32_t> chain_cnt;            // [num_nodes] scratch of the detection pass (zero between passes)
     int32_t *smflag = nullptr;                 // device [2 * kSmSlots]: chain warps running per SM, ticket warps standing aside
     int32_t tie_mode = 0;                      // 0 exact (numba's argsort), 1 stable (insertion order among equal scores)
+    bool shard_chains = false;                 // ZEBRA_SHARD_CHAINS=1: hub chains on node-sharded handles too
     bool sm_yield = true;                      // ZEBRA_SM_YIELD=0 switches the standing aside off
     uint32_t *dbg_owner = nullptr;             // debug (ZEBRA_DEBUG_ITEMS=1): who processed each item of the launch
     size_t dbg_cap = 0;
@@ -293,6 +294,10 @@ void detect_chains(zebra_tppr *h, const NodeT *src, const NodeT *dst, int64_t n,
 {
     cs.n = 0;
     if (!h->chains_enabled || n < kChainMinEdges || h->max_chains <= 0) return;
+    // node-sharded handles: chain warps (and helpers for other ranks' chains) are built and tested, but measured
+    // on 2 B200 they gain 0-7 % of `value` (a cross-shard reply edge costs two NVLink hops plus the partner's
+    // update whoever walks the chain) and cost 15 % of `e2e` (heavier host pass): off unless ZEBRA_SHARD_CHAINS=1
+    if (h->world > 1 && !h->shard_chains) return;
     const uint64_t N = static_cast<uint64_t>(h->num_nodes);
     if (h->chain_cnt.size() != N) h->chain_cnt.assign(N, 0);
     int32_t *cnt = h->chain_cnt.data();
@@ -997,6 +1002,7 @@ int zebra_tppr_create(zebra_tppr_t **out, int64_t num_nodes, int32_t k, int32_t 
         h->chains_enabled = h->max_chains > 0;
     }
     if (const char *e = getenv("ZEBRA_HOST_THREADS")) h->host_threads = std::max(0, atoi(e));
+    if (const char *e = getenv("ZEBRA_SHARD_CHAINS")) h->shard_chains = atoi(e) != 0;
     if (const char *e = getenv("ZEBRA_SM_YIELD")) h->sm_yield = atoi(e) != 0;
     if (const char *e = getenv("ZEBRA_DEBUG_ITEMS")) h->dbg_items = atoi(e) != 0;
     if (const char *e = getenv("ZEBRA_WAIT_TIMEOUT_MS")) h->wait_ns = static_cast<unsigned long long>(std::max(1, atoi(e))) * 1000000ull;
@@ -1325,6 +1331,7 @@ int zebra_debug_host_pass(int64_t num_nodes, int32_t world, int32_t rank, const 
         ChainSet cs;
         ChainBuild cb;
         h.shard_max_blocks = 296;
+        h.shard_chains = true;
         detect_chains<int32_t>(&h, host_src, host_dst, n, cs);
         fill_soa_sharded(&h, img.get(), cap, host_src, host_dst, host_neg, host_ts, host_eidx, list, nullptr, &cs, &cb);
         {
