@@ -1,6 +1,6 @@
 #!/bin/bash
 # One gpurun call: GPU parity tests, perf probe, bench (ours + reference arm), ncu launch list + full capture.
-# Usage (from the repo root on the GPU box): bash tools/gpu_check.sh [tests|probe|bench|ncu|kernels|lazy|e2e ...]
+# Usage (from the repo root on the GPU box): bash tools/gpu_check.sh [tests|probe|star|chain|stress|bench|configs|ncu|kernels|lazy|e2e|sanitize ...]
 set -u
 mkdir -p gpurun_out
 WHAT="${*:-tests probe bench ncu kernels lazy}"
@@ -45,8 +45,17 @@ sanitize)
 star)
   ZEBRA_TPPR_LIB=zebra_b200/lib/libzebra_tppr_prof.so timeout 600 python tools/perf_probe.py --star > gpurun_out/star_prof.log 2>&1; echo "star prof rc=$?"; cat gpurun_out/star_prof.log
   timeout 600 python tools/perf_probe.py --star > gpurun_out/star.log 2>&1; echo "star rc=$?"; cat gpurun_out/star.log ;;
+chain)
+  # per-phase cycles of the hottest chain (profile build) and plain timings on a Wiki-Talk-shaped prefix
+  ZEBRA_TPPR_LIB=zebra_b200/lib/libzebra_tppr_prof.so timeout 600 python tools/perf_chain.py > gpurun_out/chain_prof.log 2>&1; echo "chain prof rc=$?"; cat gpurun_out/chain_prof.log
+  timeout 600 python tools/perf_chain.py > gpurun_out/chain.log 2>&1; echo "chain rc=$?"; cat gpurun_out/chain.log ;;
+stress)
+  timeout 900 python tools/stress_chains.py 60 > gpurun_out/stress_chains.log 2>&1; echo "stress rc=$?"; tail -3 gpurun_out/stress_chains.log ;;
+configs)
+  for w in wikipedia reddit mooc superuser; do
+    timeout 600 python bench.py --workload $w > gpurun_out/bench_$w.json 2> gpurun_out/bench_$w.err; echo "bench $w rc=$?"; done ;;
 e2e)
   # the reference's train.py, reference arm against levels 1 and 2 (three configs would take ~6 GPU-minutes: one here)
-  timeout 900 python tools/e2e_train.py --ref baseline/_ref --name wikipedia --epochs 3 --levels ref 1 2 --out gpurun_out/e2e 2>&1 | tail -4 ;;
+  timeout 1500 python tools/e2e_train.py --ref baseline/_ref --name ${E2E_NAME:-wikipedia} --epochs 2 --levels ref 1 2 3 --out gpurun_out/e2e 2>&1 | tail -5 ;;
 esac
 done
