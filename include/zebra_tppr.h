@@ -277,6 +277,30 @@ int zebra_prune_topk(zebra_csr_t *csr, const int32_t *host_q_nodes, const double
                      void *dev_out, void *host_out, void *stream);
 int64_t zebra_prune_launches(const zebra_csr_t *csr);
 
+/* zebra_prune_topk_static: the pruning query for callers that cannot allocate.  It has NO counterpart in the
+ * reference; it was added (code under CUDA graph capture, tight serving
+ * loops and harnesses that forbid cudaMalloc).  Same kernel, same output layout and bits as zebra_prune_topk,
+ * but every buffer is the caller's: the adjacency (the four arrays of zebra_csr_create), the queries and the
+ * output (zebra_prune_out_bytes(nq,k) bytes) are DEVICE pointers on the current device, and the kernel's per-warp
+ * work area plus the staged queries live in one file-scope device array of ZEBRA_PRUNE_STATIC_BYTES that every
+ * GPU loading the library holds until exit.  The call allocates and frees nothing (no cudaMalloc / cudaFree /
+ * cudaMallocAsync / pinned memory), does not synchronise, and enqueues three kernels on `stream`.
+ * Limits (a clear error beyond them, nothing is launched): nq <= ZEBRA_PRUNE_STATIC_MAX_QUERIES per call, and
+ * width + width^2 + ... + width^depth states per query must fit the work area once (44 bytes per state in
+ * ZEBRA_PRUNE_STATIC_BYTES - 1 MiB: about 730,000 states; the usual width 10-20, depth 2 needs 5-19 KB per
+ * warp and runs 1,700-6,000 warps at once).
+ * Every call on a device SHARES the array and finds the previous call's contents in it; nothing in it has to
+ * start at zero, so nothing is cleared.  Calls that overlap on the GPU (two streams, two threads) race: order
+ * them on one stream or with events.
+ * Query nodes cannot be checked on the host: an id outside [0, num_nodes) yields a zero row with filled = -1
+ * (zebra_prune_topk rejects the call instead). */
+#define ZEBRA_PRUNE_STATIC_BYTES (32u << 20)
+#define ZEBRA_PRUNE_STATIC_MAX_QUERIES 65536
+int zebra_prune_topk_static(const int64_t *dev_indptr, const int32_t *dev_adj_node, const int32_t *dev_adj_eidx,
+                            const double *dev_adj_ts, int64_t num_nodes, const int32_t *dev_q_nodes,
+                            const double *dev_q_ts, int64_t nq, int32_t width, int32_t depth, double alpha,
+                            double beta, int32_t k, void *dev_out, void *stream);
+
 /* ---- neighbour gather: replaces the gather / concat / weight-normalisation half of
  *      GraphDiffusionEmbedding.compute_embedding_tppr_ensemble (modules/embedding_module.py:236-271)
  *      and TimeEncode.forward (model/time_encoding.py:23-28) -----------------------------------------

@@ -53,6 +53,7 @@ SIGNATURES = {
     "zebra_prune_out_bytes": (C.c_size_t, [_I64, _I32]),
     "zebra_prune_topk": (C.c_int, [_VP, _VP, _VP, _I64, _I32, _I32, _D, _D, _I32, _VP, _VP, _VP]),
     "zebra_prune_launches": (_I64, [_VP]),
+    "zebra_prune_topk_static": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _VP, _VP, _I64, _I32, _I32, _D, _D, _I32, _VP, _VP]),
     "zebra_gather_fwd": (C.c_int, [_VP, _I32, _I64, _I32, _VP, _I64, _I32, _VP, _I64, _I32, _VP, _VP, _I32, _VP, _VP, _VP, _VP, _VP]),
     "zebra_gather_bwd": (C.c_int, [_VP, _I32, _I64, _I32, _VP, _VP, _VP, _VP, _VP, _I64, _I32, _I32, _VP]),
     "zebra_gather_bwd_sorted": (C.c_int, [_I32, _I64, _I32, _VP, _VP, _VP, _VP, _VP, _VP, _I64, _I32, _I32, _VP]),

@@ -6,6 +6,7 @@
 
 #include <algorithm>
 #include <cstring>
+#include <mutex>
 
 using zebra::fail;
 
@@ -167,3 +168,129 @@ int zebra_prune_topk(zebra_csr_t *c, const int32_t *host_q_nodes, const double *
 int64_t zebra_prune_launches(const zebra_csr_t *c) { return c ? c->launches : 0; }
 
 }  // extern "C"
+
+// ---- zebra_prune_topk_static: the same query without any allocation ------------------------------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (CUDA graph capture, tight serving loops).  prune_topk_kernel's per-warp work area and the staged
+// queries live in ONE file-scope device array of ZEBRA_PRUNE_STATIC_BYTES that every GPU loading the library
+// holds until exit.  Every call on a device shares it: calls that overlap on the GPU race.  Nothing in it has to
+// start at zero (the kernel writes every state, dictionary slot and rank before it reads it, and the staging
+// area is rewritten for [0, nq) by every call), so nothing is cleared between calls.
+namespace zebra {
+
+constexpr size_t kStaticBytes = ZEBRA_PRUNE_STATIC_BYTES;
+constexpr size_t kStaticStageBytes = 1u << 20;                       // [0, 1 MiB): q_ts f64[max] | q_nodes i32[max]
+constexpr int64_t kStaticMaxQueries = ZEBRA_PRUNE_STATIC_MAX_QUERIES;
+constexpr size_t kStaticWorkBytes = kStaticBytes - kStaticStageBytes; // per-warp work areas
+static_assert(kStaticMaxQueries * 12 <= (int64_t)kStaticStageBytes, "staging area too small");
+
+static __device__ __align__(256) unsigned char g_prune_static[kStaticBytes];
+
+// Copies the caller's queries into the staging area; a node id outside [0, num_nodes) becomes a query that
+// finds no neighbour (node 0 at time -inf) instead of an out-of-bounds read of indptr.
+__global__ void prune_static_stage_kernel(const int32_t *q_nodes, const double *q_ts, int64_t nq, int64_t num_nodes,
+                                          double *s_ts, int32_t *s_nodes)
+{
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < nq;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int32_t v = q_nodes[i];
+        const bool ok = v >= 0 && v < num_nodes;
+        s_nodes[i] = ok ? v : 0;
+        s_ts[i] = ok ? q_ts[i] : -__longlong_as_double(0x7ff0000000000000ll);
+    }
+}
+
+// filled[i] = -1 for the queries the staging kernel neutralised
+__global__ void prune_static_mark_kernel(const int32_t *q_nodes, int64_t nq, int64_t num_nodes, int32_t *o_filled)
+{
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < nq;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int32_t v = q_nodes[i];
+        if (v < 0 || v >= num_nodes) o_filled[i] = -1;
+    }
+}
+
+constexpr int kStaticMaxDevices = 64;
+static std::mutex g_static_mu;
+static unsigned char *g_static_ptr[kStaticMaxDevices];      // device address of g_prune_static, per device
+static int g_static_sms[kStaticMaxDevices];
+
+}  // namespace zebra
+
+extern "C" int zebra_prune_topk_static(const int64_t *dev_indptr, const int32_t *dev_adj_node, const int32_t *dev_adj_eidx,
+                                       const double *dev_adj_ts, int64_t num_nodes, const int32_t *dev_q_nodes,
+                                       const double *dev_q_ts, int64_t nq, int32_t width, int32_t depth, double alpha,
+                                       double beta, int32_t k, void *dev_out, void *stream)
+{
+    using namespace zebra;
+    if (nq < 0) return fail("negative query count");
+    if (num_nodes <= 0) return fail("num_nodes must be positive");
+    if (k < 1 || k > 32) return fail("k=%d unsupported by the pruning kernel (1 <= k <= 32: one output slot per lane)", k);
+    if (width < 1 || depth < 1) return fail("width and depth must be positive");
+    if (nq == 0) return 0;
+    if (!dev_indptr || !dev_adj_node || !dev_adj_eidx || !dev_adj_ts || !dev_q_nodes || !dev_q_ts || !dev_out)
+        return fail("null argument");
+    if (nq > kStaticMaxQueries)
+        return fail("nq=%lld exceeds the %lld queries per call of the allocation-free entry point (split the batch or use "
+                    "zebra_prune_topk)", (long long)nq, (long long)kStaticMaxQueries);
+    int64_t t_max = 0, lvl = 1;
+    for (int d = 0; d < depth; ++d) {
+        lvl *= width;
+        t_max += lvl;
+        if (t_max > (1 << 22)) break;
+    }
+    const size_t per_warp = t_max > (1 << 22) ? kStaticWorkBytes + 1 : prune_scratch_bytes(t_max);
+    if (per_warp > kStaticWorkBytes)
+        return fail("width=%d depth=%d needs %zu bytes of work area per warp, more than the %zu-byte static work area of the "
+                    "allocation-free entry point (use zebra_prune_topk)", width, depth, per_warp, kStaticWorkBytes);
+    int dev = -1;
+    CU(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kStaticMaxDevices) return fail("device %d out of range", dev);
+    unsigned char *base = nullptr;
+    int sms = 0;
+    {   // once per device, with that device current: the array's NAME is a host-side stand-in, its device
+        // address comes from the runtime
+        std::lock_guard<std::mutex> lk(g_static_mu);
+        if (!g_static_ptr[dev]) {
+            void *ptr = nullptr;
+            CU(cudaGetSymbolAddress(&ptr, g_prune_static));
+            if (!ptr) return fail("cudaGetSymbolAddress returned a null address for the static work area");
+            int n = 0;
+            CU(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
+            g_static_sms[dev] = n;
+            g_static_ptr[dev] = static_cast<unsigned char *>(ptr);
+        }
+        base = g_static_ptr[dev];
+        sms = g_static_sms[dev];
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    double *s_ts = reinterpret_cast<double *>(base);
+    int32_t *s_nodes = reinterpret_cast<int32_t *>(s_ts + kStaticMaxQueries);
+    const unsigned aux_blocks = static_cast<unsigned>(std::min<int64_t>((nq + 255) / 256, sms));
+    prune_static_stage_kernel<<<aux_blocks, 256, 0, st>>>(dev_q_nodes, dev_q_ts, nq, num_nodes, s_ts, s_nodes);
+    CU(cudaGetLastError());
+    // as many warps as fit the work area, at most one per query and 64 per SM
+    int64_t warps = std::min<int64_t>(nq, static_cast<int64_t>(kStaticWorkBytes / per_warp));
+    warps = std::min<int64_t>(warps, static_cast<int64_t>(sms) * 64);
+    const int wpb = warps >= 8 ? 8 : static_cast<int>(warps);
+    const int64_t blocks = warps / wpb;
+    PruneParams p;
+    memset(&p, 0, sizeof p);
+    p.indptr = dev_indptr; p.adj_node = dev_adj_node; p.adj_eidx = dev_adj_eidx; p.adj_ts = dev_adj_ts;
+    p.q_ts = s_ts; p.q_nodes = s_nodes;
+    p.nq = nq; p.num_nodes = num_nodes;
+    p.width = width; p.depth = depth; p.k = k; p.t_max = static_cast<int32_t>(t_max);
+    p.alpha = alpha; p.beta = beta;
+    const size_t plane = static_cast<size_t>(nq) * k;
+    p.o_node = reinterpret_cast<int32_t *>(dev_out);
+    p.o_eidx = p.o_node + plane;
+    p.o_dt = reinterpret_cast<float *>(p.o_eidx + plane);
+    p.o_w = p.o_dt + plane;
+    p.o_filled = reinterpret_cast<int32_t *>(p.o_w + plane);
+    p.scratch = reinterpret_cast<char *>(base + kStaticStageBytes); p.scratch_per_warp = per_warp;
+    prune_topk_kernel<<<static_cast<unsigned>(blocks), wpb * 32, 0, st>>>(p);
+    CU(cudaGetLastError());
+    prune_static_mark_kernel<<<aux_blocks, 256, 0, st>>>(dev_q_nodes, nq, num_nodes, p.o_filled);
+    CU(cudaGetLastError());
+    return 0;
+}
