@@ -613,7 +613,7 @@ def run_ours(args):
         traffic, traffic_src = (args.traffic, "--traffic") if args.traffic is not None else ncu_traffic()
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong" if split else "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_text(st),
                        "edges_per_gpu": E,
@@ -629,11 +629,12 @@ def run_ours(args):
                     "step": f"all {plan.n_batches} batches through tppr_finder.stream_epoch (host numpy in, host numpy out per "
                             f"batch; windows of {args.e2e_window} batches pipelined: host dependency pass, H2D, kernel, D2H)",
                     "launches_per_step": launches_e2e,
-                    "per_call_drop_in": {"value": world * call_edges / call_s, "unit": UNIT,
+                    "per_call_drop_in": {"value": (1 if split else world) * call_edges / call_s, "unit": UNIT,
                                          "what": f"first {nb_call} batches, one synchronous streaming_topk call per batch"}},
             "gpu_launches": launches,
             "clocks": clocks,
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak * (world if split else 1), "unit": "GB/s",
+                         "frac": achieved / (peak * (world if split else 1)),
                          "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "kernel": "tppr_span_kernel",
                          "bytes_per_edge": bytes_per_edge(), "algorithmic_bytes_per_launch": alg_per_launch,
                          "launch_ms": per_launch_ms,
@@ -643,9 +644,10 @@ def run_ours(args):
                                                    "step of its dependency chain (every update needs the previous one)"}},
         }
         if stable_ms is not None:
-            line["tie_modes"] = {"exact": {"value": value / world, "ms_per_step": ms / args.steps},
+            line["tie_modes"] = {"exact": {"value": value / (1 if split else world), "ms_per_step": ms / args.steps},
                                  "stable": {"value": E / (stable_ms * 1e-3), "ms_per_step": stable_ms,
-                                            "what": "equal scores keep insertion order (oracle tie_mode 1, tests/test_gpu_ties.py)"}}
+                                            "what": "equal scores keep insertion order (oracle tie_mode 1, tests/test_gpu_ties.py)"
+                                                    + ("; rank 0's instance only" if split else "")}}
         if world == 1 and not args.no_flat:
             # the same kernel on a hub-free stream of the same size class (uniform endpoints): no long
             # dependency chain, i.e. the kernel's throughput regime, where HBM is the relevant roofline

@@ -1,0 +1,138 @@
+"""Batch assembly of a whole pass before its loop (reference: train.py:196-203,
+evaluation/evaluation.py:19-33, utils/util.py:69-86, utils/data_processing.py:80-93).
+
+The reference slices every batch out of the split on the host, draws its negatives, and hands the five arrays to
+the model, one batch at a time; the T-PPR query of the batch then runs synchronously inside the model call.  For
+the validation / test passes everything about those batches is fixed before the loop starts: the split is static
+and the sampler is seeded and reset at the top of the pass (evaluation.py:9-10).  `PassSchedule` therefore
+
+* draws the negatives of every batch up front — with the sampler's own `sample(size)` calls in the loop's order,
+  so the numbers ARE the reference's (numpy's MT19937 stream; nothing is re-implemented);
+* lays the pass out as the five flat arrays the loop slices (`batch(b)` returns the same views the reference's
+  loop builds), and keeps a device-resident copy of them (`device_arrays()`): one H2D per pass;
+* announces the pass to the streaming finder (`tppr_finder.schedule_pass`): the span is uploaded once, streamed
+  `window` batches per launch ahead of the model, and each of the model's per-batch queries is answered from rows
+  that are already in HBM.  A query that does not match the announcement falls back to the per-call path after a
+  roll-back (finder.py), so announcing never changes a result.
+
+`RandEdgeSampler` mirrors utils/util.py:69-86 (same constructor, same draws) for callers that do not import the
+reference; `read_edge_csv` reads the `ml_{name}.csv` edge list (utils/data_processing.py:81-91).
+The training loop's batches depend on an unseeded global numpy stream (train.py:203) and are not announced.
+"""
+from __future__ import annotations
+
+import math
+
+import numpy as np
+
+
+class RandEdgeSampler:
+    """utils/util.py:69-86: negatives drawn uniformly from the distinct sources / destinations."""
+
+    def __init__(self, src_list, dst_list, seed=None):
+        self.seed = None
+        self.src_list = np.unique(src_list)
+        self.dst_list = np.unique(dst_list)
+        if seed is not None:
+            self.seed = seed
+            self.random_state = np.random.RandomState(self.seed)
+
+    def sample(self, size):
+        if self.seed is None:
+            src_index = np.random.randint(0, len(self.src_list), size)
+            dst_index = np.random.randint(0, len(self.dst_list), size)
+        else:
+            src_index = self.random_state.randint(0, len(self.src_list), size)
+            dst_index = self.random_state.randint(0, len(self.dst_list), size)
+        return self.src_list[src_index], self.dst_list[dst_index]
+
+    def reset_random_state(self):
+        self.random_state = np.random.RandomState(self.seed)
+
+
+def read_edge_csv(path):
+    """The edge list of `ml_{name}.csv` as the reference reads it (utils/data_processing.py:81-91): columns u, i,
+    ts, label, idx -> (sources, destinations, timestamps, edge_idxs, labels), in file (chronological) order."""
+    import pandas as pd
+    df = pd.read_csv(path)
+    return df.u.values, df.i.values, df.ts.values, df.idx.values, df.label.values
+
+
+class PassSchedule:
+    """All batches of one pass over `data` (an object with sources, destinations, timestamps, edge_idxs — the
+    reference's Data), assembled before the loop.  `sampler` is the pass's negative sampler (already reset); its
+    `sample(size)` is called once per batch, in batch order, exactly as the reference's loop does."""
+
+    def __init__(self, data, sampler, batch_size):
+        self.batch_size = int(batch_size)
+        self.sources = np.asarray(data.sources)
+        self.destinations = np.asarray(data.destinations)
+        self.timestamps = np.asarray(data.timestamps)
+        self.edge_idxs = np.asarray(data.edge_idxs)
+        self.n = len(self.sources)
+        self.n_batches = math.ceil(self.n / self.batch_size) if self.n else 0
+        negs = []
+        for b in range(self.n_batches):
+            lo, hi = self.bounds(b)
+            _, neg = sampler.sample(hi - lo)            # evaluation.py:27, train.py:203
+            negs.append(np.asarray(neg))
+        self.negatives = np.concatenate(negs) if negs else np.zeros(0, self.destinations.dtype)
+        self._finder = None
+        self._announced = self._last = None
+        self._dev = None
+
+    def bounds(self, b):
+        lo = b * self.batch_size
+        return lo, min(self.n, lo + self.batch_size)
+
+    def batch(self, b):
+        """(sources, destinations, negatives, timestamps, edge_idxs) of batch b: what the reference's loop hands to
+        `compute_edge_probabilities` (train.py:199-203, evaluation.py:22-30)."""
+        lo, hi = self.bounds(b)
+        return (self.sources[lo:hi], self.destinations[lo:hi], self.negatives[lo:hi], self.timestamps[lo:hi],
+                self.edge_idxs[lo:hi])
+
+    def device_arrays(self, device=None):
+        """The pass resident on the device: dict of CUDA tensors (sources, destinations, negatives int64;
+        timestamps float64; edge_idxs int64), batch b = rows [b*bs, (b+1)*bs).  One H2D per array per pass."""
+        import torch
+        if self._dev is None:
+            dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+            self._dev = {
+                "sources": torch.from_numpy(np.ascontiguousarray(self.sources, dtype=np.int64)).to(dev),
+                "destinations": torch.from_numpy(np.ascontiguousarray(self.destinations, dtype=np.int64)).to(dev),
+                "negatives": torch.from_numpy(np.ascontiguousarray(self.negatives, dtype=np.int64)).to(dev),
+                "timestamps": torch.from_numpy(np.ascontiguousarray(self.timestamps, dtype=np.float64)).to(dev),
+                "edge_idxs": torch.from_numpy(np.ascontiguousarray(self.edge_idxs, dtype=np.int64)).to(dev),
+            }
+        return self._dev
+
+    # ---- the streaming finder runs ahead of the loop ----
+    def announce(self, model_or_finder, window=64):
+        """Announce the pass to the streaming finder of `model_or_finder` (a zebra_b200 tppr_finder, or a model whose
+        embedding module holds one with tppr_strategy 'streaming').  Returns True if it was announced."""
+        from .finder import tppr_finder
+        f = model_or_finder
+        if not isinstance(f, tppr_finder):
+            em = getattr(model_or_finder, "embedding_module", None)
+            if getattr(em, "tppr_strategy", None) != "streaming":
+                return False
+            f = getattr(em, "tppr_finder", None)
+        if not isinstance(f, tppr_finder) or not self.n_batches:
+            return False
+        self._finder = f
+        self._announced = f.schedule_pass(self.sources, self.destinations, self.negatives, self.timestamps,
+                                          self.edge_idxs, self.batch_size, window)
+        return True
+
+    def stats(self):
+        a = self._announced or self._last
+        return None if a is None else {"batches": a.n_batches, "served": a.hits, "launches": a.launches,
+                                       "rolled_back": a.rolled_back}
+
+    def close(self):
+        """End of the pass (normal or not): anything still announced is settled."""
+        a, self._announced = self._announced, None
+        self._last = a or self._last
+        if a is not None and self._finder is not None and self._finder._sched is a:
+            a.abandon()

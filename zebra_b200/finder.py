@@ -63,6 +63,7 @@ class tppr_finder:  # noqa: N801  (name kept from the reference)
         self._record_bytes = self._L.zebra_tppr_record_bytes(h)
         self._host_out = None
         self._tables = None
+        self._sched = None              # an announced pass (schedule_pass), see _ScheduledPass
         self.reset_val_tppr()
         self.reset_tppr()
 
@@ -78,6 +79,7 @@ class tppr_finder:  # noqa: N801  (name kept from the reference)
         return [t.clone() for t in tables] if self.strict_snapshots else list(tables)
 
     def reset_tppr(self):
+        self._settle()
         self._tables = self._new_tables()
         self._bind()
 
@@ -85,13 +87,16 @@ class tppr_finder:  # noqa: N801  (name kept from the reference)
         self._val_tables = self._new_tables()
 
     def backup_tppr(self):
+        self._settle()
         return self._snapshot(self._tables)
 
     def restore_tppr(self, backup):
+        self._settle()
         self._tables = list(backup)
         self._bind()
 
     def restore_val_tppr(self):
+        self._settle()
         self._tables = self._snapshot(self._val_tables)
         self._bind()
 
@@ -109,6 +114,17 @@ class tppr_finder:  # noqa: N801  (name kept from the reference)
             raise ValueError("source_nodes/timestamps do not match edge_idxs")
         nbytes = self._L.zebra_tppr_out_bytes(self._h, n, rows_per_edge)
         host = None
+        if self._sched is not None:
+            # an announced pass: the rows of this batch were computed with its window, ahead of the call
+            hit = self._sched.take(nodes, ts, eidx, rows_per_edge, inst)
+            if hit is not None:
+                if to_host and nbytes:
+                    if self._host_out is None or self._host_out.numel() < nbytes:
+                        self._host_out = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+                        self._dev_scratch = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+                    host = self._host_out
+                    host[:nbytes].copy_(hit[:nbytes])          # synchronous D2H into the pinned buffer
+                return hit, host, rows, nbytes
         if to_host and nbytes:
             # numpy-returning calls: the device copy of the rows is scratch, kept across calls (no allocation per batch)
             if self._host_out is None or self._host_out.numel() < nbytes:
@@ -168,10 +184,16 @@ class tppr_finder:  # noqa: N801  (name kept from the reference)
         dst = np.ascontiguousarray(targets, dtype=np.int64)
         ts = np.ascontiguousarray(timestamps, dtype=np.float64)
         eidx = np.ascontiguousarray(edge_idxs, dtype=np.int64)
+        self._settle()
+        self._update_only(src, dst, ts, eidx)
+        self._val_tables = self._snapshot(self._tables)
+
+    def _update_only(self, src, dst, ts, eidx):
+        src = np.ascontiguousarray(src, dtype=np.int64)
+        dst = np.ascontiguousarray(dst, dtype=np.int64)
         with torch.cuda.device(self.device):
             check(self._L.zebra_tppr_update_only(self._h, _ptr(src), _ptr(dst), _ptr(ts), _ptr(eidx), len(src),
                                                  self._stream_ptr()))
-        self._val_tables = self._snapshot(self._tables)
 
     # ---- pipelined epochs (include/zebra_tppr.h "pipelined epochs") ----
     def stream_epoch(self, src, dst, neg, timestamps, edge_idxs, batch_size, rows_per_edge=3, window=128,
@@ -197,6 +219,7 @@ class tppr_finder:  # noqa: N801  (name kept from the reference)
             raise ValueError("src/dst/neg/timestamps/edge_idxs do not match")
         if n == 0:
             return
+        self._settle()
         L = self._L
         ep = C.c_void_p()
         with torch.cuda.device(self.device):
@@ -239,6 +262,26 @@ class tppr_finder:  # noqa: N801  (name kept from the reference)
                                [tf[j, 2] for j in range(T)], [tf[j, 3] for j in range(T)])
         finally:
             L.zebra_tppr_epoch_end(ep)
+
+    # ---- announced passes (the batches of a pass are known before its loop) ----
+    def schedule_pass(self, src, dst, neg, timestamps, edge_idxs, batch_size, window=64):
+        """Announce the batches the next `streaming_topk*` calls will bring (a validation or test pass:
+        train.py:196-203 slices them one by one, evaluation/evaluation.py:19-33 draws their seeded negatives one by
+        one — both are known before the loop starts).  The span goes to the device once (a StreamPlan) and is
+        streamed `window` batches per launch AHEAD of the calls; a call whose arguments equal the next announced
+        batch returns the rows already computed for it (same bytes, same final state as per-call streaming).
+        A call that brings anything else, or any state call (reset / backup / restore / ...), ends the
+        announcement first: the tables are put back to the start of the window in flight, the batches consumed so
+        far are replayed, and the call proceeds as usual — announcing a pass never changes a result."""
+        self._settle()
+        sp = _ScheduledPass(self, src, dst, neg, timestamps, edge_idxs, batch_size, window)
+        if sp.n_batches:
+            self._sched = sp
+        return sp
+
+    def _settle(self):
+        if self._sched is not None:
+            self._sched.abandon()
 
     # ---- resident spans (include/zebra_tppr.h "plans") ----
     def make_plan(self, src, dst, neg, timestamps, edge_idxs, batch_size, rows_per_edge=3):
@@ -352,3 +395,93 @@ class StreamPlan:
             self.close()
         except Exception:
             pass
+
+
+class _ScheduledPass:
+    """State of `tppr_finder.schedule_pass`: the plan of the pass, the window computed ahead, the copy of the
+    tables taken at the start of that window (what a mismatching call rolls back to)."""
+
+    def __init__(self, finder, src, dst, neg, timestamps, edge_idxs, batch_size, window):
+        self.f = finder
+        self.bs = int(batch_size)
+        self.window = max(1, int(window))
+        self.src = np.ascontiguousarray(src, dtype=np.int32)
+        self.dst = np.ascontiguousarray(dst, dtype=np.int32)
+        self.neg = np.ascontiguousarray(neg, dtype=np.int32)
+        self.ts = np.ascontiguousarray(timestamps, dtype=np.float64)
+        self.eidx = np.ascontiguousarray(edge_idxs, dtype=np.int64)
+        self.n = len(self.src)
+        self.n_batches = (self.n + self.bs - 1) // self.bs if self.n else 0
+        self.next = 0                   # next batch a call is expected to bring
+        self.w0 = self.w1 = 0           # batches [w0, w1) have been streamed
+        self.snap = None                # the tables before batch w0
+        self.hits = self.launches = 0
+        self.rolled_back = False
+        self.plan = self.out = None
+        if self.n_batches:
+            self.plan = finder.make_plan(self.src, self.dst, self.neg, self.ts, self.eidx, self.bs, 3)
+            self.out = self.plan.alloc_out(min(self.window, self.n_batches))
+
+    def _matches(self, b, nodes, ts, eidx):
+        lo = b * self.bs
+        n = min(self.bs, self.n - lo)
+        hi = lo + n
+        return (len(eidx) == n and len(nodes) == 3 * n and np.array_equal(eidx, self.eidx[lo:hi])
+                and np.array_equal(nodes[:n], self.src[lo:hi]) and np.array_equal(nodes[n:2 * n], self.dst[lo:hi])
+                and np.array_equal(nodes[2 * n:], self.neg[lo:hi]) and np.array_equal(ts[:n], self.ts[lo:hi]))
+
+    def take(self, nodes, ts, eidx, rows_per_edge, inst):
+        """The device rows of the call if it brings the next announced batch, else None (after settling)."""
+        b = self.next
+        if rows_per_edge != 3 or inst != -1 or b >= self.n_batches or not self._matches(b, nodes, ts, eidx):
+            self.abandon()
+            return None
+        f = self.f
+        if b >= self.w1:
+            cnt = min(self.window, self.n_batches - b)
+            self.snap = [t.clone() for t in f._tables]
+            self.plan.run(b, cnt, cnt, out=self.out, out_slots=cnt)
+            self.w0, self.w1 = b, b + cnt
+            self.launches += 1
+        slot = b - self.w0
+        nb = self.plan.batch_edges(b)
+        nbytes = f._L.zebra_tppr_out_bytes(f._h, nb, 3)
+        rows = self.out[slot * self.plan.slot_bytes: slot * self.plan.slot_bytes + max(nbytes, 1)]
+        self.next = b + 1
+        self.hits += 1
+        if self.next == self.n_batches:
+            self._finish()
+        return rows
+
+    def abandon(self):
+        """End the announcement: leave the tables as per-call streaming of the consumed batches would."""
+        f = self.f
+        if f._sched is self:
+            f._sched = None
+        if self.plan is None:
+            return
+        redo = None
+        if self.next < self.w1:
+            # the window ran ahead of the calls: back to its start, then the consumed part of it again (as one
+            # update-only span: a plan's batches run strictly in order, and rows are not needed a second time)
+            for t, s0 in zip(f._tables, self.snap):
+                t.copy_(s0)
+            if self.next > self.w0:
+                redo = (self.w0 * self.bs, self.next * self.bs)
+            self.rolled_back = True
+        self._finish()
+        if redo is not None:
+            lo, hi = redo
+            f._update_only(self.src[lo:hi], self.dst[lo:hi], self.ts[lo:hi], self.eidx[lo:hi])
+
+    def _finish(self):
+        f = self.f
+        if f._sched is self:
+            f._sched = None
+        self.snap = None
+        if self.plan is not None:
+            torch.cuda.current_stream(f.device).synchronize()    # the plan's device arrays are freed below
+            self.plan.close()
+            self.plan = None
+
+    cancel = abandon

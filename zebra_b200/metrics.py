@@ -16,8 +16,13 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import os
 
 import numpy as np
+
+PASS_SCHEDULE = os.environ.get("ZEBRA_PASS_SCHEDULE", "1") != "0"    # announce validation / test passes to the finder
+PASS_WINDOW = int(os.environ.get("ZEBRA_PASS_WINDOW", "64"))          # batches streamed per launch, ahead of the model
+LAST_PASS = None                                                      # PassSchedule.stats() of the last pass (diagnostics)
 
 
 def edge_metrics(pos, neg, batch_size=None):
@@ -44,19 +49,27 @@ def eval_edge_prediction(model, negative_edge_sampler, data, n_neighbors, batch_
     """Drop-in for evaluation/evaluation.py:7-47: identical batches, identical seeded negatives, identical
     model calls; the probabilities stay on the device and are scored there."""
     import torch
+    from .batches import PassSchedule
     assert negative_edge_sampler.seed is not None
     negative_edge_sampler.reset_random_state()
     rows = []
     with torch.no_grad():
         model = model.eval()
-        n_inst = data.n_interactions
-        for batch_idx in range(math.ceil(n_inst / batch_size)):
-            s, e = batch_idx * batch_size, min(n_inst, (batch_idx + 1) * batch_size)
-            size = e - s
-            _, negative_samples = negative_edge_sampler.sample(size)
-            pos_prob, neg_prob = model.compute_edge_probabilities(data.sources[s:e], data.destinations[s:e], negative_samples,
-                                                                  data.timestamps[s:e], data.edge_idxs[s:e], n_neighbors, train=False)
-            rows.append(edge_metrics(pos_prob, neg_prob))
+        # the whole pass assembled before the loop (row f2): same slices, same seeded draws in the same order;
+        # the streaming finder is told what is coming and computes the T-PPR rows a window of batches ahead
+        sched = PassSchedule(data, negative_edge_sampler, batch_size)
+        if PASS_SCHEDULE:
+            sched.announce(model, PASS_WINDOW)
+        try:
+            for batch_idx in range(sched.n_batches):
+                src, dst, negative_samples, ts, eidx = sched.batch(batch_idx)
+                pos_prob, neg_prob = model.compute_edge_probabilities(src, dst, negative_samples, ts, eidx, n_neighbors,
+                                                                      train=False)
+                rows.append(edge_metrics(pos_prob, neg_prob))
+        finally:
+            sched.close()
+            global LAST_PASS
+            LAST_PASS = sched.stats()
     if not rows:
         return float("nan"), float("nan"), float("nan")
     m = torch.cat(rows).cpu().numpy()            # the one device-to-host copy of the pass
