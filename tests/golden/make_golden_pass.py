@@ -38,6 +38,18 @@ def main():
                 _, neg = sampler.sample(e - s)
                 negs.append(neg)
             out[f"neg_seed{seed}_bs{bs}"] = np.concatenate(negs)
+    # the training loop's sampler: unseeded, numpy's global stream (train.py:88,140,203), two epochs over the
+    # "training" slice [0, lo) with a ragged last batch, then one more draw that pins the stream position
+    train = ref.RandEdgeSampler(st.src[:lo], st.dst[:lo])
+    np.random.seed(0)
+    for ep in range(2):
+        negs = []
+        for b in range(math.ceil(lo / 200)):
+            s, e = b * 200, min(lo, (b + 1) * 200)
+            _, neg = train.sample(e - s)
+            negs.append(neg)
+        out[f"train_neg_epoch{ep}"] = np.concatenate(negs)
+    out["train_after"] = np.random.randint(0, 1 << 30, 4)
     np.savez_compressed(os.path.join(HERE, "pass_schedule.npz"), **out)
     print("wrote pass_schedule.npz", {k: getattr(v, "shape", v) for k, v in out.items()})
 

@@ -48,3 +48,46 @@ def test_read_edge_csv(tmp_path):
     u, i, ts, idx, lab = read_edge_csv(str(p))
     assert u.tolist() == [1, 2, 1] and i.tolist() == [5, 6, 6] and ts.tolist() == [0.0, 3.5, 9.25]
     assert idx.tolist() == [1, 2, 3] and lab.tolist() == [0, 1, 0]
+
+
+def _train(g):
+    lo = int(g["lo"])
+    return types.SimpleNamespace(sources=g["src"][:lo], destinations=g["dst"][:lo], timestamps=g["ts"][:lo],
+                                 edge_idxs=g["eidx"][:lo])
+
+
+def test_train_lookahead_hands_out_the_reference_draws_and_leaves_the_stream_where_it_was():
+    from zebra_b200.batches import TrainLookahead
+    g = H.load("pass_schedule")
+    data = _train(g)
+    n = len(data.sources)
+    sampler = RandEdgeSampler(data.sources, data.destinations)
+    look = TrainLookahead(data)
+    np.random.seed(0)
+    for ep in range(2):
+        negs = []
+        for b in range(-(-n // 200)):
+            size = min(n, (b + 1) * 200) - b * 200
+            _, neg = look.take(sampler, size, sampler.sample)
+            negs.append(neg)
+        assert np.array_equal(np.concatenate(negs), g[f"train_neg_epoch{ep}"]), ep
+    assert np.array_equal(np.random.randint(0, 1 << 30, 4), g["train_after"])
+    assert look.epochs == 2 and look.enabled
+
+
+def test_train_lookahead_gives_way_to_a_loop_it_did_not_predict():
+    from zebra_b200.batches import TrainLookahead
+    g = H.load("pass_schedule")
+    data = _train(g)
+    sizes = [200, 200, 200, 77, 200, 13, 200]
+    plain = RandEdgeSampler(data.sources, data.destinations)
+    np.random.seed(5)
+    want = [plain.sample(s)[1] for s in sizes]
+    tail = np.random.randint(0, 1 << 30, 4)
+    sampler = RandEdgeSampler(data.sources, data.destinations)
+    look = TrainLookahead(data)
+    np.random.seed(5)
+    got = [look.take(sampler, s, sampler.sample)[1] for s in sizes]
+    assert all(np.array_equal(a, b) for a, b in zip(got, want))
+    assert np.array_equal(np.random.randint(0, 1 << 30, 4), tail)
+    assert not look.enabled

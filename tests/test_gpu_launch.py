@@ -15,6 +15,7 @@ pytestmark = pytest.mark.gpu
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF = os.path.join(ROOT, "baseline", "_ref")
+STDERR = {}
 
 
 def _run(level, work, name, strategy):
@@ -31,6 +32,7 @@ def _run(level, work, name, strategy):
     val = re.findall(r"val ap: ([\d.]+), new node val ap: ([\d.]+)", text)
     test = re.findall(r"Test statistics: (Old|New) nodes -- auc: ([\d.]+), ap: ([\d.]+)", text)
     assert val and len(test) == 2, text[-2000:]
+    STDERR[level] = r.stderr
     return [float(x) for x in val[-1]] + [float(ap) for _, _, ap in test], [x for x in val[-1]] + [ap for _, _, ap in test]
 
 
@@ -51,3 +53,14 @@ def test_train_py_through_launcher_matches_reference(tmp_path, strategy):
     for level in ("1", "2", "3"):
         for a, b in zip(res[level][0], ref_v):
             assert abs(a - b) <= 0.002, (level, res[level][1], ref_s)       # 0.2 AP points
+    if strategy == "streaming":
+        # level 3 assembles every pass before its loop and announces it to the finder (zebra_b200/batches.py): the
+        # training epoch and the four validation / test passes were served from rows computed ahead, none rolled back
+        m = re.search(r"zebra_b200 announced passes: (\{.*\})", STDERR["3"])
+        assert m, STDERR["3"][-2000:]
+        import json
+        summ = json.loads(m.group(1))
+        assert summ["train"]["passes"] == 1 and summ["train"]["served"] == summ["train"]["batches"] > 0, summ
+        assert summ["eval"]["passes"] >= 2 and summ["eval"]["served"] == summ["eval"]["batches"] > 0, summ
+        assert summ["train"]["rolled_back"] == 0 and summ["eval"]["rolled_back"] == 0, summ
+        assert summ["train"]["launches"] < summ["train"]["batches"], summ

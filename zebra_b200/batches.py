@@ -17,13 +17,20 @@ and the sampler is seeded and reset at the top of the pass (evaluation.py:9-10).
 
 `RandEdgeSampler` mirrors utils/util.py:69-86 (same constructor, same draws) for callers that do not import the
 reference; `read_edge_csv` reads the `ml_{name}.csv` edge list (utils/data_processing.py:81-91).
-The training loop's batches depend on an unseeded global numpy stream (train.py:203) and are not announced.
+The training loop draws its negatives from numpy's GLOBAL stream (train.py:88 seeds it, train.py:203 /
+utils/util.py:79-80 are its only consumers in the reference), so its epoch is predictable as well: `TrainLookahead`
+(installed on the reference's RandEdgeSampler by `install()`, launcher level 3) draws the whole epoch at the epoch's
+first `sample()` call — same calls, same order, hence the same numbers and the same stream position at the end of
+the epoch — announces the epoch to the finder and hands the draws out call by call.  A call that asks for another
+size than predicted puts the global stream back to where the reference's loop would have it and ends the lookahead.
 """
 from __future__ import annotations
 
 import math
 
 import numpy as np
+
+PASS_LOG = []          # one stats dict per announced pass (diagnostics; the launcher prints a summary at exit)
 
 
 class RandEdgeSampler:
@@ -108,7 +115,7 @@ class PassSchedule:
         return self._dev
 
     # ---- the streaming finder runs ahead of the loop ----
-    def announce(self, model_or_finder, window=64):
+    def announce(self, model_or_finder, window=64, kind="eval"):
         """Announce the pass to the streaming finder of `model_or_finder` (a zebra_b200 tppr_finder, or a model whose
         embedding module holds one with tppr_strategy 'streaming').  Returns True if it was announced."""
         from .finder import tppr_finder
@@ -123,6 +130,7 @@ class PassSchedule:
         self._finder = f
         self._announced = f.schedule_pass(self.sources, self.destinations, self.negatives, self.timestamps,
                                           self.edge_idxs, self.batch_size, window)
+        PASS_LOG.append({"kind": kind, "pass": self._announced})
         return True
 
     def stats(self):
@@ -136,3 +144,112 @@ class PassSchedule:
         self._last = a or self._last
         if a is not None and self._finder is not None and self._finder._sched is a:
             a.abandon()
+
+
+class TrainLookahead:
+    """The training epoch of the reference's loop (train.py:195-203), assembled at its first batch.
+
+    `train_data`: the split the loop slices (utils/data_processing.py:107, element 1 of get_data's result).
+    `take(sampler, size, draw)` stands in for `sampler.sample(size)` of the UNSEEDED sampler; `draw(size)` is the
+    sampler's original method.  Nothing else in the reference reads numpy's global stream, so drawing batch b+1..B
+    before batch b is consumed changes no number; the stream position after the epoch's last call is the
+    reference's.  Between epochs nothing is drawn ahead."""
+
+    def __init__(self, train_data, window=64, finder=None):
+        self.data = train_data
+        self.window = int(window)
+        self.finder = finder            # callable returning the streaming finder to announce to (or None)
+        self.sizes, self.draws, self.states, self.k = [], [], [], 0
+        self.enabled = True
+        self.epochs = 0
+        self._announced = None
+
+    def _begin_epoch(self, size, draw):
+        n = len(self.data.sources)
+        bs = int(size)
+        self.sizes = [bs] * (n // bs) + ([n % bs] if n % bs else [])
+        self.state0 = np.random.get_state()
+        self.draws, self.states = [], []
+        for s in self.sizes:
+            self.draws.append(draw(s))
+            self.states.append(np.random.get_state())
+        self.k = 0
+        self.epochs += 1
+        f = self.finder() if self.finder is not None else None
+        if f is not None and self.sizes:
+            neg = np.concatenate([d[1] for d in self.draws])
+            self._announced = f.schedule_pass(self.data.sources, self.data.destinations, neg, self.data.timestamps,
+                                              self.data.edge_idxs, bs, self.window)
+            PASS_LOG.append({"kind": "train", "pass": self._announced})
+
+    def take(self, sampler, size, draw):
+        n = len(self.data.sources)
+        if not self.enabled or n == 0 or size <= 0:
+            return draw(size)
+        if self.k >= len(self.sizes):
+            if size > n:
+                return draw(size)
+            self._begin_epoch(size, draw)
+        if size != self.sizes[self.k]:
+            # not the loop that was predicted: the global stream goes back to where that loop has it
+            np.random.set_state(self.states[self.k - 1] if self.k else self.state0)
+            a, self._announced = self._announced, None
+            if a is not None:
+                a.abandon()
+            self.enabled = False
+            self.sizes, self.draws, self.states, self.k = [], [], [], 0
+            return draw(size)
+        out = self.draws[self.k]
+        self.draws[self.k] = None
+        self.k += 1
+        return out
+
+
+def pass_summary():
+    """Counts over PASS_LOG: {kind: {passes, batches, served, launches, rolled_back}}."""
+    out = {}
+    for e in PASS_LOG:
+        a = e["pass"]
+        d = out.setdefault(e["kind"], {"passes": 0, "batches": 0, "served": 0, "launches": 0, "rolled_back": 0})
+        d["passes"] += 1
+        d["batches"] += a.n_batches
+        d["served"] += a.hits
+        d["launches"] += a.launches
+        d["rolled_back"] += int(a.rolled_back)
+    return out
+
+
+def _live_streaming_finder():
+    from .finder import tppr_finder
+    for r in reversed(tppr_finder._live):      # train.py builds one model per run: the newest finder is the one in use
+        f = r()
+        if f is not None:
+            return f
+    return None
+
+
+def install(window=64):
+    """Launcher level 3: the reference's unseeded RandEdgeSampler (the training sampler, train.py:140) hands out an
+    epoch drawn at its first batch, and that epoch is announced to the streaming finder.  The seeded samplers
+    (validation / test) are left alone — their passes are announced by metrics.eval_edge_prediction."""
+    import utils.data_processing as dp          # the reference's modules (reference root is on sys.path)
+    import utils.util as U
+    state = {}
+    get_data = dp.get_data
+
+    def get_data_capture(*a, **kw):
+        res = get_data(*a, **kw)
+        state["look"] = TrainLookahead(res[1], window, _live_streaming_finder)
+        return res
+    dp.get_data = get_data_capture
+    sample = U.RandEdgeSampler.sample
+
+    def sample_ahead(self, size):
+        look = state.get("look")
+        if self.seed is not None or look is None or len(self.src_list) == 0:
+            return sample(self, size)
+        if state.setdefault("sampler", self) is not self:      # a second unseeded sampler: not the loop we know
+            return sample(self, size)
+        return look.take(self, size, lambda s: sample(self, s))
+    U.RandEdgeSampler.sample = sample_ahead
+    return state

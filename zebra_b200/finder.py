@@ -16,6 +16,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import weakref
 
 import numpy as np
 import torch
@@ -32,6 +33,8 @@ def _ptr(a):
 
 
 class tppr_finder:  # noqa: N801  (name kept from the reference)
+    _live = []          # weak references to the finders alive in this process, oldest first (batches.install)
+
     def __init__(self, num_nodes, k, n_tppr, alpha_list, beta_list, device=None, strict_snapshots=None, tie_mode=None):
         if not torch.cuda.is_available():
             raise RuntimeError("zebra_b200.tppr_finder needs a CUDA device (B200, sm_100a); there is no CPU fallback")
@@ -64,6 +67,7 @@ class tppr_finder:  # noqa: N801  (name kept from the reference)
         self._host_out = None
         self._tables = None
         self._sched = None              # an announced pass (schedule_pass), see _ScheduledPass
+        tppr_finder._live[:] = [r for r in tppr_finder._live if r() is not None] + [weakref.ref(self)]
         self.reset_val_tppr()
         self.reset_tppr()
 
@@ -414,13 +418,18 @@ class _ScheduledPass:
         self.n_batches = (self.n + self.bs - 1) // self.bs if self.n else 0
         self.next = 0                   # next batch a call is expected to bring
         self.w0 = self.w1 = 0           # batches [w0, w1) have been streamed
-        self.snap = None                # the tables before batch w0
+        self.snap = self.snap_ids = None    # the records of the window's endpoints before batch w0
         self.hits = self.launches = 0
         self.rolled_back = False
-        self.plan = self.out = None
+        self.plan = self.out = self.ends = None
         if self.n_batches:
             self.plan = finder.make_plan(self.src, self.dst, self.neg, self.ts, self.eidx, self.bs, 3)
             self.out = self.plan.alloc_out(min(self.window, self.n_batches))
+            # endpoints of every edge on the device, once per pass (index lists of the per-window record copies)
+            self.ends = torch.from_numpy(np.stack([self.src, self.dst]).astype(np.int64)).to(finder.device)
+
+    def _rows(self, table):
+        return table.view(torch.int64).view(-1, self.f._record_bytes // 8)
 
     def _matches(self, b, nodes, ts, eidx):
         lo = b * self.bs
@@ -439,7 +448,11 @@ class _ScheduledPass:
         f = self.f
         if b >= self.w1:
             cnt = min(self.window, self.n_batches - b)
-            self.snap = [t.clone() for t in f._tables]
+            # what a roll-back needs: the records of the window's endpoints as they are now (negatives are only
+            # read).  Duplicates stay in the index list: every copy of a node carries the same record.
+            lo, hi = b * self.bs, min(self.n, (b + cnt) * self.bs)
+            self.snap_ids = self.ends[:, lo:hi].reshape(-1)
+            self.snap = [self._rows(t).index_select(0, self.snap_ids) for t in f._tables]
             self.plan.run(b, cnt, cnt, out=self.out, out_slots=cnt)
             self.w0, self.w1 = b, b + cnt
             self.launches += 1
@@ -465,23 +478,25 @@ class _ScheduledPass:
             # the window ran ahead of the calls: back to its start, then the consumed part of it again (as one
             # update-only span: a plan's batches run strictly in order, and rows are not needed a second time)
             for t, s0 in zip(f._tables, self.snap):
-                t.copy_(s0)
+                self._rows(t).index_copy_(0, self.snap_ids, s0)
             if self.next > self.w0:
-                redo = (self.w0 * self.bs, self.next * self.bs)
+                lo, hi = self.w0 * self.bs, self.next * self.bs
+                redo = (self.src[lo:hi], self.dst[lo:hi], self.ts[lo:hi], self.eidx[lo:hi])
             self.rolled_back = True
         self._finish()
         if redo is not None:
-            lo, hi = redo
-            f._update_only(self.src[lo:hi], self.dst[lo:hi], self.ts[lo:hi], self.eidx[lo:hi])
+            f._update_only(*redo)
 
     def _finish(self):
         f = self.f
         if f._sched is self:
             f._sched = None
-        self.snap = None
+        self.snap = self.snap_ids = None
         if self.plan is not None:
             torch.cuda.current_stream(f.device).synchronize()    # the plan's device arrays are freed below
             self.plan.close()
             self.plan = None
+        # what the pass held: the ring stays alive only through the rows handed out last
+        self.out = self.ends = self.src = self.dst = self.neg = self.ts = self.eidx = None
 
     cancel = abandon

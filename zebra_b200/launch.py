@@ -11,7 +11,10 @@
             3: level 2 plus the raw messages of a batch built by one kernel (zebra_b200/messages.py) and the
                link-prediction metrics off scikit-learn (zebra_b200/metrics.py): validation and
                test passes score their batches on the device with one D2H per pass, the training loop's per-batch
-               metrics use cheap host restatements of the same definitions;
+               metrics use cheap host restatements of the same definitions; every pass (training epochs included) is
+               assembled before its loop and announced to the streaming finder, which streams it a window of
+               batches ahead of the model's per-batch queries (zebra_b200/batches.py; ZEBRA_PASS_SCHEDULE=0 turns
+               it off);
             0: only the finder classes are replaced (numpy in / numpy out, the strict drop-in);
             ref: nothing is replaced (the reference's numba CPU path; used for the side-by-side runs).
 `--workdir` directory to run in; the reference reads `../data/{name}/ml_{name}.csv|.npy` relative to it
@@ -63,9 +66,14 @@ def install(level: str):
         embedding.LAZY_MEMORY = level in ("2", "3")
         embedding.patch(em.GraphDiffusionEmbedding)
     if level == "3":
-        from . import messages, metrics
+        from . import batches, messages, metrics
         metrics.install()
         messages.install()
+        if os.environ.get("ZEBRA_PASS_SCHEDULE", "1") != "0":
+            import atexit
+            import json
+            batches.install(int(os.environ.get("ZEBRA_PASS_WINDOW", "64")))
+            atexit.register(lambda: print("zebra_b200 announced passes: " + json.dumps(batches.pass_summary()), file=sys.stderr))
 
 
 def main(argv=None):
