@@ -1,5 +1,5 @@
 """Timing probe of the two stateless kernels next to the span kernel: the fused neighbour gather
-(gather_fwd_kernel / gather_bwd_kernel) and the pruning query (prune_topk_kernel).  CUDA events,
+(gather_fwd8_kernel / gather_bwd_sorted_kernel) and the pruning query (prune_topk_kernel).  CUDA events,
 L2 flushed between timed launches, algorithmic bytes per SURVEY.md section 8(d).
 
     python tools/perf_kernels.py            # prints one line per case

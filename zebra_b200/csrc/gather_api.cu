@@ -1,6 +1,7 @@
 // gather_api.cu — C ABI of the fused neighbour gather (include/zebra_tppr.h, "neighbour gather").
 // Stateless: every pointer is caller-owned device memory; the call only enqueues kernels on `stream`.
 #include "common.cuh"
+#include <cstdlib>
 #include "gather_device.cuh"
 #include "../../include/zebra_tppr.h"
 
@@ -51,11 +52,21 @@ int gather_fwd_impl(const void *dev_topk, int32_t n_tppr, int64_t rows, int32_t 
     const bool vec = dim_mem % 4 == 0 && dim_edge % 4 == 0 && dim_time % 4 == 0 && aligned16(dev_memory) &&
                      aligned16(dev_edge_feat) && aligned16(dev_time_w) && aligned16(dev_time_b) && aligned16(dev_x) &&
                      (!dev_src_rows || aligned16(dev_src_rows)) && (!dev_upd_rows || aligned16(dev_upd_rows));
-    const int64_t warps = static_cast<int64_t>(n_tppr) * rows * k + (dev_src_rows ? rows : 0);
-    const unsigned blocks = static_cast<unsigned>((warps + 7) / 8);
+    const int64_t slots = static_cast<int64_t>(n_tppr) * rows * k;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    if (vec) zebra::gather_fwd_kernel<true><<<blocks, 256, 0, st>>>(p);
-    else zebra::gather_fwd_kernel<false><<<blocks, 256, 0, st>>>(p);
+    static const bool one_slot = getenv("ZEBRA_GATHER_ONE_SLOT") && atoi(getenv("ZEBRA_GATHER_ONE_SLOT")) != 0;   // developer knob
+    if (!one_slot) {
+        // eight slots per warp (gather_fwd8_kernel)
+        const int64_t warps = (slots + zebra::kGatherGroup - 1) / zebra::kGatherGroup + (dev_src_rows ? rows : 0);
+        const unsigned blocks = static_cast<unsigned>((warps + 7) / 8);
+        if (vec) zebra::gather_fwd8_kernel<true><<<blocks, 256, 0, st>>>(p);
+        else zebra::gather_fwd8_kernel<false><<<blocks, 256, 0, st>>>(p);
+    } else {
+        const int64_t warps = slots + (dev_src_rows ? rows : 0);
+        const unsigned blocks = static_cast<unsigned>((warps + 7) / 8);
+        if (vec) zebra::gather_fwd_kernel<true><<<blocks, 256, 0, st>>>(p);
+        else zebra::gather_fwd_kernel<false><<<blocks, 256, 0, st>>>(p);
+    }
     CU(cudaGetLastError());
     return 0;
 }

@@ -15,6 +15,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <type_traits>
 
 namespace zebra {
 
@@ -123,6 +124,119 @@ gather_fwd_kernel(const GatherParams p)
         }
     } else if (p.src_rows && warp < slots + p.R) {
         const int64_t r = warp - slots;
+        const int node = p.src_nodes[r];
+        if (node < 0 || node >= p.num_nodes) { if (lane == 0) atomicExch(p.status, 1); }
+        else copy_row<VEC>(p.src_rows + static_cast<size_t>(r) * p.Dm, memory_row(p, node), p.Dm, lane);
+    }
+}
+
+// The same gather with EIGHT consecutive slots per warp (VEC: rows are 16-byte multiples, float4 items; otherwise
+// float items — configs without edge features have De = 1).  Why: with one slot per warp the row copies keep 25 / 43 of 32 lanes busy per
+// pass and, worse, every warp runs cosf twice — the lanes of the slowest-decaying time dimensions (dt*w beyond
+// 105,615: Payne-Hanek reduction) and all the others diverge.  Here
+//   * the 8 x (Dm + De)/4 float4 items of the group are walked as ONE flat list (all 32 lanes busy, four
+//     independent loads in flight per lane before the first store);
+//   * the time encoding gives lane l the slot l & 7 and the dimension quads (l >> 3) + 4t: in pass t every lane of
+//     the warp works on the same four quads, so the slow reduction is paid in the first pass (or two) by all
+//     lanes together and the remaining passes are uniformly fast.
+// Arithmetic per element is unchanged (fmul, fadd, cosf): bit-identical to the one-slot kernel.
+constexpr int kGatherGroup = 8;
+constexpr int kGatherLoads = 4;      // independent loads a lane has in flight before its first store (8: -10 % on large launches)
+
+template <bool VEC>
+__global__ void __launch_bounds__(256)
+gather_fwd8_kernel(const GatherParams p)
+{
+    typedef typename std::conditional<VEC, float4, float>::type T;      // unit of the row copies
+    constexpr int kSh = VEC ? 2 : 0;
+    __shared__ const T *s_mem[8][kGatherGroup];
+    __shared__ const T *s_edge[8][kGatherGroup];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int64_t warp = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t slots = static_cast<int64_t>(p.n_tppr) * p.R * p.k;
+    const int64_t groups = (slots + kGatherGroup - 1) / kGatherGroup;
+    const int64_t plane = p.R * p.k;
+    const int Du = (p.Dm + p.De + p.Dt) >> kSh, Dmu = p.Dm >> kSh, W = (p.Dm + p.De) >> kSh;
+    if (warp < groups) {
+        // lane l (and l + 8, l + 16, l + 24) looks after slot first + (l & 7)
+        const int64_t slot = warp * kGatherGroup + (lane & 7);
+        bool ok = false;
+        float dt = 0.f;
+        if (slot < slots) {
+            const int64_t j = static_cast<uint32_t>(slot) / static_cast<uint32_t>(plane), o = slot - j * plane;
+            const char *base = p.topk + static_cast<size_t>(j) * plane * 16;
+            const int node = reinterpret_cast<const int32_t *>(base)[o];
+            const int eidx = reinterpret_cast<const int32_t *>(base + plane * 4)[o];
+            dt = reinterpret_cast<const float *>(base + plane * 8)[o];
+            ok = node >= 0 && node < p.num_nodes && eidx >= 0 && eidx < p.n_edge_rows;
+            if (!ok && lane < kGatherGroup) atomicExch(p.status, 1);
+            if (ok && lane < kGatherGroup) {
+                s_mem[wib][lane] = reinterpret_cast<const T *>(memory_row(p, node));
+                s_edge[wib][lane] = reinterpret_cast<const T *>(p.edge_feat + static_cast<size_t>(eidx) * p.De);
+            }
+            // normalised weights of the row this slot starts (left-to-right fp32 sum, as the one-slot kernel)
+            const int64_t row = static_cast<uint32_t>(o) / static_cast<uint32_t>(p.k);
+            if (lane < kGatherGroup && o - row * p.k == 0) {
+                const float *w = reinterpret_cast<const float *>(base + plane * 12) + row * p.k;
+                float *out = p.wn + static_cast<size_t>(j) * plane + row * p.k;
+                float sum = 0.f;
+                for (int c = 0; c < p.k; ++c) sum = __fadd_rn(sum, w[c]);
+                for (int c = 0; c < p.k; ++c) out[c] = (sum == 0.f) ? 0.f : __fdiv_rn(w[c], sum);
+            }
+        }
+        const unsigned vmask = __ballot_sync(0xffffffffu, ok) & 0xffu;
+        __syncwarp();
+        T *xg = reinterpret_cast<T *>(p.X) + static_cast<size_t>(warp) * kGatherGroup * Du;
+        // ---- memory row | edge row of the 8 slots: one flat list of 8 * W items ----
+        int sl = 0, c = lane;
+        while (c >= W) { c -= W; ++sl; }
+        while (sl < kGatherGroup) {
+            T v[kGatherLoads];
+            T *d[kGatherLoads];
+            #pragma unroll
+            for (int u = 0; u < kGatherLoads; ++u) {
+                d[u] = nullptr;
+                if (sl < kGatherGroup) {
+                    if ((vmask >> sl) & 1u) {
+                        const T *src = c < Dmu ? s_mem[wib][sl] + c : s_edge[wib][sl] + (c - Dmu);
+                        v[u] = __ldg(src);
+                        d[u] = xg + static_cast<size_t>(sl) * Du + c;
+                    }
+                    c += 32;
+                    while (c >= W) { c -= W; ++sl; }
+                }
+            }
+            #pragma unroll
+            for (int u = 0; u < kGatherLoads; ++u)
+                if (d[u]) *d[u] = v[u];
+        }
+        // ---- time encoding: lane -> slot (lane & 7); pass t covers dimensions [16t, 16t + 16) of all 8 slots ----
+        if (ok) {
+            if (VEC) {
+                float4 *xt = reinterpret_cast<float4 *>(xg) + static_cast<size_t>(lane & 7) * Du + W;
+                for (int c4 = lane >> 3; c4 < (p.Dt >> 2); c4 += 4) {
+                    const float4 w = __ldg(reinterpret_cast<const float4 *>(p.time_w) + c4);
+                    const float4 b = __ldg(reinterpret_cast<const float4 *>(p.time_b) + c4);
+                    float4 r;
+                    r.x = cos_arg(__fadd_rn(__fmul_rn(dt, w.x), b.x)); r.y = cos_arg(__fadd_rn(__fmul_rn(dt, w.y), b.y));
+                    r.z = cos_arg(__fadd_rn(__fmul_rn(dt, w.z), b.z)); r.w = cos_arg(__fadd_rn(__fmul_rn(dt, w.w), b.w));
+                    xt[c4] = r;
+                }
+            } else {
+                // scalar rows: store u of a pass writes four adjacent floats per slot (lanes l, l+8, l+16, l+24)
+                float *xt = reinterpret_cast<float *>(xg) + static_cast<size_t>(lane & 7) * Du + W;
+                for (int c0 = 0; c0 < p.Dt; c0 += 16) {
+                    #pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int cc = c0 + 4 * u + (lane >> 3);
+                        if (cc < p.Dt)
+                            xt[cc] = cos_arg(__fadd_rn(__fmul_rn(dt, __ldg(p.time_w + cc)), __ldg(p.time_b + cc)));
+                    }
+                }
+            }
+        }
+    } else if (p.src_rows && warp < groups + p.R) {
+        const int64_t r = warp - groups;
         const int node = p.src_nodes[r];
         if (node < 0 || node >= p.num_nodes) { if (lane == 0) atomicExch(p.status, 1); }
         else copy_row<VEC>(p.src_rows + static_cast<size_t>(r) * p.Dm, memory_row(p, node), p.Dm, lane);
