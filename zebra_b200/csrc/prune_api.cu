@@ -5,6 +5,7 @@
 #include "../../include/zebra_tppr.h"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 
@@ -24,6 +25,8 @@ struct zebra_csr {
     char *scratch = nullptr;
     size_t scratch_cap = 0;
     int sms = 0;
+    int smem_max = 0;               // opt-in shared memory per block of the device
+    size_t smem_set = 0;            // dynamic shared memory the kernel has been allowed so far
     int64_t launches = 0;
 };
 
@@ -127,18 +130,38 @@ int zebra_prune_topk(zebra_csr_t *c, const int32_t *host_q_nodes, const double *
         }
         outp = c->out_dev;
     }
-    // grid: enough warps to cover the queries, at most 8 blocks of 8 warps per SM
-    const int warps_per_block = 8;
-    int64_t blocks = std::min<int64_t>((nq + warps_per_block - 1) / warps_per_block, static_cast<int64_t>(c->sms) * 8);
     const size_t per_warp = zebra::prune_scratch_bytes(t_max);
-    // very wide/deep queries: bound the work area to 2 GB by running fewer warps
-    while (blocks > 1 && per_warp * warps_per_block * static_cast<size_t>(blocks) > (2ull << 30)) blocks = (blocks + 1) / 2;
-    const size_t need = per_warp * warps_per_block * static_cast<size_t>(blocks);
-    if (c->scratch_cap < need) {
-        CU(cudaStreamSynchronize(st));
-        if (c->scratch) CU(cudaFree(c->scratch));
-        CU(cudaMalloc(&c->scratch, need));
-        c->scratch_cap = need;
+    // the per-warp work areas live in shared memory when a block of 8 (4, 2, 1) warps fits its share of the SM
+    // (ZEBRA_PRUNE_GLOBAL_SCRATCH=1: the round-1 layout in global memory, a developer knob)
+    static const bool force_global = getenv("ZEBRA_PRUNE_GLOBAL_SCRATCH") && atoi(getenv("ZEBRA_PRUNE_GLOBAL_SCRATCH")) != 0;
+    int warps_per_block = 8;
+    size_t smem = 0;
+    if (!force_global) {
+        if (!c->smem_max) CU(cudaDeviceGetAttribute(&c->smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, c->device));
+        const size_t room = std::min<size_t>(static_cast<size_t>(c->smem_max), 200u << 10);
+        for (int w = 8; w >= 1 && !smem; w >>= 1)
+            if (per_warp * w <= room) { warps_per_block = w; smem = per_warp * w; }
+    }
+    int64_t blocks;
+    if (smem) {
+        if (smem > c->smem_set) {
+            CU(cudaFuncSetAttribute(zebra::prune_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+            c->smem_set = smem;
+        }
+        const int64_t per_sm = std::max<int64_t>(1, std::min<int64_t>(8, (220u << 10) / (smem + 1024)));
+        blocks = std::min<int64_t>((nq + warps_per_block - 1) / warps_per_block, static_cast<int64_t>(c->sms) * per_sm);
+    } else {
+        // grid: enough warps to cover the queries, at most 8 blocks of 8 warps per SM
+        blocks = std::min<int64_t>((nq + warps_per_block - 1) / warps_per_block, static_cast<int64_t>(c->sms) * 8);
+        // very wide/deep queries: bound the work area to 2 GB by running fewer warps
+        while (blocks > 1 && per_warp * warps_per_block * static_cast<size_t>(blocks) > (2ull << 30)) blocks = (blocks + 1) / 2;
+        const size_t need = per_warp * warps_per_block * static_cast<size_t>(blocks);
+        if (c->scratch_cap < need) {
+            CU(cudaStreamSynchronize(st));
+            if (c->scratch) CU(cudaFree(c->scratch));
+            CU(cudaMalloc(&c->scratch, need));
+            c->scratch_cap = need;
+        }
     }
     zebra::PruneParams p;
     memset(&p, 0, sizeof p);
@@ -154,8 +177,8 @@ int zebra_prune_topk(zebra_csr_t *c, const int32_t *host_q_nodes, const double *
     p.o_dt = reinterpret_cast<float *>(p.o_eidx + plane);
     p.o_w = p.o_dt + plane;
     p.o_filled = reinterpret_cast<int32_t *>(p.o_w + plane);
-    p.scratch = c->scratch; p.scratch_per_warp = per_warp;
-    zebra::prune_topk_kernel<<<static_cast<unsigned>(blocks), warps_per_block * 32, 0, st>>>(p);
+    p.scratch = smem ? nullptr : c->scratch; p.scratch_per_warp = per_warp;
+    zebra::prune_topk_kernel<<<static_cast<unsigned>(blocks), warps_per_block * 32, smem, st>>>(p);
     CU(cudaGetLastError());
     c->launches++;
     if (host_out) {

@@ -31,8 +31,8 @@ struct PruneParams {
     int32_t *o_node, *o_eidx;   // [nq, k]
     float *o_dt, *o_w;
     int32_t *o_filled;          // [nq] 1 = the reference would have written this row
-    char *scratch;              // per-warp work area
-    size_t scratch_per_warp;
+    char *scratch;              // per-warp work areas in global memory, or NULL: the work areas are the block's
+    size_t scratch_per_warp;    // dynamic shared memory (blockDim.x / 32 areas of scratch_per_warp bytes)
 };
 
 // bytes of per-warp scratch for t_max states
@@ -110,7 +110,11 @@ prune_topk_kernel(const PruneParams p)
     const int64_t n_warps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
     const unsigned full = 0xffffffffu;
     const int T = p.t_max + 2;
-    char *base = p.scratch + static_cast<size_t>(warp) * p.scratch_per_warp;
+    // the work area of a query is read and written dozens of times per state by dependent steps: in shared memory
+    // when the host found room for it (the usual width 10-20, depth 2 needs 5-19 KB per warp), else in global memory
+    extern __shared__ __align__(16) char prune_smem[];
+    char *base = p.scratch ? p.scratch + static_cast<size_t>(warp) * p.scratch_per_warp
+                           : prune_smem + static_cast<size_t>(threadIdx.x >> 5) * p.scratch_per_warp;
     double *s_ts = reinterpret_cast<double *>(base);
     double *s_w = s_ts + T;
     double *d_val = s_w + T;
