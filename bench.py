@@ -599,6 +599,21 @@ def run_ours(args):
         f.streaming_topk(*b)
     call_s = time.perf_counter() - t0
     call_edges = sum(len(b[2]) for b in batches)
+    # the call the launcher's levels 1-3 make: rows left on the device (streaming_topk_raw), per call and on an
+    # announced pass (tppr_finder.schedule_pass: the batches streamed 64 per launch ahead of the calls)
+    dev_s = {}
+    hi_e = min(E, nb_call * BS)
+    for mode in ("per_call", "announced"):
+        f.reset_tppr()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        if mode == "announced":
+            f.schedule_pass(st.src[:hi_e], st.dst[:hi_e], neg[:hi_e], st.ts[:hi_e], st.eidx[:hi_e], BS, 64)
+        for b in batches:
+            f.streaming_topk_raw(*b)
+        torch.cuda.synchronize()
+        dev_s[mode] = time.perf_counter() - t0
+    f.sync_check()
 
     t = torch.tensor([ms, e2e_s], dtype=torch.float64, device=dev)
     if world > 1:
@@ -630,7 +645,11 @@ def run_ours(args):
                             f"batch; windows of {args.e2e_window} batches pipelined: host dependency pass, H2D, kernel, D2H)",
                     "launches_per_step": launches_e2e,
                     "per_call_drop_in": {"value": (1 if split else world) * call_edges / call_s, "unit": UNIT,
-                                         "what": f"first {nb_call} batches, one synchronous streaming_topk call per batch"}},
+                                         "what": f"first {nb_call} batches, one synchronous streaming_topk call per batch"},
+                    "per_call_device_rows": {"value": (1 if split else world) * call_edges / dev_s["per_call"],
+                                             "announced_pass": (1 if split else world) * call_edges / dev_s["announced"], "unit": UNIT,
+                                             "what": "same batches through streaming_topk_raw (rows stay in HBM: what the launcher's "
+                                                     "levels 1-3 call), per call and with the pass announced to the finder first"}},
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak * (world if split else 1), "unit": "GB/s",
