@@ -426,7 +426,7 @@ class _ScheduledPass:
             self.plan = finder.make_plan(self.src, self.dst, self.neg, self.ts, self.eidx, self.bs, 3)
             self.out = self.plan.alloc_out(min(self.window, self.n_batches))
             # endpoints of every edge on the device, once per pass (index lists of the per-window record copies)
-            self.ends = torch.from_numpy(np.stack([self.src, self.dst]).astype(np.int64)).to(finder.device)
+            self.ends = torch.from_numpy(np.stack([self.src, self.dst])).to(finder.device)         # int32 [2, n]
 
     def _rows(self, table):
         return table.view(torch.int64).view(-1, self.f._record_bytes // 8)
@@ -435,9 +435,12 @@ class _ScheduledPass:
         lo = b * self.bs
         n = min(self.bs, self.n - lo)
         hi = lo + n
-        return (len(eidx) == n and len(nodes) == 3 * n and np.array_equal(eidx, self.eidx[lo:hi])
-                and np.array_equal(nodes[:n], self.src[lo:hi]) and np.array_equal(nodes[n:2 * n], self.dst[lo:hi])
-                and np.array_equal(nodes[2 * n:], self.neg[lo:hi]) and np.array_equal(ts[:n], self.ts[lo:hi]))
+        if len(eidx) != n or len(nodes) != 3 * n or len(ts) < n:
+            return False
+        # plain elementwise compares: np.array_equal's argument handling costs more than the compare at this size
+        return bool((eidx == self.eidx[lo:hi]).all() and (nodes[:n] == self.src[lo:hi]).all()
+                    and (nodes[n:2 * n] == self.dst[lo:hi]).all() and (nodes[2 * n:] == self.neg[lo:hi]).all()
+                    and (ts[:n] == self.ts[lo:hi]).all())
 
     def take(self, nodes, ts, eidx, rows_per_edge, inst):
         """The device rows of the call if it brings the next announced batch, else None (after settling)."""
@@ -478,7 +481,7 @@ class _ScheduledPass:
             # the window ran ahead of the calls: back to its start, then the consumed part of it again (as one
             # update-only span: a plan's batches run strictly in order, and rows are not needed a second time)
             for t, s0 in zip(f._tables, self.snap):
-                self._rows(t).index_copy_(0, self.snap_ids, s0)
+                self._rows(t).index_copy_(0, self.snap_ids.long(), s0)
             if self.next > self.w0:
                 lo, hi = self.w0 * self.bs, self.next * self.bs
                 redo = (self.src[lo:hi], self.dst[lo:hi], self.ts[lo:hi], self.eidx[lo:hi])
