@@ -1,6 +1,6 @@
 #!/bin/bash
 # One gpurun call: GPU parity tests, perf probe, bench (ours + reference arm), ncu launch list + full capture.
-# Usage (from the repo root on the GPU box): bash tools/gpu_check.sh [tests|probe|star|chain|stress|bench|configs|ncu|kernels|lazy|e2e|sanitize ...]
+# Usage (from the repo root on the GPU box): bash tools/gpu_check.sh [tests|probe|star|chain|stress|bench|configs|ncu|kernels|lazy|schedule|e2e|sanitize ...]
 set -u
 mkdir -p gpurun_out
 WHAT="${*:-tests probe bench ncu kernels lazy}"
@@ -29,7 +29,7 @@ ncu)
   done ;;
 kernels)
   timeout 600 python tools/perf_kernels.py > gpurun_out/kernels.log 2>&1; echo "kernels rc=$?"; cat gpurun_out/kernels.log
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:"gather_fwd|prune_topk" -c 6 -f -o gpurun_out/prof_kernels python tools/perf_kernels.py > gpurun_out/ncu_kernels.log 2>&1
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:"gather_fwd8|prune_topk" -c 6 -f -o gpurun_out/prof_kernels python tools/perf_kernels.py > gpurun_out/ncu_kernels.log 2>&1
   echo "ncu kernels rc=$?" ;;
 lazy)
   # lazy memory update (level 2): microbench + launch list of the selection / lazy gather kernels
@@ -54,6 +54,13 @@ stress)
 configs)
   for w in wikipedia reddit mooc superuser; do
     timeout 600 python bench.py --workload $w > gpurun_out/bench_$w.json 2> gpurun_out/bench_$w.err; echo "bench $w rc=$?"; done ;;
+schedule)
+  # announced passes: per-batch cost per call against an announced pass, four stream shapes; the
+  # allocation-free pruning entry point in a process of its own
+  for w in reddit:120000 wikitalk:400000 wikipedia:157474 superuser:400000; do
+    timeout 300 python tools/perf_schedule.py --workload ${w%%:*} --edges ${w##*:}
+  done > gpurun_out/perf_schedule.log 2>&1; cat gpurun_out/perf_schedule.log
+  timeout 300 python -m pytest tests/test_zz_no_alloc.py -m gpu -x -q > gpurun_out/pytest_noalloc_alone.log 2>&1; echo "no_alloc alone rc=$?" ;;
 e2e)
   # the reference's train.py, reference arm against levels 1 and 2 (three configs would take ~6 GPU-minutes: one here)
   timeout 1500 python tools/e2e_train.py --ref baseline/_ref --name ${E2E_NAME:-wikipedia} --epochs 2 --levels ref 1 2 3 --out gpurun_out/e2e 2>&1 | tail -5 ;;
