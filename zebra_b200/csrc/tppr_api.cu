@@ -163,7 +163,7 @@ struct zebra_tppr {
     size_t plan_stage_cap = 0;
     // hub chains (tppr_device.cuh "hub chains"): the chain nodes of the span being streamed
     bool chains_enabled = true;
-    int32_t max_chains = zebra::kMaxChains;
+    int32_t max_chains = 8;                     // chain nodes per span (ZEBRA_CHAINS, at most zebra::kMaxChains): 1-8 measured 2.5 % faster than 24 on the Wiki-Talk-shaped stream, equal on the Reddit- and MOOC-shaped ones
     std::vector<int32_t> chain_cnt;            // [num_nodes] scratch of the detection pass (zero between passes)
     int32_t *smflag = nullptr;                 // device [2 * kSmSlots]: chain warps running per SM, ticket warps standing aside
     int32_t tie_mode = 0;                      // 0 exact (numba's argsort), 1 stable (insertion order among equal scores)
