@@ -295,6 +295,7 @@ class tppr_finder:  # noqa: N801  (name kept from the reference)
     # ---- introspection (tests) ----
     def state(self, inst, nodes):
         """Vectors of `nodes` in instance `inst`: list of (eidx, node, ts, score, norm) in slot order."""
+        self._settle()          # an announced pass runs ahead of its calls: report the state the calls have reached
         ids = np.ascontiguousarray(nodes, dtype=np.int64)
         m, k = len(ids), self.k
         cnt = np.zeros(m, np.int32); e = np.zeros((m, k), np.int32); nd = np.zeros((m, k), np.int32)
@@ -366,6 +367,8 @@ class StreamPlan:
         if out is None and self.rows_per_edge:
             out = self.alloc_out(out_slots)
         f = self.f
+        if f._sched is not None and f._sched.plan is not self:
+            f._settle()         # another plan while a pass is announced: that pass ends first
         with torch.cuda.device(f.device):
             check(f._L.zebra_tppr_plan_run(f._h, self._p, first, n_batches, batches_per_launch,
                                            _ptr(out) if self.rows_per_edge else None, out_slots, f._stream_ptr()))
