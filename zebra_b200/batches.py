@@ -34,24 +34,20 @@ PASS_LOG = []          # one stats dict per announced pass (diagnostics; the lau
 
 
 class RandEdgeSampler:
-    """utils/util.py:69-86: negatives drawn uniformly from the distinct sources / destinations."""
+    """Same constructor, attributes and draws as utils/util.py:69-86: negatives are uniform over the DISTINCT
+    sources / destinations; `size` source indices are drawn first, then `size` destination indices, from the
+    sampler's own RandomState when seeded and from numpy's global stream otherwise."""
 
     def __init__(self, src_list, dst_list, seed=None):
-        self.seed = None
-        self.src_list = np.unique(src_list)
-        self.dst_list = np.unique(dst_list)
+        self.src_list, self.dst_list = np.unique(src_list), np.unique(dst_list)
+        self.seed = seed
         if seed is not None:
-            self.seed = seed
-            self.random_state = np.random.RandomState(self.seed)
+            self.reset_random_state()
 
     def sample(self, size):
-        if self.seed is None:
-            src_index = np.random.randint(0, len(self.src_list), size)
-            dst_index = np.random.randint(0, len(self.dst_list), size)
-        else:
-            src_index = self.random_state.randint(0, len(self.src_list), size)
-            dst_index = self.random_state.randint(0, len(self.dst_list), size)
-        return self.src_list[src_index], self.dst_list[dst_index]
+        rng = np.random if self.seed is None else self.random_state
+        picks = [rng.randint(0, len(pool), size) for pool in (self.src_list, self.dst_list)]     # sources first
+        return self.src_list[picks[0]], self.dst_list[picks[1]]
 
     def reset_random_state(self):
         self.random_state = np.random.RandomState(self.seed)
